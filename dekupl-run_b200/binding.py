@@ -1,0 +1,267 @@
+"""ctypes binding of libdekupl_b200.so (include/dekupl_b200.h)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+
+NF_REFERENCE, NF_FULL = 0, 1
+MAX_SAMPLES = 256
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class DkError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"dekupl_b200 error {code}: {msg}")
+        self.code = code
+
+
+def lib_path():
+    return os.path.join(_HERE, "libdekupl_b200.so")
+
+
+def declared_symbols():
+    """every dk_* function include/dekupl_b200.h declares"""
+    hdr = open(os.path.join(_HERE, "..", "include", "dekupl_b200.h")).read()
+    return sorted(set(re.findall(r"\b(dk_[a-z0-9_]+)\s*\(", hdr)))
+
+
+class PathStats(C.Structure):
+    _fields_ = [("U", C.c_uint64), ("R", C.c_uint64), ("R_pos", C.c_uint64), ("D", C.c_uint64),
+                ("ties", C.c_uint64 * 3), ("nf", C.c_double * MAX_SAMPLES),
+                ("ms_join", C.c_double), ("ms_nf", C.c_double), ("ms_ttest", C.c_double), ("ms_bh", C.c_double)]
+
+
+def load_library():
+    """Load the CUDA library. Fails loudly when it has not been built (no fallback)."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    p = lib_path()
+    if not os.path.exists(p):
+        raise DkError(-5, f"{p} not found: build it with dekupl-run_b200/csrc/build.sh (no CPU fallback exists)")
+    L = C.CDLL(p)
+    vp, u64, i32, dbl = C.c_void_p, C.c_uint64, C.c_int, C.c_double
+    P = C.POINTER
+    sig = {
+        "dk_init": (i32, [P(vp), i32]), "dk_free": (None, [vp]), "dk_last_error": (C.c_char_p, [vp]),
+        "dk_version": (C.c_char_p, []), "dk_set_stream": (i32, [vp, vp]), "dk_sync": (i32, [vp]),
+        "dk_launch_count": (u64, [vp]), "dk_stage_ms": (dbl, [vp, i32]),
+        "dk_join_counts": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, P(vp)]),
+        "dk_join_counts_dev": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, P(vp)]),
+        "dk_matrix_from_host": (i32, [vp, i32, u64, vp, vp, P(vp)]),
+        "dk_matrix_rows": (u64, [vp]), "dk_matrix_union": (u64, [vp]), "dk_matrix_samples": (i32, [vp]),
+        "dk_matrix_export": (i32, [vp, vp, u64, u64, vp, vp]),
+        "dk_matrix_export_dev": (i32, [vp, vp, u64, u64, vp, vp]),
+        "dk_matrix_checksum": (i32, [vp, vp, P(u64), P(u64)]), "dk_matrix_free": (None, [vp, vp]),
+        "dk_compute_nf": (i32, [vp, vp, i32, u64, P(dbl), P(u64)]),
+        "dk_nf_begin": (i32, [vp, vp, P(vp), P(u64)]), "dk_nf_set_rank": (i32, [vp, vp, u64]),
+        "dk_nf_hist_dev": (i32, [vp, vp, vp]), "dk_nf_advance_dev": (i32, [vp, vp, vp]),
+        "dk_nf_result": (i32, [vp, vp, P(dbl)]), "dk_nf_end": (None, [vp, vp]),
+        "dk_ttest_rows": (i32, [vp, vp, P(dbl), P(i32), i32, P(i32), i32, P(vp)]),
+        "dk_ttest_candidates": (i32, [vp, vp, dbl, P(u64), P(vp)]),
+        "dk_ttest_adjust_global": (i32, [vp, vp, vp, u64, u64]),
+        "dk_ttest_adjust": (i32, [vp, vp, dbl]),
+        "dk_ttest_filter": (i32, [vp, vp, dbl, dbl, P(u64), P(u64)]),
+        "dk_ttest_export_survivors": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+        "dk_ttest_export_rows": (i32, [vp, vp, vp, vp, vp]),
+        "dk_ttest_rows_count": (u64, [vp]), "dk_ttest_free": (None, [vp, vp]),
+        "dk_run_path": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, i32, P(i32), i32, P(i32), i32, dbl, dbl, i32,
+                              P(PathStats), P(vp), P(vp)]),
+    }
+    for name, (res, args) in sig.items():
+        f = getattr(L, name)
+        f.restype, f.argtypes = res, args
+    _LIB = L
+    return L
+
+
+def _np_ptr(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else C.c_void_p(0)
+
+
+class Matrix:
+    def __init__(self, ctx, handle):
+        self.ctx, self.h = ctx, handle
+
+    @property
+    def rows(self):
+        return int(self.ctx.L.dk_matrix_rows(self.h))
+
+    @property
+    def union(self):
+        return int(self.ctx.L.dk_matrix_union(self.h))
+
+    @property
+    def samples(self):
+        return int(self.ctx.L.dk_matrix_samples(self.h))
+
+    def export(self, row0=0, nrows=None, keys=True):
+        n = self.rows - row0 if nrows is None else nrows
+        k = np.empty(n, dtype=np.uint64) if keys else None
+        c = np.empty((n, self.samples), dtype=np.int32)
+        self.ctx._chk(self.ctx.L.dk_matrix_export(self.ctx.h, self.h, row0, n, _np_ptr(k), _np_ptr(c)))
+        return k, c
+
+    def checksum(self):
+        x, s = C.c_uint64(0), C.c_uint64(0)
+        self.ctx._chk(self.ctx.L.dk_matrix_checksum(self.ctx.h, self.h, C.byref(x), C.byref(s)))
+        return int(x.value), int(s.value)
+
+    def free(self):
+        if self.h:
+            self.ctx.L.dk_matrix_free(self.ctx.h, self.h)
+            self.h = None
+
+
+class TtestResult:
+    def __init__(self, ctx, handle, matrix):
+        self.ctx, self.h, self.matrix = ctx, handle, matrix
+        self.D = 0
+        self.ties = (0, 0, 0)
+
+    @property
+    def rows(self):
+        return int(self.ctx.L.dk_ttest_rows_count(self.h))
+
+    def adjust(self, p_cut):
+        self.ctx._chk(self.ctx.L.dk_ttest_adjust(self.ctx.h, self.h, float(p_cut)))
+
+    def candidates(self, p_cut):
+        n, p = C.c_uint64(0), C.c_void_p(0)
+        self.ctx._chk(self.ctx.L.dk_ttest_candidates(self.ctx.h, self.h, float(p_cut), C.byref(n), C.byref(p)))
+        return int(n.value), p.value
+
+    def adjust_global(self, all_p_dev_ptr, n_all, R_global):
+        self.ctx._chk(self.ctx.L.dk_ttest_adjust_global(self.ctx.h, self.h, C.c_void_p(all_p_dev_ptr), n_all, R_global))
+
+    def filter(self, pmax, fmin):
+        d, t = C.c_uint64(0), (C.c_uint64 * 3)()
+        self.ctx._chk(self.ctx.L.dk_ttest_filter(self.ctx.h, self.h, float(pmax), float(fmin), C.byref(d), t))
+        self.D, self.ties = int(d.value), tuple(int(x) for x in t)
+        return self.D
+
+    def export_rows(self, adj=True):
+        R = self.rows
+        p, f = np.empty(R), np.empty(R)
+        a = np.empty(R) if adj else None
+        self.ctx._chk(self.ctx.L.dk_ttest_export_rows(self.ctx.h, self.h, _np_ptr(p), _np_ptr(f), _np_ptr(a)))
+        return p, f, a
+
+    def export_survivors(self):
+        D, S = self.D, self.matrix.samples
+        out = dict(row=np.empty(D, np.uint64), key=np.empty(D, np.uint64), p_adj=np.empty(D), meanA=np.empty(D),
+                   meanB=np.empty(D), log2fc=np.empty(D), norm=np.empty((D, S)))
+        self.ctx._chk(self.ctx.L.dk_ttest_export_survivors(
+            self.ctx.h, self.h, _np_ptr(out["row"]), _np_ptr(out["key"]), _np_ptr(out["p_adj"]), _np_ptr(out["meanA"]),
+            _np_ptr(out["meanB"]), _np_ptr(out["log2fc"]), _np_ptr(out["norm"])))
+        return out
+
+    def free(self):
+        if self.h:
+            self.ctx.L.dk_ttest_free(self.ctx.h, self.h)
+            self.h = None
+
+
+class Context:
+    """One GPU, one caller thread (mirrors the single-threaded reference tools)."""
+
+    def __init__(self, device=0):
+        self.L = load_library()
+        h = C.c_void_p(0)
+        rc = self.L.dk_init(C.byref(h), int(device))
+        if rc != 0:
+            raise DkError(rc, self.L.dk_last_error(None).decode())
+        self.h = h
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise DkError(rc, self.L.dk_last_error(self.h).decode())
+
+    def close(self):
+        if self.h:
+            self.L.dk_free(self.h)
+            self.h = None
+
+    def set_stream(self, cuda_stream_ptr):
+        self._chk(self.L.dk_set_stream(self.h, C.c_void_p(cuda_stream_ptr)))
+
+    def sync(self):
+        self._chk(self.L.dk_sync(self.h))
+
+    @property
+    def launches(self):
+        return int(self.L.dk_launch_count(self.h))
+
+    def stage_ms(self, which):
+        return float(self.L.dk_stage_ms(self.h, which))
+
+    # ---- joinCounts -----------------------------------------------------------
+    @staticmethod
+    def _tables(keys, cnts, n):
+        S = len(keys)
+        kp, cp = (C.c_void_p * S)(*keys), (C.c_void_p * S)(*cnts)
+        nn = (C.c_uint64 * S)(*n)
+        return S, kp, cp, nn
+
+    def join_counts(self, keys, cnts, min_rec=1, min_abund=1, emit_stale_tail=False):
+        """keys/cnts: lists of numpy arrays (uint64 sorted / int32), one per sample (host)."""
+        keys = [np.ascontiguousarray(k, dtype=np.uint64) for k in keys]
+        cnts = [np.ascontiguousarray(c, dtype=np.int32) for c in cnts]
+        S, kp, cp, nn = self._tables([k.ctypes.data for k in keys], [c.ctypes.data for c in cnts], [len(k) for k in keys])
+        out = C.c_void_p(0)
+        self._chk(self.L.dk_join_counts(self.h, S, kp, cp, nn, min_rec, min_abund, int(emit_stale_tail), C.byref(out)))
+        return Matrix(self, out)
+
+    def join_counts_dev(self, key_ptrs, cnt_ptrs, n, min_rec=1, min_abund=1, emit_stale_tail=False):
+        """device pointers (ints), e.g. torch tensors' data_ptr()"""
+        S, kp, cp, nn = self._tables(key_ptrs, cnt_ptrs, n)
+        out = C.c_void_p(0)
+        self._chk(self.L.dk_join_counts_dev(self.h, S, kp, cp, nn, min_rec, min_abund, int(emit_stale_tail), C.byref(out)))
+        return Matrix(self, out)
+
+    def matrix_from_host(self, cnts, keys=None):
+        cnts = np.ascontiguousarray(cnts, dtype=np.int32)
+        R, S = cnts.shape
+        if keys is not None:
+            keys = np.ascontiguousarray(keys, dtype=np.uint64)
+        out = C.c_void_p(0)
+        self._chk(self.L.dk_matrix_from_host(self.h, S, R, _np_ptr(keys), _np_ptr(cnts), C.byref(out)))
+        return Matrix(self, out)
+
+    # ---- computeNF ------------------------------------------------------------
+    def compute_nf(self, m, mode=NF_REFERENCE, step_rows=0):
+        S = m.samples
+        nf, info = (C.c_double * S)(), (C.c_uint64 * 4)()
+        self._chk(self.L.dk_compute_nf(self.h, m.h, mode, step_rows, nf, info))
+        return np.array(nf[:]), dict(consumed=int(info[0]), steps=int(info[1]), undefined_zone=int(info[2]), n_pos=int(info[3]))
+
+    # ---- TtestFilter ----------------------------------------------------------
+    def ttest_rows(self, m, nf, idxA, idxB):
+        nf = np.ascontiguousarray(nf, dtype=np.float64)
+        a, b = (C.c_int * len(idxA))(*idxA), (C.c_int * len(idxB))(*idxB)
+        out = C.c_void_p(0)
+        self._chk(self.L.dk_ttest_rows(self.h, m.h, nf.ctypes.data_as(C.POINTER(C.c_double)), a, len(idxA), b, len(idxB),
+                                       C.byref(out)))
+        return TtestResult(self, out, m)
+
+    # ---- whole path -----------------------------------------------------------
+    def run_path(self, key_ptrs, cnt_ptrs, n, device_inputs, min_rec, min_abund, nf_mode, idxA, idxB, pmax, fmin,
+                 nf_text_roundtrip=True, keep=False):
+        S, kp, cp, nn = self._tables(key_ptrs, cnt_ptrs, n)
+        a, b = (C.c_int * len(idxA))(*idxA), (C.c_int * len(idxB))(*idxB)
+        st = PathStats()
+        om, ot = C.c_void_p(0), C.c_void_p(0)
+        self._chk(self.L.dk_run_path(self.h, S, kp, cp, nn, int(device_inputs), min_rec, min_abund, nf_mode, a, len(idxA), b,
+                                     len(idxB), float(pmax), float(fmin), int(nf_text_roundtrip), C.byref(st),
+                                     C.byref(om) if keep else None, C.byref(ot) if keep else None))
+        stats = dict(U=int(st.U), R=int(st.R), R_pos=int(st.R_pos), D=int(st.D), ties=tuple(int(x) for x in st.ties),
+                     nf=np.array(st.nf[:S]), ms_join=st.ms_join, ms_nf=st.ms_nf, ms_ttest=st.ms_ttest, ms_bh=st.ms_bh)
+        if keep:
+            m = Matrix(self, om)
+            t = TtestResult(self, ot, m) if ot.value else None
+            if t is not None:
+                t.D, t.ties = stats["D"], stats["ties"]
+            return stats, m, t
+        return stats

@@ -1,0 +1,236 @@
+// dk_api.cu — C-ABI glue: host-buffer entry points, matrix import/export, whole-path driver.
+#include <math.h>
+#include <stdlib.h>
+#include "dk_common.cuh"
+
+void dk_matrix_release(dk_ctx *ctx, dk_matrix *m);
+void dk_ttest_release(dk_ctx *ctx, dk_ttest *t);
+
+extern "C" int dk_join_counts_dev(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int32_t *const *cnts_dev,
+                                  const uint64_t *n, int min_rec, int min_abund, int emit_stale_tail, dk_matrix **out)
+{
+    if (!ctx || !keys_dev || !cnts_dev || !n) return dk_fail(ctx, DK_ERR_ARG, "join_counts: NULL argument");
+    return dk_join_impl(ctx, S, keys_dev, cnts_dev, n, min_rec, min_abund, emit_stale_tail, out);
+}
+
+// upload S host dumps into two device slabs (each sample 256-byte aligned)
+static int upload_dumps(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                        unsigned char **slab, std::vector<const uint64_t *> &kd, std::vector<const int32_t *> &cd)
+{
+    size_t tot = 0;
+    std::vector<size_t> ko(S), co(S);
+    for (int s = 0; s < S; s++) { ko[s] = tot; tot += dk_round_up(n[s] * 8 + 16, 256); }
+    for (int s = 0; s < S; s++) { co[s] = tot; tot += dk_round_up(n[s] * 4 + 16, 256); }
+    *slab = (unsigned char *)dk_dev_alloc(ctx, tot);
+    if (!*slab) return DK_ERR_NOMEM;
+    for (int s = 0; s < S; s++) {
+        kd[s] = (const uint64_t *)(*slab + ko[s]);
+        cd[s] = (const int32_t *)(*slab + co[s]);
+        if (n[s]) {
+            DK_CUDA(ctx, cudaMemcpyAsync(*slab + ko[s], keys[s], n[s] * 8, cudaMemcpyHostToDevice, ctx->stream));
+            DK_CUDA(ctx, cudaMemcpyAsync(*slab + co[s], cnts[s], n[s] * 4, cudaMemcpyHostToDevice, ctx->stream));
+        }
+    }
+    return DK_OK;
+}
+
+extern "C" int dk_join_counts(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts,
+                              const uint64_t *n, int min_rec, int min_abund, int emit_stale_tail, dk_matrix **out)
+{
+    if (!ctx || !keys || !cnts || !n) return dk_fail(ctx, DK_ERR_ARG, "join_counts: NULL argument");
+    if (S < 1 || S > DK_MAX_SAMPLES) return dk_fail(ctx, DK_ERR_ARG, "join: S=%d outside [1,%d]", S, DK_MAX_SAMPLES);
+    unsigned char *slab = nullptr;
+    std::vector<const uint64_t *> kd(S);
+    std::vector<const int32_t *> cd(S);
+    DK_TRY(upload_dumps(ctx, S, keys, cnts, n, &slab, kd, cd));
+    int rc = dk_join_impl(ctx, S, kd.data(), cd.data(), n, min_rec, min_abund, emit_stale_tail, out);
+    cudaStreamSynchronize(ctx->stream);
+    dk_dev_release(ctx, slab);
+    return rc;
+}
+
+// ---- matrix ---------------------------------------------------------------------
+__global__ void k_identity_chunks(uint32_t *order, uint64_t *lbase, uint32_t *chunk_rows, uint32_t n_chunks, uint64_t R)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_chunks) {
+        order[i] = i;
+        lbase[i] = (uint64_t)i * DK_CH;
+        uint64_t left = R - (uint64_t)i * DK_CH;
+        chunk_rows[i] = left < DK_CH ? (uint32_t)left : DK_CH;
+    }
+    if (i == 0) lbase[n_chunks] = R;
+}
+
+extern "C" int dk_matrix_from_host(dk_ctx *ctx, int S, uint64_t R, const uint64_t *keys, const int32_t *cnts, dk_matrix **out)
+{
+    if (!ctx || !out || (R && !cnts)) return dk_fail(ctx, DK_ERR_ARG, "matrix_from_host: NULL argument");
+    if (S < 1 || S > DK_MAX_SAMPLES) return dk_fail(ctx, DK_ERR_ARG, "matrix_from_host: S=%d outside [1,%d]", S, DK_MAX_SAMPLES);
+    cudaStream_t st = ctx->stream;
+    dk_matrix *m = new dk_matrix();
+    m->S = S; m->R = R; m->U = 0;
+    m->n_chunks = (R + DK_CH - 1) / DK_CH;
+    m->cap_chunks = m->n_chunks + 1;
+    m->has_keys = keys != nullptr;
+    m->keys = (uint64_t *)dk_dev_alloc(ctx, 8 * m->cap_chunks * DK_CH);
+    m->cnts = (int32_t *)dk_dev_alloc(ctx, 4 * m->cap_chunks * DK_CH * S);
+    m->chunk_rows = (uint32_t *)dk_dev_alloc(ctx, 4 * m->cap_chunks);
+    m->order = (uint32_t *)dk_dev_alloc(ctx, 4 * (m->n_chunks + 2));
+    m->lbase = (uint64_t *)dk_dev_alloc(ctx, 8 * (m->n_chunks + 3));
+    if (!m->keys || !m->cnts || !m->chunk_rows || !m->order || !m->lbase) { dk_matrix_release(ctx, m); return DK_ERR_NOMEM; }
+    if (R) {
+        if (keys) DK_CUDA(ctx, cudaMemcpyAsync(m->keys, keys, 8 * R, cudaMemcpyHostToDevice, st));
+        DK_CUDA(ctx, cudaMemcpyAsync(m->cnts, cnts, 4 * R * S, cudaMemcpyHostToDevice, st));
+    }
+    unsigned g = (unsigned)((m->n_chunks + 255) / 256);
+    k_identity_chunks<<<g ? g : 1, 256, 0, st>>>(m->order, m->lbase, m->chunk_rows, (uint32_t)m->n_chunks, R); DK_LAUNCHED(ctx);
+    DK_CUDA(ctx, cudaStreamSynchronize(st));
+    *out = m;
+    return DK_OK;
+}
+extern "C" uint64_t dk_matrix_rows(const dk_matrix *m) { return m ? m->R : 0; }
+extern "C" uint64_t dk_matrix_union(const dk_matrix *m) { return m ? m->U : 0; }
+extern "C" int dk_matrix_samples(const dk_matrix *m) { return m ? m->S : 0; }
+extern "C" void dk_matrix_free(dk_ctx *ctx, dk_matrix *m) { if (ctx) dk_matrix_release(ctx, m); }
+
+// one thread per (row, 4-byte word): contiguous row-major destination, chunked source
+__global__ void k_matrix_gather(const uint64_t *keys, const int32_t *cnts, const uint64_t *lbase, const uint32_t *order,
+                                uint32_t n_chunks, int S, uint64_t row0, uint64_t nrows, uint64_t *okeys, int32_t *ocnts)
+{
+    uint64_t r = (uint64_t)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
+    if (r >= nrows) return;
+    uint64_t row = row0 + r;
+    uint32_t lo = 0, hi = n_chunks;
+    while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (lbase[mid] <= row) lo = mid; else hi = mid; }
+    size_t ph = (size_t)order[lo] * DK_CH + (size_t)(row - lbase[lo]);
+    int lane = threadIdx.x & 31;
+    if (ocnts) for (int j = lane; j < S; j += 32) ocnts[r * (size_t)S + j] = cnts[ph * (size_t)S + j];
+    if (okeys && lane == 0) okeys[r] = keys[ph];
+}
+
+extern "C" int dk_matrix_export_dev(dk_ctx *ctx, const dk_matrix *m, uint64_t row0, uint64_t nrows, uint64_t *keys_dev,
+                                    int32_t *cnts_dev)
+{
+    if (!ctx || !m) return dk_fail(ctx, DK_ERR_ARG, "matrix_export: NULL argument");
+    if (row0 + nrows > m->R) return dk_fail(ctx, DK_ERR_ARG, "matrix_export: rows [%llu,+%llu) beyond R=%llu",
+                                            (unsigned long long)row0, (unsigned long long)nrows, (unsigned long long)m->R);
+    if (!nrows) return DK_OK;
+    if (keys_dev && !m->has_keys) return dk_fail(ctx, DK_ERR_ARG, "matrix_export: matrix has no keys");
+    k_matrix_gather<<<(unsigned)((nrows + 7) / 8), 256, 0, ctx->stream>>>(m->keys, m->cnts, m->lbase, m->order, (uint32_t)m->n_chunks,
+                                                                      m->S, row0, nrows, keys_dev, cnts_dev);
+    DK_LAUNCHED(ctx);
+    return DK_OK;
+}
+extern "C" int dk_matrix_export(dk_ctx *ctx, const dk_matrix *m, uint64_t row0, uint64_t nrows, uint64_t *keys, int32_t *cnts)
+{
+    if (!ctx || !m) return dk_fail(ctx, DK_ERR_ARG, "matrix_export: NULL argument");
+    if (!nrows) return DK_OK;
+    uint64_t *dk = keys ? (uint64_t *)dk_dev_alloc(ctx, 8 * nrows) : nullptr;
+    int32_t *dc = cnts ? (int32_t *)dk_dev_alloc(ctx, 4 * nrows * m->S) : nullptr;
+    if ((keys && !dk) || (cnts && !dc)) return DK_ERR_NOMEM;
+    int rc = dk_matrix_export_dev(ctx, m, row0, nrows, dk, dc);
+    if (rc == DK_OK) {
+        if (keys) DK_CUDA(ctx, cudaMemcpyAsync(keys, dk, 8 * nrows, cudaMemcpyDeviceToHost, ctx->stream));
+        if (cnts) DK_CUDA(ctx, cudaMemcpyAsync(cnts, dc, 4 * nrows * m->S, cudaMemcpyDeviceToHost, ctx->stream));
+        DK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    dk_dev_release(ctx, dk); dk_dev_release(ctx, dc);
+    return rc;
+}
+
+__global__ void k_matrix_checksum(const uint64_t *keys, const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
+                                  uint32_t n_chunks, int S, int has_keys, unsigned long long *out)
+{
+    uint32_t oc = blockIdx.x;
+    if (oc >= n_chunks) return;
+    uint32_t rows = (uint32_t)(lbase[oc + 1] - lbase[oc]);
+    size_t p0 = (size_t)order[oc] * DK_CH;
+    unsigned long long x = 0, s = 0;
+    for (uint32_t i = threadIdx.x; i < rows * (uint32_t)S; i += blockDim.x) s += (unsigned long long)(uint32_t)cnts[p0 * S + i];
+    if (has_keys) for (uint32_t i = threadIdx.x; i < rows; i += blockDim.x) x ^= keys[p0 + i];
+    for (int o = 16; o; o >>= 1) { x ^= __shfl_down_sync(0xffffffffu, x, o); s += __shfl_down_sync(0xffffffffu, s, o); }
+    if ((threadIdx.x & 31) == 0) { atomicXor(&out[0], x); atomicAdd(&out[1], s); }
+}
+extern "C" int dk_matrix_checksum(dk_ctx *ctx, const dk_matrix *m, uint64_t *key_xor, uint64_t *cnt_sum)
+{
+    if (!ctx || !m) return dk_fail(ctx, DK_ERR_ARG, "matrix_checksum: NULL argument");
+    unsigned long long *d = (unsigned long long *)dk_dev_alloc(ctx, 64);
+    if (!d) return DK_ERR_NOMEM;
+    DK_CUDA(ctx, cudaMemsetAsync(d, 0, 64, ctx->stream));
+    if (m->n_chunks) {
+        k_matrix_checksum<<<(unsigned)m->n_chunks, 128, 0, ctx->stream>>>(m->keys, m->cnts, m->order, m->lbase, (uint32_t)m->n_chunks,
+                                                                        m->S, m->has_keys ? 1 : 0, d);
+        DK_LAUNCHED(ctx);
+    }
+    unsigned long long h[2];
+    DK_CUDA(ctx, cudaMemcpyAsync(h, d, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    DK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (key_xor) *key_xor = h[0];
+    if (cnt_sum) *cnt_sum = h[1];
+    dk_dev_release(ctx, d);
+    return DK_OK;
+}
+
+// ---- whole path -------------------------------------------------------------------
+// "%f" round trip of the NFs: computeNF prints 6 decimals (computeNF.c:174) and
+// TtestFilter reads them back with atof (TtestFilter.c:261), so the t-test never sees
+// the full-precision factor. Formatting S numbers is pipeline glue, not compute.
+static double nf_text_round(double v)
+{
+    char buf[64];
+    snprintf(buf, sizeof buf, "%f", v);
+    return atof(buf);
+}
+
+extern "C" int dk_run_path(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                           int device_inputs, int min_rec, int min_abund, int nf_mode, const int *idxA, int nA,
+                           const int *idxB, int nB, double pmax, double fmin_, int nf_text_roundtrip, dk_path_stats *stats,
+                           dk_matrix **out_matrix, dk_ttest **out_test)
+{
+    if (!ctx || !keys || !cnts || !n) return dk_fail(ctx, DK_ERR_ARG, "run_path: NULL argument");
+    if (out_matrix) *out_matrix = nullptr;
+    if (out_test) *out_test = nullptr;
+    dk_matrix *m = nullptr;
+    dk_ttest *t = nullptr;
+    int rc = device_inputs ? dk_join_counts_dev(ctx, S, keys, cnts, n, min_rec, min_abund, 0, &m)
+                           : dk_join_counts(ctx, S, keys, cnts, n, min_rec, min_abund, 0, &m);
+    if (rc != DK_OK) return rc;
+    dk_path_stats st;
+    memset(&st, 0, sizeof st);
+    st.U = m->U; st.R = m->R; st.ms_join = ctx->stage_ms[0];
+    uint64_t info[4] = {0, 0, 0, 0};
+    if (m->R == 0) { rc = DK_OK; goto finish; }
+    rc = dk_compute_nf(ctx, m, nf_mode, 0, st.nf, info);
+    if (rc != DK_OK) goto fail;
+    st.R_pos = info[3]; st.ms_nf = ctx->stage_ms[1];
+    {
+        double nf_used[DK_MAX_SAMPLES];
+        for (int s = 0; s < S; s++) nf_used[s] = nf_text_roundtrip ? nf_text_round(st.nf[s]) : st.nf[s];
+        rc = dk_ttest_rows(ctx, m, nf_used, idxA, nA, idxB, nB, &t);
+        if (rc != DK_OK) goto fail;
+        st.ms_ttest = ctx->stage_ms[2];
+        cudaEventRecord(ctx->ev[0], ctx->stream);
+        rc = dk_ttest_adjust(ctx, t, pmax);
+        if (rc != DK_OK) goto fail;
+        rc = dk_ttest_filter(ctx, t, pmax, fmin_, &st.D, st.ties);
+        if (rc != DK_OK) goto fail;
+        cudaEventRecord(ctx->ev[1], ctx->stream);
+        cudaStreamSynchronize(ctx->stream);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
+        st.ms_bh = ms; ctx->stage_ms[3] = ms;
+    }
+finish:
+    if (stats) *stats = st;
+    if (out_test) *out_test = t; else dk_ttest_release(ctx, t);
+    if (out_matrix) *out_matrix = m;
+    else {
+        if (out_test && t) { dk_ttest_release(ctx, t); *out_test = nullptr; }   // a test object needs its matrix
+        dk_matrix_release(ctx, m);
+    }
+    return DK_OK;
+fail:
+    dk_ttest_release(ctx, t);
+    dk_matrix_release(ctx, m);
+    return rc;
+}

@@ -1,0 +1,175 @@
+// dk_bh.cu — Benjamini-Hochberg + final filter (reference: TtestFilter.c:456-497).
+// The reference sorts all R p-values descending and keeps a running minimum of
+// R/(R-i)*p. adj(p) = min(1, min_{q>=p} R/#{p'<=q} * q) depends on the VALUE only, and
+// any q > P has R/#*q >= q > P, so rows with adj <= P are decided exactly by the
+// candidates {p <= P} alone. We therefore sort only the candidates (ascending),
+// compute v at the last element of every tie run, take a suffix minimum, and look
+// each local candidate up. Multi-GPU: candidates are all-gathered by the caller.
+#include <math.h>
+#include "dk_common.cuh"
+
+void dk_ttest_release(dk_ctx *ctx, dk_ttest *t);
+
+__global__ void k_fill_nan(double *p, uint64_t n)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = __longlong_as_double(0x7FF8000000000000ll);
+}
+// count (out==nullptr) or append candidates p <= cut, warp-aggregated
+__global__ void k_bh_candidates(const double *p_raw, uint64_t R, double cut, unsigned long long *counter, double *cp,
+                                uint32_t *crow, uint64_t cap)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool c = (i < R) && (p_raw[i] <= cut);
+    unsigned b = __ballot_sync(0xffffffffu, c);
+    if (!b) return;
+    int lane = threadIdx.x & 31, leader = __ffs(b) - 1;
+    unsigned long long base = 0;
+    if (lane == leader) base = atomicAdd(counter, (unsigned long long)__popc(b));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (c && cp) {
+        uint64_t k = base + __popc(b & ((1u << lane) - 1u));
+        if (k < cap) { cp[k] = p_raw[i]; crow[k] = (uint32_t)i; }
+    }
+}
+__global__ void k_iota_u32(uint32_t *v, uint64_t n)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) v[i] = (uint32_t)i;
+}
+// v[j] at the last element of each tie run (ascending order), +inf elsewhere (TtestFilter.c:467)
+__global__ void k_bh_v(const uint64_t *sk, uint64_t n, double Rg, double *v)
+{
+    uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    bool last = (j + 1 == n) || (sk[j + 1] != sk[j]);
+    double p = __longlong_as_double((long long)sk[j]);
+    v[j] = last ? (Rg / (double)(j + 1)) * p : __longlong_as_double(0x7FF0000000000000ll);
+}
+// suffix minimum in three steps: tile minima, suffix over tiles (one block), apply
+#define SM_T 256
+#define SM_V 8
+__global__ void k_sufmin_tiles(const double *v, uint64_t n, double *tmin)
+{
+    __shared__ double sh[SM_T / 32];
+    uint64_t base = (uint64_t)blockIdx.x * SM_T * SM_V;
+    double m = __longlong_as_double(0x7FF0000000000000ll);
+    for (int i = 0; i < SM_V; i++) {
+        uint64_t k = base + (uint64_t)i * SM_T + threadIdx.x;
+        if (k < n) m = fmin(m, v[k]);
+    }
+    for (int o = 16; o; o >>= 1) m = fmin(m, __shfl_down_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < SM_T / 32; w++) m = fmin(m, sh[w]);
+        tmin[blockIdx.x] = m;
+    }
+}
+__global__ void k_sufmin_scan_tiles(double *tmin, uint64_t nt)   // tmin[t] <- min over tiles > t (exclusive suffix)
+{
+    if (threadIdx.x || blockIdx.x) return;
+    double run = __longlong_as_double(0x7FF0000000000000ll);
+    for (uint64_t t = nt; t-- > 0;) { double x = tmin[t]; tmin[t] = run; run = fmin(run, x); }
+}
+__global__ void k_sufmin_apply(double *v, uint64_t n, const double *tmin)
+{
+    // one thread walks SM_V consecutive items backwards; block-level suffix over thread minima
+    __shared__ double sh[SM_T];
+    uint64_t base = (uint64_t)blockIdx.x * SM_T * SM_V + (uint64_t)threadIdx.x * SM_V;
+    const double INF = __longlong_as_double(0x7FF0000000000000ll);
+    double loc[SM_V], m = INF;
+    for (int i = 0; i < SM_V; i++) { loc[i] = (base + i < n) ? v[base + i] : INF; m = fmin(m, loc[i]); }
+    sh[threadIdx.x] = m;
+    __syncthreads();
+    for (int o = 1; o < SM_T; o <<= 1) {
+        double t = (threadIdx.x + o < SM_T) ? sh[threadIdx.x + o] : INF;
+        __syncthreads();
+        sh[threadIdx.x] = fmin(sh[threadIdx.x], t);
+        __syncthreads();
+    }
+    double run = fmin(tmin[blockIdx.x], (threadIdx.x + 1 < SM_T) ? sh[threadIdx.x + 1] : INF);
+    for (int i = SM_V - 1; i >= 0; i--) {
+        run = fmin(run, loc[i]);
+        if (base + i < n) v[base + i] = run;
+    }
+}
+// adj for each local candidate: find its p in the sorted global candidate list
+__global__ void k_bh_lookup(const double *cp, const uint32_t *crow, uint64_t nc, const uint64_t *sk, const double *F,
+                            uint64_t n_all, double *p_adj)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nc) return;
+    uint64_t key = (uint64_t)__double_as_longlong(cp[i]);
+    uint64_t lo = 0, hi = n_all;
+    while (lo < hi) { uint64_t mid = (lo + hi) >> 1; if (sk[mid] < key) lo = mid + 1; else hi = mid; }
+    double f = (lo < n_all) ? F[lo] : 1.0;
+    p_adj[crow[i]] = f > 1.0 ? 1.0 : f;                              // dmin(1,new) :475
+}
+
+extern "C" int dk_ttest_candidates(dk_ctx *ctx, dk_ttest *t, double p_cut, uint64_t *n_cand, const double **cand_p_dev)
+{
+    if (!ctx || !t) return dk_fail(ctx, DK_ERR_ARG, "ttest_candidates: NULL argument");
+    cudaStream_t st = ctx->stream;
+    unsigned long long *ctr = (unsigned long long *)dk_dev_alloc(ctx, 64);
+    if (!ctr) return DK_ERR_NOMEM;
+    DK_CUDA(ctx, cudaMemsetAsync(ctr, 0, 64, st));
+    unsigned grid = (unsigned)((t->R + 255) / 256);
+    uint64_t nc = 0;
+    if (t->R) {
+        k_bh_candidates<<<grid, 256, 0, st>>>(t->p_raw, t->R, p_cut, ctr, nullptr, nullptr, 0); DK_LAUNCHED(ctx);
+        DK_CUDA(ctx, cudaMemcpyAsync(&nc, ctr, 8, cudaMemcpyDeviceToHost, st));
+        DK_CUDA(ctx, cudaStreamSynchronize(st));
+    }
+    dk_dev_release(ctx, t->cand_p); dk_dev_release(ctx, t->cand_row);
+    t->cand_p = (double *)dk_dev_alloc(ctx, sizeof(double) * (nc + 1));
+    t->cand_row = (uint32_t *)dk_dev_alloc(ctx, sizeof(uint32_t) * (nc + 1));
+    if (!t->cand_p || !t->cand_row) return DK_ERR_NOMEM;
+    if (nc) {
+        DK_CUDA(ctx, cudaMemsetAsync(ctr, 0, 8, st));
+        k_bh_candidates<<<grid, 256, 0, st>>>(t->p_raw, t->R, p_cut, ctr, t->cand_p, t->cand_row, nc); DK_LAUNCHED(ctx);
+    }
+    t->n_cand = nc; t->p_cut = p_cut; t->cand_cap = nc + 1;
+    dk_dev_release(ctx, ctr);
+    if (n_cand) *n_cand = nc;
+    if (cand_p_dev) *cand_p_dev = t->cand_p;
+    return DK_OK;
+}
+
+extern "C" int dk_ttest_adjust_global(dk_ctx *ctx, dk_ttest *t, const double *all_cand_p_dev, uint64_t n_all, uint64_t R_global)
+{
+    if (!ctx || !t) return dk_fail(ctx, DK_ERR_ARG, "ttest_adjust: NULL argument");
+    cudaStream_t st = ctx->stream;
+    dk_dev_release(ctx, t->p_adj);
+    t->p_adj = (double *)dk_dev_alloc(ctx, sizeof(double) * (t->R + 1));
+    if (!t->p_adj) return DK_ERR_NOMEM;
+    if (t->R) { k_fill_nan<<<(unsigned)((t->R + 255) / 256), 256, 0, st>>>(t->p_adj, t->R); DK_LAUNCHED(ctx); }
+    if (n_all == 0 || t->n_cand == 0) return DK_OK;
+    uint64_t *k0 = (uint64_t *)dk_dev_alloc(ctx, 8 * n_all), *k1 = (uint64_t *)dk_dev_alloc(ctx, 8 * n_all);
+    uint32_t *v0 = (uint32_t *)dk_dev_alloc(ctx, 4 * n_all), *v1 = (uint32_t *)dk_dev_alloc(ctx, 4 * n_all);
+    double *F = (double *)dk_dev_alloc(ctx, 8 * n_all);
+    uint64_t nt = (n_all + SM_T * SM_V - 1) / (SM_T * SM_V);
+    double *tmin = (double *)dk_dev_alloc(ctx, 8 * nt);
+    if (!k0 || !k1 || !v0 || !v1 || !F || !tmin) return DK_ERR_NOMEM;
+    DK_CUDA(ctx, cudaMemcpyAsync(k0, all_cand_p_dev, 8 * n_all, cudaMemcpyDeviceToDevice, st));
+    k_iota_u32<<<(unsigned)((n_all + 255) / 256), 256, 0, st>>>(v0, n_all); DK_LAUNCHED(ctx);
+    uint64_t *sk; uint32_t *sv;
+    DK_TRY(dk_sort_pairs_u64(ctx, k0, v0, k1, v1, n_all, &sk, &sv));
+    k_bh_v<<<(unsigned)((n_all + 255) / 256), 256, 0, st>>>(sk, n_all, (double)R_global, F); DK_LAUNCHED(ctx);
+    k_sufmin_tiles<<<(unsigned)nt, SM_T, 0, st>>>(F, n_all, tmin); DK_LAUNCHED(ctx);
+    k_sufmin_scan_tiles<<<1, 32, 0, st>>>(tmin, nt); DK_LAUNCHED(ctx);
+    k_sufmin_apply<<<(unsigned)nt, SM_T, 0, st>>>(F, n_all, tmin); DK_LAUNCHED(ctx);
+    k_bh_lookup<<<(unsigned)((t->n_cand + 255) / 256), 256, 0, st>>>(t->cand_p, t->cand_row, t->n_cand, sk, F, n_all, t->p_adj);
+    DK_LAUNCHED(ctx);
+    dk_dev_release(ctx, k0); dk_dev_release(ctx, k1); dk_dev_release(ctx, v0); dk_dev_release(ctx, v1);
+    dk_dev_release(ctx, F); dk_dev_release(ctx, tmin);
+    return DK_OK;
+}
+
+extern "C" int dk_ttest_adjust(dk_ctx *ctx, dk_ttest *t, double p_cut)
+{
+    uint64_t nc = 0;
+    const double *cp = nullptr;
+    DK_TRY(dk_ttest_candidates(ctx, t, p_cut, &nc, &cp));
+    return dk_ttest_adjust_global(ctx, t, cp, nc, t->R);
+}

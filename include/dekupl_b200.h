@@ -1,0 +1,150 @@
+/*
+ * dekupl_b200.h — C ABI of libdekupl_b200.so: the B200-native count-matrix hot
+ * path of DE-kupl (joinCounts -> computeNF -> TtestFilter).
+ *
+ * The reference (Transipedia/dekupl-run) has no FFI: its boundary is three
+ * single-threaded CLIs over gz/TSV text. Each entry point below cites the
+ * reference interface it replaces; the drop-in CLIs (same names, argv, stdout)
+ * in dekupl-run_b200/host/ are thin main()s over this ABI.
+ *
+ * Conventions: plain C, int return codes (0 = ok, <0 = DK_ERR_*), message via
+ * dk_last_error(); no exceptions; all array arguments are CALLER-OWNED; pointers
+ * are HOST pointers unless the name ends in _dev; library-owned objects
+ * (dk_matrix, dk_ttest) are released with their *_free. A context is bound to
+ * one GPU and one caller thread (the reference tools are single-threaded).
+ * There is NO CPU fallback: without a CUDA device every call fails loudly.
+ *
+ * Packed formats: k-mer key = uint64, 2 bits/base A=0 C=1 G=2 T=3, first base in
+ * the most significant used bits (k <= 31; as share/mergeTags/dna.h:49-59), so
+ * unsigned order == strcmp order of the reference. Count = int32 (reference:
+ * `int` via atoi). Matrix row = key + S counts, row-major.
+ */
+#ifndef DEKUPL_B200_H
+#define DEKUPL_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DK_OK               0
+#define DK_ERR_CUDA        -1   /* CUDA runtime/driver error (message has details) */
+#define DK_ERR_ARG         -2   /* bad argument (S out of range, misaligned pointer, ...) */
+#define DK_ERR_NOMEM       -3
+#define DK_ERR_UNSUPPORTED -4   /* reference behaviour we refuse to imitate (e.g. group of 1 => Boost abort) */
+#define DK_ERR_NODEVICE    -5
+
+#define DK_MAX_SAMPLES 256
+
+#define DK_NF_REFERENCE 0  /* computeNF.c:138-168 prefix / early-stop semantics */
+#define DK_NF_FULL      1  /* median of ratios over ALL rows (README semantics) */
+
+typedef struct dk_ctx dk_ctx;
+typedef struct dk_matrix dk_matrix;   /* device-resident filtered count matrix */
+typedef struct dk_ttest dk_ttest;     /* device-resident per-row test results  */
+
+/* ---- context ---------------------------------------------------------------*/
+int  dk_init(dk_ctx **out, int device);           /* device = CUDA ordinal */
+void dk_free(dk_ctx *ctx);
+const char *dk_last_error(const dk_ctx *ctx);     /* never freed by the caller; ctx may be NULL */
+const char *dk_version(void);
+/* work is enqueued on this CUDA stream (a cudaStream_t passed as void*); default: a stream the ctx owns */
+int  dk_set_stream(dk_ctx *ctx, void *cuda_stream);
+int  dk_sync(dk_ctx *ctx);
+/* number of kernels this context has launched so far (bench.py's gpu_launches) */
+uint64_t dk_launch_count(const dk_ctx *ctx);
+/* device time (ms, CUDA events on the ctx stream) of the last call of each stage:
+ * which = 0 join, 1 nf, 2 ttest rows, 3 BH+filter, 4 merge kernel alone */
+double dk_stage_ms(const dk_ctx *ctx, int which);
+
+/* ---- joinCounts (replaces share/joinCounts/joinCounts.c:72-115 main loop) ----
+ * keys[s]/cnts[s]: n[s] records of sample s, keys ascending. Row kept iff
+ * #{s : present && cnt >= min_abund} >= min_rec (joinCounts.c:81-83,104).
+ * emit_stale_tail != 0 reproduces the extra all-zero row printed when
+ * min_rec <= 0 (joinCounts.c:104-114). Device pointers must be 16-byte aligned. */
+int dk_join_counts(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts,
+                   const uint64_t *n, int min_rec, int min_abund, int emit_stale_tail,
+                   dk_matrix **out);
+int dk_join_counts_dev(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int32_t *const *cnts_dev,
+                       const uint64_t *n, int min_rec, int min_abund, int emit_stale_tail,
+                       dk_matrix **out);
+
+/* ---- matrix ----------------------------------------------------------------*/
+/* wrap an existing row-major matrix (what computeNF / TtestFilter read from raw-counts.tsv) */
+int dk_matrix_from_host(dk_ctx *ctx, int S, uint64_t R, const uint64_t *keys /* may be NULL */,
+                        const int32_t *cnts, dk_matrix **out);
+uint64_t dk_matrix_rows(const dk_matrix *m);      /* R: rows that passed the filter */
+uint64_t dk_matrix_union(const dk_matrix *m);     /* U: union k-mers merged (0 for from_host) */
+int      dk_matrix_samples(const dk_matrix *m);
+/* gather rows [row0,row0+nrows) in reference order into caller buffers (either may be NULL) */
+int dk_matrix_export(dk_ctx *ctx, const dk_matrix *m, uint64_t row0, uint64_t nrows,
+                     uint64_t *keys, int32_t *cnts);
+int dk_matrix_export_dev(dk_ctx *ctx, const dk_matrix *m, uint64_t row0, uint64_t nrows,
+                         uint64_t *keys_dev, int32_t *cnts_dev);
+/* order-independent checksums over all rows: xor of keys, sum of all counts (mod 2^64) */
+int dk_matrix_checksum(dk_ctx *ctx, const dk_matrix *m, uint64_t *key_xor, uint64_t *cnt_sum);
+void dk_matrix_free(dk_ctx *ctx, dk_matrix *m);
+
+/* ---- computeNF (replaces share/computeNF/computeNF.c:109-168) ---------------
+ * mode DK_NF_REFERENCE: step_rows = rows per step (0 => the reference's 1,000,000).
+ * info (may be NULL): info[0] = rows consumed, info[1] = steps evaluated,
+ * info[2] = 1 if R fell in the reference's undefined zone step<=R<2*step (we
+ * return the step-1 factors there), info[3] = all-positive rows used. */
+int dk_compute_nf(dk_ctx *ctx, const dk_matrix *m, int mode, uint64_t step_rows,
+                  double *nf_out, uint64_t *info);
+/* multi-GPU DK_NF_FULL building blocks: exact global median of the per-sample ratios by
+ * MSB-first radix select on the order-preserving uint64 image of the fp64 ratio, 8 rounds
+ * of 8 bits. Per round the caller all-reduces (sum) S*256 uint64 bins over the ranks:
+ *   dk_nf_begin -> all-reduce n_pos -> dk_nf_set_rank(total/2)
+ *   8x { dk_nf_hist_dev(hist) -> all-reduce(hist) -> dk_nf_advance_dev(hist) }
+ *   dk_nf_result -> dk_nf_end                                                     */
+typedef struct dk_nf_state dk_nf_state;
+int dk_nf_begin(dk_ctx *ctx, const dk_matrix *m, dk_nf_state **out, uint64_t *n_pos /* all-positive rows of this shard */);
+int dk_nf_set_rank(dk_ctx *ctx, dk_nf_state *st, uint64_t k /* 0-based rank, reference: size/2 */);
+int dk_nf_hist_dev(dk_ctx *ctx, dk_nf_state *st, uint64_t *hist_dev /* [S*256] device, overwritten */);
+int dk_nf_advance_dev(dk_ctx *ctx, dk_nf_state *st, uint64_t *hist_dev /* reduced bins; zeroed on return */);
+int dk_nf_result(dk_ctx *ctx, dk_nf_state *st, double *nf_out /* exp(median ratio), S values */);
+void dk_nf_end(dk_ctx *ctx, dk_nf_state *st);
+
+/* ---- TtestFilter (replaces share/TtestFilter/TtestFilter.c:373-497, t-test mode) --
+ * idxA/idxB: column indices of the two groups in conditions-file order
+ * (TtestFilter.c:251-284); nf[S]: normalisation factors as TtestFilter sees them
+ * (i.e. after the %f round trip). Groups of size < 2 => DK_ERR_UNSUPPORTED (the
+ * reference aborts inside Boost). */
+int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf,
+                  const int *idxA, int nA, const int *idxB, int nB, dk_ttest **out);
+/* BH over candidates p <= p_cut (exact for every row whose adjusted p <= p_cut; p_cut >= 1 => all rows).
+ * Single GPU: dk_ttest_adjust(ctx,t,p_cut). Multi GPU: _candidates -> caller all-gathers
+ * the candidate p-values and all-reduces R -> _adjust_global. */
+int dk_ttest_candidates(dk_ctx *ctx, dk_ttest *t, double p_cut, uint64_t *n_cand, const double **cand_p_dev);
+int dk_ttest_adjust_global(dk_ctx *ctx, dk_ttest *t, const double *all_cand_p_dev, uint64_t n_all, uint64_t R_global);
+int dk_ttest_adjust(dk_ctx *ctx, dk_ttest *t, double p_cut);
+/* TtestFilter.c:486: survivors = adj_p <= pmax && fabs(log2FC) >= fmin; returns D in *n_keep.
+ * ties (may be NULL): ties[0] = rows with adj_p within 1e-9 rel of pmax, ties[1] = rows with
+ * fabs(log2FC) within 1e-9 rel of fmin, ties[2] = rows whose sd was within 1e-13 of the sd==0 test */
+int dk_ttest_filter(dk_ctx *ctx, dk_ttest *t, double pmax, double fmin, uint64_t *n_keep, uint64_t *ties);
+/* survivors in reference order; any output may be NULL. norm_cnts = S doubles per row (count/NF, TtestFilter.c:382) */
+int dk_ttest_export_survivors(dk_ctx *ctx, const dk_ttest *t, uint64_t *row_idx, uint64_t *keys, double *p_adj,
+                              double *meanA, double *meanB, double *log2fc, double *norm_cnts);
+/* per-row vectors (R entries, reference order); p_adj is NaN where not computed (p_raw > p_cut) */
+int dk_ttest_export_rows(dk_ctx *ctx, const dk_ttest *t, double *p_raw, double *log2fc, double *p_adj);
+uint64_t dk_ttest_rows_count(const dk_ttest *t);
+void dk_ttest_free(dk_ctx *ctx, dk_ttest *t);
+
+/* ---- whole path, host buffers in, survivors out (what bench.py's e2e times) ---- */
+typedef struct {
+    uint64_t U, R, R_pos, D;          /* union rows, filtered rows, all-positive rows used by NF, survivors */
+    uint64_t ties[3];
+    double   nf[DK_MAX_SAMPLES];
+    double   ms_join, ms_nf, ms_ttest, ms_bh;
+} dk_path_stats;
+int dk_run_path(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                int device_inputs, int min_rec, int min_abund, int nf_mode,
+                const int *idxA, int nA, const int *idxB, int nB, double pmax, double fmin,
+                int nf_text_roundtrip /* round NFs through "%f" like the pipeline does */,
+                dk_path_stats *stats, dk_matrix **out_matrix /* may be NULL */, dk_ttest **out_test /* may be NULL */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,122 @@
+/* CPU ORACLE — test infrastructure only (see dekupl_oracle.h). */
+#include "dekupl_oracle.h"
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+/* ---- joinCounts (reference: share/joinCounts/joinCounts.c:72-115) ----------
+ * The reference keeps one cursor per file and, per output row, scans all
+ * cursors twice: once to collect counts of cursors equal to the current minimum
+ * (advancing them) and once to find the next minimum. Packed keys compare like
+ * strcmp on equal-length ACGT strings (A<C<G<T == 0<1<2<3, MSB first). */
+size_t orc_join(int S, const uint64_t *const *keys, const int32_t *const *cnts,
+                const size_t *n, int min_rec, int min_abund, int emit_stale_tail,
+                uint64_t *out_keys, int32_t *out_cnts, size_t cap, size_t *n_union)
+{
+    size_t *pos = (size_t *)calloc((size_t)S, sizeof(size_t));
+    int32_t *row = (int32_t *)calloc((size_t)S, sizeof(int32_t));
+    size_t R = 0, U = 0;
+    uint64_t last = 0;
+    for (;;) {
+        int any = 0;
+        uint64_t mn = 0;
+        for (int s = 0; s < S; s++)
+            if (pos[s] < n[s] && (!any || keys[s][pos[s]] < mn)) { mn = keys[s][pos[s]]; any = 1; }
+        if (!any) break;
+        int rec = 0;
+        for (int s = 0; s < S; s++) {
+            if (pos[s] < n[s] && keys[s][pos[s]] == mn) {      /* joinCounts.c:78-83 */
+                row[s] = cnts[s][pos[s]];
+                if (row[s] >= min_abund) rec++;
+                pos[s]++;
+            } else row[s] = 0;                                   /* joinCounts.c:96 */
+        }
+        U++; last = mn;
+        if (rec >= min_rec) {                                    /* joinCounts.c:104 */
+            if (R < cap) { out_keys[R] = mn; memcpy(out_cnts + R * S, row, sizeof(int32_t) * S); }
+            R++;
+        }
+    }
+    /* joinCounts.c:104-114: one more iteration runs on the stale min_kmer with
+     * all counts 0 and rec 0; it prints iff 0 >= min_rec. */
+    if (emit_stale_tail && U > 0 && 0 >= min_rec) {
+        if (R < cap) { out_keys[R] = last; memset(out_cnts + R * S, 0, sizeof(int32_t) * S); }
+        R++;
+    }
+    if (n_union) *n_union = U;
+    free(pos); free(row);
+    return R;
+}
+
+/* ---- computeNF (reference: share/computeNF/computeNF.c) -------------------- */
+typedef struct { double *a; size_t n, m; } dvec;
+static void dpush(dvec *v, double x) {
+    if (v->n == v->m) { v->m = v->m ? v->m * 2 : 1024; v->a = (double *)realloc(v->a, v->m * sizeof(double)); }
+    v->a[v->n++] = x;
+}
+static int cmp_double(const void *a, const void *b) {            /* computeNF.c:27-36 */
+    double x = *(const double *)a, y = *(const double *)b;
+    return x < y ? -1 : (x > y ? 1 : 0);
+}
+static void compute_nf(dvec *v, int S, double *nf) {             /* computeNF.c:38-47 */
+    for (int j = 0; j < S; j++) {
+        qsort(v[j].a, v[j].n, sizeof(double), cmp_double);
+        nf[j] = v[j].n ? exp(v[j].a[v[j].n / 2]) : NAN;          /* reference: UB on empty */
+    }
+}
+/* computeNF.c:18-25 + 122-130: returns 1 and pushes when the row is all-positive */
+static void push_row(const int32_t *c, int S, dvec *v) {
+    double sum = 0;
+    for (int j = 0; j < S; j++) sum += log((double)c[j]);        /* log(int) promotes to double */
+    double m = sum / S;
+    for (int j = 0; j < S; j++)
+        if (c[j] > 0 && isfinite(m)) dpush(&v[j], log((double)c[j]) - m);
+}
+
+size_t orc_nf_reference(const int32_t *cnts, size_t R, int S, size_t step,
+                        double *nf_out, int *undefined_zone)
+{
+    dvec *v = (dvec *)calloc((size_t)S, sizeof(dvec));
+    double *nf = (double *)calloc((size_t)S, sizeof(double));
+    double *nw = (double *)calloc((size_t)S, sizeof(double));
+    double min_error = 0.001 * S;                                 /* computeNF.c:53,97 */
+    size_t nb_step = 0, line = 0;
+    int have_nf = 0;
+    if (undefined_zone) *undefined_zone = 0;
+    for (size_t i = 0; i < R; i++) {
+        line++;
+        push_row(cnts + i * S, S, v);
+        if (line % step == 0) {                                   /* computeNF.c:138 */
+            compute_nf(v, S, nw);
+            if (nb_step > 0) {
+                double sum = 0;
+                /* at nb_step==1 the reference compares against uninitialised
+                 * memory (computeNF.c:95,145); we model "never converges there". */
+                for (int j = 0; j < S; j++) sum += fabs(nf[j] - nw[j]);
+                int stop = (nb_step >= 2) && (sum < min_error);
+                memcpy(nf, nw, sizeof(double) * S); have_nf = 1;
+                if (stop) break;
+            } else {
+                /* step 0 result is discarded by the reference (leaked); we keep it
+                 * only to give the 1*step <= R < 2*step zone a defined answer. */
+                memcpy(nf, nw, sizeof(double) * S);
+            }
+            nb_step++;
+        }
+    }
+    if (nb_step == 0) compute_nf(v, S, nf);                       /* computeNF.c:166-168 */
+    else if (!have_nf && undefined_zone) *undefined_zone = 1;
+    memcpy(nf_out, nf, sizeof(double) * S);
+    for (int j = 0; j < S; j++) free(v[j].a);
+    free(v); free(nf); free(nw);
+    return line;
+}
+
+void orc_nf_full(const int32_t *cnts, size_t R, int S, double *nf_out)
+{
+    dvec *v = (dvec *)calloc((size_t)S, sizeof(dvec));
+    for (size_t i = 0; i < R; i++) push_row(cnts + i * S, S, v);
+    compute_nf(v, S, nf_out);
+    for (int j = 0; j < S; j++) free(v[j].a);
+    free(v);
+}

@@ -1,0 +1,48 @@
+"""helpers shared by the CPU and GPU tests"""
+import json
+import os
+
+import numpy as np
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+BASES = "ACGT"
+CODE = {c: i for i, c in enumerate(BASES)}
+
+
+def load_json(name):
+    return json.load(open(os.path.join(GOLD, name)))
+
+
+def enc(s):
+    v = 0
+    for ch in s:
+        v = (v << 2) | CODE[ch]
+    return v
+
+
+def dec(v, k):
+    v = int(v)
+    return "".join(BASES[(v >> (2 * (k - 1 - i))) & 3] for i in range(k))
+
+
+def parse_dump_text(txt):
+    t = txt.split()
+    kmers, cnts = t[0::2], t[1::2]
+    k = len(kmers[0]) if kmers else 0
+    return np.array([enc(s) for s in kmers], dtype=np.uint64), np.array([int(c) for c in cnts], dtype=np.int32), k
+
+
+def format_join(keys, cnts, k):
+    return "".join(dec(key, k) + "".join("\t%d" % c for c in row) + "\n" for key, row in zip(keys, cnts))
+
+
+def random_dumps(rng, S, n_union, kbits, p_present, max_count, p_core=0.0):
+    """sorted distinct keys per sample; a p_core fraction of rows is present in ~all samples"""
+    keys = np.unique(rng.integers(0, 1 << kbits, size=n_union, dtype=np.uint64))
+    core = rng.random(len(keys)) < p_core
+    out_k, out_c = [], []
+    for _ in range(S):
+        m = np.where(core, rng.random(len(keys)) < 0.95, rng.random(len(keys)) < p_present)
+        out_k.append(keys[m])
+        out_c.append(rng.integers(1, max_count, size=int(m.sum())).astype(np.int32))
+    return out_k, out_c

@@ -1,0 +1,94 @@
+"""ctypes wrapper of the CPU oracle (oracle/_ref/liboracle.so). TEST-ONLY: the product never imports this."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SO = os.path.join(ROOT, "oracle", "_ref", "liboracle.so")
+_L = None
+
+
+def load():
+    global _L
+    if _L is not None:
+        return _L
+    if not os.path.exists(SO):
+        subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "_ref/liboracle.so"], check=True, capture_output=True)
+    L = C.CDLL(SO)
+    vp, u64, i32, dbl, sz = C.c_void_p, C.c_uint64, C.c_int, C.c_double, C.c_size_t
+    L.orc_join.restype = sz
+    L.orc_join.argtypes = [i32, C.POINTER(vp), C.POINTER(vp), C.POINTER(sz), i32, i32, i32, vp, vp, sz, C.POINTER(sz)]
+    L.orc_nf_reference.restype = sz
+    L.orc_nf_reference.argtypes = [vp, sz, i32, sz, vp, C.POINTER(i32)]
+    L.orc_nf_full.restype = None
+    L.orc_nf_full.argtypes = [vp, sz, i32, vp]
+    L.orc_student_t_2tail.restype = dbl
+    L.orc_student_t_2tail.argtypes = [dbl, dbl]
+    L.orc_ttest_rows.restype = None
+    L.orc_ttest_rows.argtypes = [vp, sz, i32, vp, vp, i32, vp, i32, vp, vp, vp, vp]
+    L.orc_bh.restype = None
+    L.orc_bh.argtypes = [vp, sz, vp]
+    L.orc_filter.restype = sz
+    L.orc_filter.argtypes = [vp, vp, sz, dbl, dbl, vp]
+    _L = L
+    return L
+
+
+def join(keys, cnts, min_rec=1, min_abund=1, stale_tail=False):
+    L = load()
+    S = len(keys)
+    keys = [np.ascontiguousarray(k, dtype=np.uint64) for k in keys]
+    cnts = [np.ascontiguousarray(c, dtype=np.int32) for c in cnts]
+    cap = sum(len(k) for k in keys) + 1
+    ok, oc = np.empty(cap, np.uint64), np.empty((cap, S), np.int32)
+    kp = (C.c_void_p * S)(*[k.ctypes.data for k in keys])
+    cp = (C.c_void_p * S)(*[c.ctypes.data for c in cnts])
+    nn = (C.c_size_t * S)(*[len(k) for k in keys])
+    U = C.c_size_t(0)
+    R = L.orc_join(S, kp, cp, nn, min_rec, min_abund, int(stale_tail), ok.ctypes.data, oc.ctypes.data, cap, C.byref(U))
+    return ok[:R].copy(), oc[:R].copy(), int(U.value)
+
+
+def nf_reference(cnts, step=1000000):
+    L = load()
+    cnts = np.ascontiguousarray(cnts, dtype=np.int32)
+    R, S = cnts.shape
+    nf = np.empty(S)
+    uz = C.c_int(0)
+    used = L.orc_nf_reference(cnts.ctypes.data, R, S, step, nf.ctypes.data, C.byref(uz))
+    return nf, int(used), int(uz.value)
+
+
+def nf_full(cnts):
+    L = load()
+    cnts = np.ascontiguousarray(cnts, dtype=np.int32)
+    R, S = cnts.shape
+    nf = np.empty(S)
+    L.orc_nf_full(cnts.ctypes.data, R, S, nf.ctypes.data)
+    return nf
+
+
+def ttest_rows(cnts, nf, idxA, idxB):
+    L = load()
+    cnts = np.ascontiguousarray(cnts, dtype=np.int32)
+    R, S = cnts.shape
+    nf = np.ascontiguousarray(nf, dtype=np.float64)
+    a, b = np.array(idxA, dtype=np.int32), np.array(idxB, dtype=np.int32)
+    p, mA, mB, fc = np.empty(R), np.empty(R), np.empty(R), np.empty(R)
+    L.orc_ttest_rows(cnts.ctypes.data, R, S, nf.ctypes.data, a.ctypes.data, len(a), b.ctypes.data, len(b),
+                     p.ctypes.data, mA.ctypes.data, mB.ctypes.data, fc.ctypes.data)
+    return p, mA, mB, fc
+
+
+def bh(p):
+    L = load()
+    p = np.ascontiguousarray(p, dtype=np.float64)
+    out = np.empty_like(p)
+    L.orc_bh(p.ctypes.data, len(p), out.ctypes.data)
+    return out
+
+
+def student_t_2tail(t, df):
+    return load().orc_student_t_2tail(float(t), float(df))

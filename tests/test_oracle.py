@@ -1,0 +1,135 @@
+"""CPU tests: pin the oracle (oracle/*.c) against golden vectors captured from the REAL reference
+binaries (tests/golden/make_golden.py) and against scipy for the Student-t tail."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as orc
+from common import GOLD, parse_dump_text, format_join, load_json
+
+
+def test_join_matches_reference_binary_goldens():
+    for case in load_json("join_cases.json"):
+        r, a = 1, 1
+        args = case["args"]
+        for i in range(0, len(args), 2):
+            if args[i] == "-r":
+                r = int(args[i + 1])
+            if args[i] == "-a":
+                a = int(args[i + 1])
+        dumps = [parse_dump_text(t) for t in case["inputs"]]
+        k = dumps[0][2]
+        keys, cnts, U = orc.join([d[0] for d in dumps], [d[1] for d in dumps], r, a, stale_tail=True)
+        assert format_join(keys, cnts, k) == case["stdout"], f"args={args}"
+
+
+def test_join_stale_tail_only_when_r_nonpositive():
+    k = [np.array([1, 5, 9], np.uint64), np.array([5, 7], np.uint64)]
+    c = [np.array([3, 4, 5], np.int32), np.array([6, 7], np.int32)]
+    keys, cnts, U = orc.join(k, c, 0, 1, stale_tail=True)
+    assert U == 4 and len(keys) == 5 and keys[-1] == 9 and (cnts[-1] == 0).all()
+    keys, cnts, U = orc.join(k, c, 1, 1, stale_tail=True)
+    assert len(keys) == 4
+
+
+def test_join_duplicate_keys_emit_two_rows_like_reference():
+    # duplicate k-mer inside one file: the reference prints it twice (SURVEY §8a J-edge)
+    keys, cnts, U = orc.join([np.array([4, 4, 8], np.uint64), np.array([4], np.uint64)],
+                             [np.array([1, 2, 3], np.int32), np.array([9], np.int32)])
+    assert keys.tolist() == [4, 4, 8] and cnts.tolist() == [[1, 9], [2, 0], [3, 0]]
+
+
+def _nf_text(names, nf):
+    return "sample\tnormalization_factor\n" + "".join("%s\t%f\n" % (n, v) for n, v in zip(names, nf))
+
+
+def test_nf_reference_fixture_goldens():
+    g = load_json("nf_cases.json")
+    z = np.load(os.path.join(GOLD, "nf_fixture.npz"))
+    nf, used, uz = orc.nf_reference(z["counts"])
+    assert _nf_text(z["names"], nf) == g["computeNF_fixture"]
+    assert used == len(z["counts"]) and uz == 0
+    for nm in ("bigger", "small"):
+        m = g[f"ttest_{nm}_matrix"]
+        nf, _, _ = orc.nf_reference(np.array(m["counts"], np.int32))
+        assert _nf_text(m["names"], nf) == g[f"ttest_{nm}_fixture"]
+
+
+@pytest.mark.parametrize("idx", [0, 1, 2, 3])
+def test_nf_reference_step_logic_matches_binary(idx):
+    from golden.make_golden import synth_matrix
+    case = load_json("nf_cases.json")["nf_step_cases"][idx]
+    cnts = synth_matrix(case["seed"], case["R"], case["S"])
+    nf, used, uz = orc.nf_reference(cnts)
+    if uz:
+        pytest.skip("reference prints uninitialised memory here")
+    assert _nf_text([f"s{j}" for j in range(case["S"])], nf) == case["stdout"]
+
+
+def test_nf_small_step_equals_full_prefix():
+    rng = np.random.default_rng(3)
+    cnts = rng.poisson(20, size=(5000, 4)).astype(np.int32)
+    nf_all, used, _ = orc.nf_reference(cnts, step=10 ** 6)
+    assert used == 5000
+    np.testing.assert_allclose(nf_all, orc.nf_full(cnts), rtol=0, atol=0)
+    # with a tiny step the early stop consumes a prefix only
+    nf_s, used_s, _ = orc.nf_reference(cnts, step=1000)
+    assert used_s % 1000 == 0 and used_s <= 5000
+    np.testing.assert_allclose(nf_s, orc.nf_full(cnts[:used_s]), rtol=0, atol=0)
+
+
+def test_student_t_tail_vs_scipy():
+    g = load_json("ttest_scipy.json")["student_t_2tail"]
+    for t, df, want in g:
+        got = orc.student_t_2tail(t, df)
+        if want < 1e-290:
+            assert got < 1e-280
+        else:
+            assert abs(got - want) <= 1e-11 * want + 1e-300, (t, df, got, want)
+
+
+# SURVEY §4 table (scipy-derived pins for the reference's TtestFilter fixtures, -p 0.2)
+SURVEY_ROWS = {
+    "bigger": {(16, 16, 16, 18, 18, 18): (0.3767727982505043, 0.3767727982505043, 19.501368, 15.843223, -0.299709),
+               (0, 0, 0, 16, 16, 16): (0.00073631188614349617, 0.069949629183632137, 1.000000, 14.193976, 3.827207),
+               (16, 16, 16, 2, 2, 2): (0.00392433950660651, 0.18640612656380923, 19.501368, 2.649247, -2.879921)},
+    "small": {(6, 6, 6, 8, 8, 8): (0.88865603566518181, 0.88865603566518181, 7.938013, 7.596988, -0.063350),
+              (0, 0, 0, 6, 6, 6): (0.0012933699965006257, 0.12287014966755944, 1.000000, 5.947741, 2.572342),
+              (6, 6, 6, 2, 2, 2): (0.012419775562328221, 0.5899393392105905, 7.938013, 2.649247, -1.583196)},
+}
+
+
+@pytest.mark.parametrize("nm", ["bigger", "small"])
+def test_ttest_fixture_rows_match_survey_table(nm):
+    g = load_json("nf_cases.json")
+    m = g[f"ttest_{nm}_matrix"]
+    cnts = np.array(m["counts"], np.int32)
+    nf = np.array([float(l.split()[2]) for l in g["ttest_conditions"].strip().split("\n")[1:]])
+    p, mA, mB, fc = orc.ttest_rows(cnts, nf, [0, 1, 2], [3, 4, 5])
+    adj = orc.bh(p)
+    seen = set()
+    for i, row in enumerate(cnts):
+        want = SURVEY_ROWS[nm][tuple(row.tolist())]
+        seen.add(tuple(row.tolist()))
+        assert abs(p[i] - want[0]) <= 1e-11 * want[0]
+        assert abs(adj[i] - want[1]) <= 1e-11 * want[1]
+        assert "%f" % mA[i] == "%f" % want[2] and "%f" % mB[i] == "%f" % want[3] and "%f" % fc[i] == "%f" % want[4]
+    assert len(seen) == 3
+
+
+def test_bh_definition_and_ties():
+    rng = np.random.default_rng(11)
+    p = np.round(rng.random(500), 2)          # many ties
+    adj = orc.bh(p)
+    n = len(p)
+    order = np.argsort(-p, kind="stable")
+    want = np.empty(n)
+    mn = 1.0
+    for i, j in enumerate(order):
+        mn = min(mn, n / (n - i) * p[j])
+        want[j] = min(1.0, mn)
+    np.testing.assert_allclose(adj, want, rtol=1e-15)
+    for v in np.unique(p):
+        assert len(set(adj[p == v].tolist())) == 1
