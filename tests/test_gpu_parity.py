@@ -1,0 +1,262 @@
+"""GPU parity tests (run on the B200 box): the CUDA path, called through the C ABI, against the CPU
+oracle on the same seeded inputs and against the committed golden vectors. Integer work is bit-exact;
+fp64 results are within 1e-9 relative (BASELINE.json north_star)."""
+import os
+
+import numpy as np
+import pytest
+
+import dekupl_run_b200 as dk
+import oracle_lib as orc
+from common import GOLD, format_join, load_json, parse_dump_text, random_dumps
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-9   # north_star: NF, p, adjusted p within 1e-9 relative in fp64
+
+
+def _join_both(ctx, keys, cnts, r, a, stale=False):
+    m = ctx.join_counts(keys, cnts, r, a, emit_stale_tail=stale)
+    gk, gc = m.export()
+    U, R = m.union, m.rows
+    m.free()
+    ok, oc, oU = orc.join(keys, cnts, r, a, stale_tail=stale)
+    assert U == oU and R == len(ok)
+    np.testing.assert_array_equal(gk, ok)
+    np.testing.assert_array_equal(gc, oc)
+    return gk, gc
+
+
+# ---------------------------------------------------------------- joinCounts ---
+def test_join_reference_binary_goldens(ctx):
+    for case in load_json("join_cases.json"):
+        r, a = 1, 1
+        args = case["args"]
+        for i in range(0, len(args), 2):
+            r = int(args[i + 1]) if args[i] == "-r" else r
+            a = int(args[i + 1]) if args[i] == "-a" else a
+        dumps = [parse_dump_text(t) for t in case["inputs"]]
+        m = ctx.join_counts([d[0] for d in dumps], [d[1] for d in dumps], r, a, emit_stale_tail=True)
+        keys, cnts = m.export()
+        m.free()
+        assert format_join(keys, cnts, dumps[0][2]) == case["stdout"], f"args={args}"
+
+
+@pytest.mark.parametrize("S,n_union,pp,core,r,a", [
+    (2, 1000, 0.5, 0.0, 1, 1), (4, 20000, 0.4, 0.2, 2, 5), (16, 200000, 0.075, 0.2, 3, 5),
+    (17, 30000, 0.3, 0.1, 2, 3), (32, 50000, 0.2, 0.2, 3, 2), (33, 40000, 0.2, 0.2, 4, 2),
+    (48, 60000, 0.1, 0.2, 4, 5), (64, 30000, 0.1, 0.1, 5, 3), (100, 20000, 0.1, 0.2, 8, 4),
+    (200, 12000, 0.08, 0.2, 12, 5), (256, 6000, 0.1, 0.1, 10, 3), (1, 5000, 1.0, 0.0, 1, 3),
+])
+def test_join_random_vs_oracle(ctx, S, n_union, pp, core, r, a):
+    rng = np.random.default_rng(S * 1000 + n_union)
+    keys, cnts = random_dumps(rng, S, n_union, 62, pp, 12, p_core=core)
+    _join_both(ctx, keys, cnts, r, a)
+
+
+def test_join_edge_cases(ctx):
+    rng = np.random.default_rng(5)
+    keys, cnts = random_dumps(rng, 6, 3000, 62, 0.5, 9)
+    # empty samples (the reference segfaults on an empty file; packed API defines them as absent)
+    keys[2], cnts[2] = keys[2][:0], cnts[2][:0]
+    keys[5], cnts[5] = keys[5][:0], cnts[5][:0]
+    _join_both(ctx, keys, cnts, 2, 3)
+    # all samples empty
+    m = ctx.join_counts([k[:0] for k in keys], [c[:0] for c in cnts], 1, 1)
+    assert m.rows == 0 and m.union == 0
+    m.free()
+    # single record
+    _join_both(ctx, [np.array([7], np.uint64), np.array([], np.uint64)], [np.array([3], np.int32), np.array([], np.int32)], 1, 1)
+    # r <= 0 reproduces the stale trailing row; a <= 0 never counts absent samples
+    _join_both(ctx, keys, cnts, 0, 1, stale=True)
+    _join_both(ctx, keys, cnts, 1, 0)
+    _join_both(ctx, keys, cnts, 7, 1)          # nothing can pass
+    # duplicates inside one dump are emitted as separate rows (reference behaviour)
+    _join_both(ctx, [np.array([4, 4, 8, 8, 8], np.uint64), np.array([4, 8], np.uint64)],
+               [np.array([1, 2, 3, 4, 5], np.int32), np.array([9, 7], np.int32)], 1, 1)
+    # identical dumps, maximal 31-mer keys, clustered keys (one hot bucket)
+    k = np.sort(rng.choice(1 << 20, 5000, replace=False).astype(np.uint64)) + np.uint64((1 << 62) - (1 << 20))
+    _join_both(ctx, [k, k, k], [np.full(5000, 5, np.int32)] * 3, 3, 5)
+    hot = np.unique(np.concatenate([rng.integers(0, 1 << 62, 100, dtype=np.uint64),
+                                    np.uint64(123456789) + rng.integers(0, 40000, 30000).astype(np.uint64)]))
+    _join_both(ctx, [hot[::2], hot[::3], hot], [np.ones(len(hot[::2]), np.int32) * 6, np.ones(len(hot[::3]), np.int32),
+                                                np.ones(len(hot), np.int32) * 9], 2, 5)
+    # large counts up to INT_MAX
+    _join_both(ctx, [np.array([1, 2], np.uint64)] * 2, [np.array([2 ** 31 - 1, 5], np.int32), np.array([7, 2 ** 31 - 1], np.int32)], 2, 6)
+
+
+def test_join_large_checksum_properties(ctx):
+    """size-independent properties at a size the oracle would take minutes for"""
+    rng = np.random.default_rng(99)
+    keys, cnts = random_dumps(rng, 16, 3_000_000, 62, 0.075, 40, p_core=0.2)
+    m_all = ctx.join_counts(keys, cnts, 1, 1)
+    gk, gc = m_all.export()
+    assert (np.diff(gk.astype(np.int64)) > 0).all()                       # sorted, distinct
+    assert m_all.union == len(np.unique(np.concatenate(keys))) == m_all.rows
+    for s in range(16):                                                   # every record lands in its column
+        assert int(gc[:, s].astype(np.int64).sum()) == int(cnts[s].astype(np.int64).sum())
+        assert int((gc[:, s] != 0).sum()) == len(keys[s])
+    x, sm = m_all.checksum()
+    assert x == int(np.bitwise_xor.reduce(gk)) and sm == int(gc.astype(np.int64).sum())
+    m_f = ctx.join_counts(keys, cnts, 3, 5)
+    fk, fc = m_f.export()
+    keep = (gc >= 5).sum(axis=1) >= 3                                     # filter == row-wise predicate on the full matrix
+    np.testing.assert_array_equal(fk, gk[keep])
+    np.testing.assert_array_equal(fc, gc[keep])
+    m_all.free(); m_f.free()
+
+
+# ----------------------------------------------------------------- computeNF ---
+def _nf_text(names, nf):
+    return "sample\tnormalization_factor\n" + "".join("%s\t%f\n" % (n, v) for n, v in zip(names, nf))
+
+
+def test_nf_reference_fixture_goldens(ctx):
+    g = load_json("nf_cases.json")
+    z = np.load(os.path.join(GOLD, "nf_fixture.npz"))
+    m = ctx.matrix_from_host(z["counts"])
+    nf, info = ctx.compute_nf(m, dk.NF_REFERENCE)
+    m.free()
+    assert _nf_text(z["names"], nf) == g["computeNF_fixture"]          # bytes of the real computeNF binary
+    onf, _, _ = orc.nf_reference(z["counts"])
+    np.testing.assert_allclose(nf, onf, rtol=RTOL)
+    for nm in ("bigger", "small"):
+        mm = g[f"ttest_{nm}_matrix"]
+        m = ctx.matrix_from_host(np.array(mm["counts"], np.int32))
+        nf, _ = ctx.compute_nf(m, dk.NF_REFERENCE)
+        m.free()
+        assert _nf_text(mm["names"], nf) == g[f"ttest_{nm}_fixture"]
+
+
+@pytest.mark.parametrize("idx", [0, 1, 2, 3])
+def test_nf_reference_step_logic_matches_binary(ctx, idx):
+    from golden.make_golden import synth_matrix
+    case = load_json("nf_cases.json")["nf_step_cases"][idx]
+    cnts = synth_matrix(case["seed"], case["R"], case["S"])
+    m = ctx.matrix_from_host(cnts)
+    nf, info = ctx.compute_nf(m, dk.NF_REFERENCE)
+    m.free()
+    assert not info["undefined_zone"]
+    assert _nf_text([f"s{j}" for j in range(case["S"])], nf) == case["stdout"]
+
+
+@pytest.mark.parametrize("R,S,step", [(5000, 4, 1000), (20000, 16, 3000), (2500, 48, 1000), (1500, 7, 1000), (999, 3, 1000),
+                                      (3000, 200, 1000)])
+def test_nf_reference_small_steps_vs_oracle(ctx, R, S, step):
+    rng = np.random.default_rng(R + S)
+    cnts = rng.poisson(rng.uniform(2, 40, size=(R, 1)) * rng.uniform(0.5, 2, size=(1, S))).astype(np.int32)
+    onf, oused, ouz = orc.nf_reference(cnts, step)
+    m = ctx.matrix_from_host(cnts)
+    nf, info = ctx.compute_nf(m, dk.NF_REFERENCE, step)
+    m.free()
+    assert info["undefined_zone"] == ouz
+    np.testing.assert_allclose(nf, onf, rtol=RTOL)
+    if not ouz and oused < R:
+        assert info["consumed"] == oused
+
+
+def test_nf_full_vs_oracle_and_after_join(ctx):
+    rng = np.random.default_rng(12)
+    keys, cnts = random_dumps(rng, 8, 60000, 62, 0.3, 50, p_core=0.5)
+    m = ctx.join_counts(keys, cnts, 2, 2)        # chunked (non-identity) matrix layout
+    _, gc = m.export()
+    nf, info = ctx.compute_nf(m, dk.NF_FULL)
+    nf_r, _ = ctx.compute_nf(m, dk.NF_REFERENCE, 5000)
+    m.free()
+    np.testing.assert_allclose(nf, orc.nf_full(gc), rtol=RTOL)
+    np.testing.assert_allclose(nf_r, orc.nf_reference(gc, 5000)[0], rtol=RTOL)
+    assert info["n_pos"] == int((gc > 0).all(axis=1).sum())
+
+
+def test_nf_no_positive_row_fails_loudly(ctx):
+    m = ctx.matrix_from_host(np.array([[0, 1], [2, 0]], np.int32))
+    with pytest.raises(dk.DkError):
+        ctx.compute_nf(m, dk.NF_REFERENCE)
+    m.free()
+
+
+# ---------------------------------------------------------------- TtestFilter ---
+def _ttest_both(ctx, cnts, nf, idxA, idxB, pmax, fmin, p_cut=None):
+    m = ctx.matrix_from_host(cnts)
+    t = ctx.ttest_rows(m, nf, idxA, idxB)
+    t.adjust(pmax if p_cut is None else p_cut)
+    D = t.filter(pmax, fmin)
+    p, fc, adj = t.export_rows()
+    surv = t.export_survivors()
+    ties = t.ties
+    t.free(); m.free()
+    op, omA, omB, ofc = orc.ttest_rows(cnts, nf, idxA, idxB)
+    oadj = orc.bh(op)
+    np.testing.assert_allclose(p, op, rtol=RTOL, atol=1e-300)
+    np.testing.assert_allclose(fc, ofc, rtol=RTOL, atol=1e-12)
+    keep = (oadj <= pmax) & (np.abs(ofc) >= fmin)
+    # rows within 1e-9 of a threshold are "ties" (listed, not asserted)
+    tie = (np.abs(oadj - pmax) <= 1e-9 * pmax) | ((fmin != 0) & (np.abs(np.abs(ofc) - fmin) <= 1e-9 * abs(fmin)))
+    rows = surv["row"].astype(np.int64)
+    want = np.nonzero(keep & ~tie)[0]
+    assert set(want.tolist()) <= set(rows.tolist()) <= set(np.nonzero(keep | tie)[0].tolist())
+    assert (np.diff(rows) > 0).all()                                     # reference (input) order
+    np.testing.assert_allclose(surv["p_adj"], oadj[rows], rtol=RTOL, atol=1e-300)
+    np.testing.assert_allclose(surv["meanA"], omA[rows], rtol=RTOL)
+    np.testing.assert_allclose(surv["meanB"], omB[rows], rtol=RTOL)
+    np.testing.assert_allclose(surv["norm"], cnts[rows] / nf[None, :], rtol=1e-15)
+    computed = ~np.isnan(adj)
+    exact = computed & (oadj <= (pmax if p_cut is None else p_cut))
+    np.testing.assert_allclose(adj[exact], oadj[exact], rtol=RTOL, atol=1e-300)
+    assert (adj[computed] >= oadj[computed] * (1 - RTOL)).all()          # never under-estimates
+    return D, ties
+
+
+@pytest.mark.parametrize("nm", ["bigger", "small"])
+def test_ttest_reference_fixtures(ctx, nm):
+    from test_oracle import SURVEY_ROWS
+    g = load_json("nf_cases.json")
+    mm = g[f"ttest_{nm}_matrix"]
+    cnts = np.array(mm["counts"], np.int32)
+    nf = np.array([float(l.split()[2]) for l in g["ttest_conditions"].strip().split("\n")[1:]])
+    D, _ = _ttest_both(ctx, cnts, nf, [0, 1, 2], [3, 4, 5], 0.2, 0.0, p_cut=2.0)
+    kept = sum(1 for row in cnts if SURVEY_ROWS[nm][tuple(row.tolist())][1] <= 0.2)
+    assert D == kept
+
+
+@pytest.mark.parametrize("R,nA,nB,effect,pmax,fmin", [
+    (20000, 2, 2, 3.0, 0.2, 0.0), (30000, 8, 8, 4.0, 0.05, 0.0), (5000, 3, 5, 2.0, 0.05, 1.0),
+    (8000, 24, 24, 1.5, 0.01, 0.5), (3000, 100, 100, 1.3, 0.05, 0.0), (64, 2, 3, 5.0, 0.5, 0.0), (1, 2, 2, 1.0, 1.0, 0.0),
+])
+def test_ttest_random_vs_oracle(ctx, R, nA, nB, effect, pmax, fmin):
+    rng = np.random.default_rng(R + nA)
+    S = nA + nB + 1                                    # one sample in neither group (NF 0 in the reference; unused)
+    depth = rng.uniform(0.5, 2.0, S)
+    lam = rng.gamma(0.7, 20, size=(R, 1)) * depth[None, :]
+    de = rng.random(R) < 0.05
+    perm = rng.permutation(S)
+    idxA, idxB = perm[:nA].tolist(), perm[nA:nA + nB].tolist()
+    lam[np.ix_(de, idxB)] *= effect
+    cnts = rng.poisson(lam).astype(np.int32)
+    cnts[rng.random(R) < 0.1] = 0                      # all-zero rows: sd1 == sd2 == 0 => p = 0.5
+    cnts[rng.random(R) < 0.02] = 7                     # constant rows
+    nf = np.round(depth / depth.mean(), 6)             # as read back from "%f" text
+    _ttest_both(ctx, cnts, nf, idxA, idxB, pmax, fmin)
+    _ttest_both(ctx, cnts, nf, idxA, idxB, pmax, fmin, p_cut=2.0)   # full BH
+
+
+def test_ttest_group_of_one_is_refused(ctx):
+    m = ctx.matrix_from_host(np.ones((4, 3), np.int32))
+    with pytest.raises(dk.DkError):
+        ctx.ttest_rows(m, np.ones(3), [0], [1, 2])
+    m.free()
+
+
+def test_bh_heavy_ties_and_large(ctx):
+    """BH on 2M rows with massive ties (the fixtures' 93-fold tie, scaled up)"""
+    rng = np.random.default_rng(21)
+    R = 2_000_000
+    cnts = rng.poisson(3.0, size=(R, 4)).astype(np.int32)   # tiny counts => few distinct p-values
+    nf = np.array([1.0, 1.0, 1.0, 1.0])
+    m = ctx.matrix_from_host(cnts)
+    t = ctx.ttest_rows(m, nf, [0, 1], [2, 3])
+    t.adjust(2.0)
+    p, fc, adj = t.export_rows()
+    t.free(); m.free()
+    oadj = orc.bh(p)                                          # BH of the GPU's own raw p: isolates K5
+    np.testing.assert_allclose(adj, oadj, rtol=1e-15)
+    assert len(np.unique(p)) < R // 100
