@@ -1,0 +1,342 @@
+#!/usr/bin/env python
+"""bench.py — union k-mers/s merged+tested (joinCounts -> computeNF -> TtestFilter hot path).
+
+One "step" = one pass of the whole path over one batch of synthetic dumps:
+merge+recurrence filter -> NF -> Welch t-test / log2FC -> BH -> survivor selection.
+  value : U / device time, inputs already resident in HBM (dk_run_path, device pointers)
+  e2e   : same call with pinned HOST buffers: H2D of every dump and D2H of the survivors inside the timed region
+N=1 workload: BASELINE.json configs[1] (16 samples 8v8, U=1.2G union 31-mers, 300M/sample, r=3 a=5).
+N>1: every rank holds its own prefix shard of the same per-GPU size (weak scaling); the only
+cross-rank traffic is the NF broadcast, the R all-reduce and the BH candidate all-gather.
+`--impl reference` times the reference's CPU algorithm (oracle port; TtestFilter cannot be built
+here: Boost absent) on all host threads, on a bounded prefix sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+CONFIGS = {
+    2: dict(name="cfg2: 16 samples (8v8) x 300M 31-mers/sample, U=1.2G union, Zipf(2) counts, r=3 a=5",
+            S=16, U=1_200_000_000, r=3, a=5, model="two_class", q=0.075, alpha=2.0),
+    3: dict(name="cfg3: 48 samples (24v24), U=1.0G union, r=4 a=5", S=48, U=1_000_000_000, r=4, a=5, model="two_class",
+            q=0.075, alpha=2.0),
+    5: dict(name="cfg5: 16 samples genome-like (90% recurrence-1), heavy tail, U=1.0G, r=3 a=5", S=16, U=1_000_000_000,
+            r=3, a=5, model="genome", q=0.0, alpha=1.3),
+}
+PMAX, FMIN = 0.05, 0.0
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", type=int, default=2, choices=sorted(CONFIGS))
+    ap.add_argument("--scale", type=float, default=1.0, help="fraction of the config's U (1.0 = the named workload)")
+    ap.add_argument("--nf", default="reference", choices=["reference", "full"])
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-rows", type=int, default=6_000_000, help="union rows of the CPU-baseline sample")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        self.gpu, self.p = gpu, None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                       "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if not self.p:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.p.terminate()
+        out = self.p.communicate()[0]
+        sm, mx, reasons = [], 0, set()
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx = max(mx, float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        load = sm[len(sm) // 2:] if sm else []          # samples under load = upper half
+        med = load[len(load) // 2] if load else None
+        return dict(sm_mhz=med, sm_max_mhz=mx or None, reasons=sorted(reasons), samples=len(sm))
+
+
+def algorithmic_bytes(n_records, R, S):
+    """B_alg = 12*sum N_s + R*(8+4S) + R*4S + 32*R ; merge kernel alone: 12*sum N + R*(8+4S)"""
+    merge = 12 * n_records + R * (8 + 4 * S)
+    return merge + R * 4 * S + 32 * R, merge
+
+
+# ------------------------------------------------------------------ CPU reference arm ---
+def cpu_path(keys, cnts, cfg, idxA, idxB, threads):
+    """the reference algorithm (oracle port of joinCounts -> computeNF -> TtestFilter) on `threads` host threads.
+    The merge and the per-row test are prefix-separable, so threads>1 splits the key range; NF and BH stay serial."""
+    import numpy as np
+    import oracle_lib as orc
+    S = cfg["S"]
+    t0 = time.perf_counter()
+    if threads == 1:
+        parts = [orc.join(keys, cnts, cfg["r"], cfg["a"])]
+    else:
+        allk = np.concatenate([k[:: max(1, len(k) // 64)] for k in keys if len(k)])
+        edges = np.quantile(allk, np.linspace(0, 1, threads + 1)[1:-1]).astype(np.uint64)
+        cuts = [np.concatenate([[0], np.searchsorted(k, edges), [len(k)]]) for k in keys]
+        parts = [None] * threads
+
+        def work(p):
+            parts[p] = orc.join([k[c[p]:c[p + 1]] for k, c in zip(keys, cuts)], [v[c[p]:c[p + 1]] for v, c in zip(cnts, cuts)],
+                                cfg["r"], cfg["a"])
+        th = [threading.Thread(target=work, args=(p,)) for p in range(threads)]
+        [t.start() for t in th]; [t.join() for t in th]
+    mk = np.concatenate([p[0] for p in parts]); mc = np.concatenate([p[1] for p in parts]); U = sum(p[2] for p in parts)
+    nf, _, _ = orc.nf_reference(mc)
+    nf = np.array([float("%f" % v) for v in nf])                 # the pipeline's "%f" round trip
+    R = len(mk)
+    if threads == 1 or R < threads * 4:
+        p, mA, mB, fc = orc.ttest_rows(mc, nf, idxA, idxB)
+    else:
+        res = [None] * threads
+        b = np.linspace(0, R, threads + 1).astype(int)
+
+        def work2(i):
+            res[i] = orc.ttest_rows(mc[b[i]:b[i + 1]], nf, idxA, idxB)
+        th = [threading.Thread(target=work2, args=(i,)) for i in range(threads)]
+        [t.start() for t in th]; [t.join() for t in th]
+        p, fc = np.concatenate([r[0] for r in res]), np.concatenate([r[3] for r in res])
+    adj = orc.bh(p)
+    D = int(((adj <= PMAX) & (np.abs(fc) >= FMIN)).sum())
+    return U, R, D, time.perf_counter() - t0
+
+
+def make_cpu_sample(cfg, rows):
+    import torch
+    from dekupl_run_b200 import synth
+    dev = "cuda" if torch.cuda.is_available() else "cpu"
+    k, c = synth.gen_shard(cfg["S"], cfg["U"], 0, rows, device=dev, model=cfg["model"], q=cfg["q"], alpha=cfg["alpha"], chunk=1 << 22)
+    import numpy as np
+    return [x.cpu().numpy().view(np.uint64) for x in k], [x.cpu().numpy() for x in c]
+
+
+def run_reference(args):
+    """--impl reference: rank 0 alone; the other ranks exit 0 without work"""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cfg = CONFIGS[args.config]
+    S = cfg["S"]
+    idxA, idxB = list(range(S // 2)), list(range(S // 2, S))
+    threads = os.cpu_count() or 1
+    rows = args.cpu_rows * min(threads, 8)
+    keys, cnts = make_cpu_sample(cfg, rows)
+    times, U = [], 0
+    for i in range(args.warmup + args.steps):
+        U, R, D, dt = cpu_path(keys, cnts, cfg, idxA, idxB, threads)
+        if i >= args.warmup:
+            times.append(dt)
+    ms = 1e3 * sum(times) / len(times)
+    val = U / (ms / 1e3)
+    sample = f"first {rows} of {cfg['U']} union rows of the same generator (prefix shard), {sum(len(k) for k in keys)} records"
+    print(json.dumps({
+        "impl": "reference", "metric": "union k-mers/s merged+tested", "value": val, "unit": "k-mers/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u64 keys / i32 counts / f64 statistics", "data": "synthetic",
+        "config": {"workload": cfg["name"], "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "k-mers/s", "cores": threads, "kind": "port", "sample": sample,
+                         "note": "oracle C port of joinCounts+computeNF+TtestFilter (TtestFilter needs Boost: unbuildable here), "
+                                 "prefix-split over all host threads"},
+        "e2e": {"value": val, "unit": "k-mers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+# ----------------------------------------------------------------------------- our arm ---
+def run_ours(args):
+    import numpy as np
+    import torch
+    import dekupl_run_b200 as dk
+    from dekupl_run_b200 import synth
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    cfg = CONFIGS[args.config]
+    S = cfg["S"]
+    idxA, idxB = list(range(S // 2)), list(range(S // 2, S))
+    rows_rank = int(cfg["U"] * args.scale)
+    rows_total = rows_rank * world                      # weak scaling: every rank owns a full-size prefix shard
+    t0 = time.time()
+    keys, cnts = synth.gen_shard(S, rows_total, rank * rows_rank, (rank + 1) * rows_rank, device=dev, model=cfg["model"],
+                                 q=cfg["q"], alpha=cfg["alpha"])
+    torch.cuda.synchronize()
+    t_gen = time.time() - t0
+    n = [int(k.numel()) for k in keys]
+    n_rec = sum(n)
+    kp, cp = [k.data_ptr() for k in keys], [c.data_ptr() for c in cnts]
+    ctx = dk.Context(local)
+    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    nf_mode = dk.NF_REFERENCE if args.nf == "reference" else dk.NF_FULL
+
+    if world == 1:
+        def step():
+            return ctx.run_path(kp, cp, n, True, cfg["r"], cfg["a"], nf_mode, idxA, idxB, PMAX, FMIN, nf_text_roundtrip=True)
+    else:
+        from dekupl_run_b200.distributed import GpuBackend, run_sharded
+        be = GpuBackend(ctx, dev)
+
+        def step():
+            st = run_sharded(be, kp, cp, n, cfg["r"], cfg["a"], idxA, idxB, PMAX, FMIN, nf_mode=args.nf, device=dev)
+            be.free()
+            return st
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        stats = step()
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    merge_ms, stage = [], np.zeros(4)
+    e0.record()
+    for _ in range(args.steps):
+        stats = step()
+        merge_ms.append(ctx.stage_ms(4))
+        stage += [ctx.stage_ms(0), ctx.stage_ms(1), ctx.stage_ms(2), ctx.stage_ms(3)]
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    launches = (ctx.launches - l0) // args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    if dist:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    U, R = stats["U"], stats["R"]
+    value = U / (ms / 1e3)
+    R_loc = stats.get("R_local", R)
+    b_all, b_merge = algorithmic_bytes(n_rec, R_loc, S)
+    mk = sum(merge_ms) / len(merge_ms)
+    peaks, peak_src = {}, "fallback"
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))); peak_src = "measured"
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    ach = b_merge / (mk / 1e3) / 1e9
+    out = {
+        "metric": "union k-mers/s merged+tested", "value": value, "unit": "k-mers/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u64 keys / i32 counts / f64 statistics", "data": "synthetic",
+        "config": {"workload": cfg["name"] + (f" (scale {args.scale})" if args.scale != 1.0 else ""), "rows_per_gpu": rows_rank,
+                   "union_kmers": U, "records": n_rec * world if world > 1 else n_rec, "filtered_rows": R, "survivors": stats["D"],
+                   "nf_mode": args.nf, "pmax": PMAX, "l2": "inputs (%.1f GB/GPU) far larger than the 126 MB L2" % (12 * n_rec / 1e9),
+                   "gen_s": round(t_gen, 1), "ties": list(stats["ties"])},
+        "gpu_launches": int(launches),
+        "stage_ms": {"join": stage[0] / args.steps, "merge_kernel": mk, "nf": stage[1] / args.steps, "ttest": stage[2] / args.steps,
+                     "bh_filter": stage[3] / args.steps},
+        "roofline": {"bound": "hbm", "kernel": "k_merge (k-way merge + recurrence filter)", "achieved": ach, "peak": peak,
+                     "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)",
+                     "alg_bytes_per_launch": b_merge, "kernel_ms": mk,
+                     "whole_path": {"alg_bytes": b_all, "achieved": b_all / (ms / 1e3) / 1e9, "frac": b_all / (ms / 1e3) / 1e9 / peak}},
+        "clocks": clocks,
+    }
+    # ---- e2e: host buffers through the C ABI, H2D of all dumps + D2H of the survivors inside the timed region
+    if not args.no_e2e and world == 1:
+        out["e2e"] = run_e2e(args, cfg, ctx, keys, cnts, n, idxA, idxB, nf_mode)
+    elif world > 1:
+        out["e2e"] = {"value": None, "unit": "k-mers/s", "note": "measured at N=1 only (host staging is per-GPU identical)"}
+    if rank == 0 and not args.no_cpu:
+        ck, cc = make_cpu_sample(cfg, args.cpu_rows)
+        cU, cR, cD, dt = cpu_path(ck, cc, cfg, idxA, idxB, 1)
+        out["cpu_baseline"] = {"value": cU / dt, "unit": "k-mers/s", "cores": 1, "kind": "port", "seconds": dt,
+                               "sample": f"first {args.cpu_rows} of {cfg['U']} rows of the same generator ({cU} union k-mers), "
+                                         "oracle C port of the three single-threaded reference tools"}
+    if rank == 0:
+        print(json.dumps(out))
+    if dist:
+        dist.destroy_process_group()
+
+
+def run_e2e(args, cfg, ctx, keys, cnts, n, idxA, idxB, nf_mode):
+    import numpy as np
+    import psutil
+    import torch
+    n_rec = sum(n)
+    need = 12 * n_rec
+    avail = psutil.virtual_memory().available
+    frac = 1.0
+    if need * 1.3 > avail:                              # pinned staging must fit in host RAM
+        frac = max(0.05, avail / (need * 1.5))
+    hk, hc, hn = [], [], []
+    for k, c in zip(keys, cnts):
+        m = int(k.numel() * frac)
+        hk.append(k[:m].cpu().pin_memory()); hc.append(c[:m].cpu().pin_memory()); hn.append(m)
+    if frac < 1.0:                                      # a prefix of every dump is not a prefix shard; cut by key instead
+        kmax = min(int(k[-1].item()) for k in hk if k.numel())
+        hn = [int(torch.searchsorted(k, kmax, right=True).item()) for k in hk]
+    del keys[:], cnts[:]
+    torch.cuda.empty_cache()
+    kp, cp = [k.data_ptr() for k in hk], [c.data_ptr() for c in hc]
+    h2d = 12 * sum(hn)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    times, d2h, U = [], 0, 0
+    for i in range(1 + 2):
+        torch.cuda.synchronize()
+        e0.record()
+        st, m, t = ctx.run_path(kp, cp, hn, False, cfg["r"], cfg["a"], nf_mode, idxA, idxB, PMAX, FMIN, True, keep=True)
+        surv = t.export_survivors() if t is not None else {}
+        e1.record()
+        torch.cuda.synchronize()
+        d2h = sum(v.nbytes for v in surv.values()) + 8 * 8 + 8 * cfg["S"]
+        U = st["U"]
+        if t is not None:
+            t.free()
+        m.free()
+        if i >= 1:
+            times.append(e0.elapsed_time(e1))
+    ms = sum(times) / len(times)
+    return {"value": U / (ms / 1e3), "unit": "k-mers/s", "ms_per_step": ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "union_kmers": U, "workload_fraction": frac,
+            "note": "dk_run_path on pinned host dumps; D2H = survivor table + stats (the filtered matrix stays on the device)"}
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -1,0 +1,147 @@
+"""Prefix-sharded hot path over N GPUs (one process per GPU, torch.distributed for the plumbing).
+
+Rows are independent for the merge, the filter and the per-row test, so every rank runs those on
+its own k-mer prefix shard with no data-path collective (rank order == key order, so the
+concatenation of the ranks' outputs is the reference's sorted output). Global pieces only:
+  * NF, reference mode : computeNF consumes a PREFIX of the sorted matrix -> the ranks owning the
+                         first rows compute it; here rank 0 (its shard must cover the rows consumed),
+                         then one broadcast of S doubles.
+  * NF, full mode      : exact global median per sample by radix select; per round one all-reduce
+                         of S*256 uint64 histogram bins (8 rounds).
+  * BH                 : all-reduce of R, all-gather of the candidate p-values (p <= P); every rank
+                         ranks the global candidate list and adjusts its own rows.
+The per-rank compute is behind a small backend interface so the collective logic can be tested on
+CPU with gloo (tests/test_distributed_cpu.py drives it with an oracle-backed backend)."""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def nf_text_round(nf):
+    """computeNF prints "%f" (computeNF.c:174); TtestFilter reads it back with atof (TtestFilter.c:261)"""
+    return np.array([float("%f" % v) for v in nf])
+
+
+class GpuBackend:
+    """per-rank compute through the C ABI (libdekupl_b200.so)"""
+
+    def __init__(self, ctx, device):
+        self.ctx, self.device = ctx, device
+        self.m = self.t = self.nfs = None
+
+    def join(self, key_ptrs, cnt_ptrs, n, r, a):
+        self.m = self.ctx.join_counts_dev(key_ptrs, cnt_ptrs, n, r, a)
+        return self.m.rows, self.m.union
+
+    def nf_reference(self, step_rows=0):
+        from .binding import NF_REFERENCE
+        return self.ctx.compute_nf(self.m, NF_REFERENCE, step_rows)
+
+    # full mode building blocks
+    def nf_begin(self):
+        import ctypes as C
+        st, n = C.c_void_p(0), C.c_uint64(0)
+        self.ctx._chk(self.ctx.L.dk_nf_begin(self.ctx.h, self.m.h, C.byref(st), C.byref(n)))
+        self.nfs = st
+        self.hist = torch.zeros(self.m.samples * 256, dtype=torch.int64, device=self.device)
+        return int(n.value)
+
+    def nf_set_rank(self, k):
+        self.ctx._chk(self.ctx.L.dk_nf_set_rank(self.ctx.h, self.nfs, k))
+
+    def nf_hist(self):
+        self.ctx._chk(self.ctx.L.dk_nf_hist_dev(self.ctx.h, self.nfs, self.hist.data_ptr()))
+        self.ctx.sync()
+        return self.hist
+
+    def nf_advance(self, hist):
+        self.ctx._chk(self.ctx.L.dk_nf_advance_dev(self.ctx.h, self.nfs, hist.data_ptr()))
+
+    def nf_result(self):
+        import ctypes as C
+        S = self.m.samples
+        out = (C.c_double * S)()
+        self.ctx._chk(self.ctx.L.dk_nf_result(self.ctx.h, self.nfs, out))
+        self.ctx.L.dk_nf_end(self.ctx.h, self.nfs)
+        self.nfs = None
+        return np.array(out[:])
+
+    def ttest_rows(self, nf, idxA, idxB):
+        self.t = self.ctx.ttest_rows(self.m, nf, idxA, idxB)
+
+    def candidates(self, p_cut):
+        """-> float64 tensor (device) of this rank's candidate p-values"""
+        n, ptr = self.t.candidates(p_cut)
+        self.ctx.sync()
+        if n == 0:
+            return torch.empty(0, dtype=torch.float64, device=self.device)
+        from .torch_interop import tensor_from_ptr
+        return tensor_from_ptr(ptr, n, torch.float64, self.device)
+
+    def adjust_global(self, all_p, R_global):
+        self.t.adjust_global(all_p.data_ptr() if all_p.numel() else 0, all_p.numel(), R_global)
+
+    def filter(self, pmax, fmin):
+        return self.t.filter(pmax, fmin), self.t.ties
+
+    def free(self):
+        if self.t is not None:
+            self.t.free()
+        if self.m is not None:
+            self.m.free()
+        self.t = self.m = None
+
+
+def _all_gather_var(x, group=None):
+    """all-gather of 1-D tensors of different lengths (sizes first, then padded payload)"""
+    world = dist.get_world_size(group)
+    n = torch.tensor([x.numel()], dtype=torch.int64, device=x.device)
+    sizes = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(sizes, n, group=group)
+    sizes = [int(s.item()) for s in sizes]
+    mx = max(sizes)
+    if mx == 0:
+        return x
+    pad = torch.zeros(mx, dtype=x.dtype, device=x.device)
+    pad[: x.numel()] = x
+    out = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(out, pad, group=group)
+    return torch.cat([o[:s] for o, s in zip(out, sizes)])
+
+
+def run_sharded(backend, key_ptrs, cnt_ptrs, n, r, a, idxA, idxB, pmax, fmin, nf_mode="reference", nf_step=0,
+                nf_text_roundtrip=True, device=None):
+    """one pass of the whole path on this rank's shard; returns the global stats (identical on every rank)"""
+    rank, world = dist.get_rank(), dist.get_world_size()
+    R_loc, U_loc = backend.join(key_ptrs, cnt_ptrs, n, r, a)
+    tot = torch.tensor([R_loc, U_loc], dtype=torch.int64, device=device)
+    dist.all_reduce(tot)
+    R_glob, U_glob = int(tot[0].item()), int(tot[1].item())
+    S = len(key_ptrs)
+    nf = torch.zeros(S, dtype=torch.float64, device=device)
+    if nf_mode == "reference":
+        if rank == 0:
+            v, info = backend.nf_reference(nf_step)
+            nf = torch.tensor(v, dtype=torch.float64, device=device)
+        dist.broadcast(nf, src=0)
+        nf = nf.cpu().numpy()
+    else:
+        n_pos = backend.nf_begin()
+        t = torch.tensor([n_pos], dtype=torch.int64, device=device)
+        dist.all_reduce(t)
+        backend.nf_set_rank(int(t.item()) // 2)               # element [size/2], computeNF.c:43
+        for _ in range(8):
+            h = backend.nf_hist()
+            dist.all_reduce(h)
+            backend.nf_advance(h)
+        nf = backend.nf_result()
+    nf_used = nf_text_round(nf) if nf_text_roundtrip else nf
+    backend.ttest_rows(nf_used, idxA, idxB)
+    cand = backend.candidates(pmax)
+    all_p = _all_gather_var(cand)
+    backend.adjust_global(all_p, R_glob)
+    D_loc, ties = backend.filter(pmax, fmin)
+    d = torch.tensor([D_loc, ties[0], ties[1], ties[2]], dtype=torch.int64, device=device)
+    dist.all_reduce(d)
+    return dict(U=U_glob, R=R_glob, D=int(d[0].item()), ties=tuple(int(x) for x in d[1:].tolist()), nf=nf,
+                R_local=R_loc, U_local=U_loc, D_local=D_loc, n_cand=int(all_p.numel()))
