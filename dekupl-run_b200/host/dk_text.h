@@ -1,0 +1,137 @@
+// dk_text.h — text side of the drop-in CLIs: gz/plain file slurp, kseq-compatible tokenisation,
+// 2-bit k-mer codec, buffered formatting. The reference tools read through klib's kstream
+// (share/*/kseq.h:90-141): tokens end at ANY isspace byte, files may be gzip (multi-member) or
+// plain, the last line may lack '\n', numbers are parsed with atoi/atof.
+#pragma once
+#include <ctype.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <zlib.h>
+#include <string>
+#include <vector>
+
+struct DkFile {
+    std::vector<char> buf;   // whole decompressed content + trailing '\0'
+    bool load(const char *path)
+    {
+        gzFile fp = gzopen(path, "r");            // transparent for plain files, concatenated members handled by zlib
+        if (!fp) return false;
+        gzbuffer(fp, 1 << 20);
+        size_t cap = 1 << 22, len = 0;
+        buf.resize(cap);
+        for (;;) {
+            if (cap - len < (1 << 20)) { cap *= 2; buf.resize(cap); }
+            int n = gzread(fp, buf.data() + len, (unsigned)(cap - len - 1 > (1u << 30) ? (1u << 30) : cap - len - 1));
+            if (n <= 0) break;
+            len += (size_t)n;
+        }
+        gzclose(fp);
+        buf.resize(len + 1);
+        buf[len] = '\0';
+        return true;
+    }
+    size_t size() const { return buf.size() - 1; }
+};
+
+// cursor over a DkFile with ks_getuntil(KS_SEP_SPACE) semantics: a token is the (possibly empty)
+// run of bytes up to the next isspace byte; dret = that delimiter (0 at EOF).
+struct DkCursor {
+    const char *p, *end;
+    int dret = 0;
+    DkCursor(const DkFile &f) : p(f.buf.data()), end(f.buf.data() + f.size()) {}
+    bool eof() const { return p >= end; }
+    // returns false when no token could be read (EOF before any byte)
+    bool token(const char *&s, size_t &len)
+    {
+        if (p >= end) { dret = 0; return false; }
+        s = p;
+        while (p < end && !isspace((unsigned char)*p)) p++;
+        len = (size_t)(p - s);
+        if (p < end) { dret = (unsigned char)*p; p++; } else dret = 0;
+        return true;
+    }
+    void skip_line()   // as `while ((dret = ks_getc(ks)) > 0 && dret != '\n')`
+    {
+        if (dret == '\n') return;
+        while (p < end && *p != '\n') p++;
+        if (p < end) { dret = '\n'; p++; } else dret = 0;
+    }
+    bool line(const char *&s, size_t &len)   // KS_SEP_LINE
+    {
+        if (p >= end) return false;
+        s = p;
+        while (p < end && *p != '\n') p++;
+        len = (size_t)(p - s);
+        if (p < end) { dret = '\n'; p++; } else dret = 0;
+        return true;
+    }
+};
+
+static inline int dk_atoi(const char *s, size_t len)   // atoi on a non-terminated token
+{
+    size_t i = 0;
+    bool neg = false;
+    if (i < len && (s[i] == '+' || s[i] == '-')) { neg = s[i] == '-'; i++; }
+    long long v = 0;
+    for (; i < len && s[i] >= '0' && s[i] <= '9'; i++) { v = v * 10 + (s[i] - '0'); if (v > 0x7fffffffLL + 1) v = 0x7fffffffLL + 1; }
+    v = neg ? -v : v;
+    return (int)v;
+}
+
+// 2-bit packing, first base most significant; returns false on k > 31 or a non-ACGT byte
+static inline bool dk_encode(const char *s, size_t len, uint64_t &out)
+{
+    if (len == 0 || len > 31) return false;
+    uint64_t v = 0;
+    for (size_t i = 0; i < len; i++) {
+        unsigned c;
+        switch (s[i]) {
+            case 'A': c = 0; break;
+            case 'C': c = 1; break;
+            case 'G': c = 2; break;
+            case 'T': c = 3; break;
+            default: return false;
+        }
+        v = (v << 2) | c;
+    }
+    out = v;
+    return true;
+}
+static inline void dk_decode(uint64_t v, int k, char *out)
+{
+    for (int i = k - 1; i >= 0; i--) { out[i] = "ACGT"[v & 3]; v >>= 2; }
+}
+
+struct DkOut {   // buffered stdout/gz writer
+    FILE *fp = nullptr;
+    gzFile gz = nullptr;
+    std::vector<char> b;
+    DkOut() { b.reserve(1 << 22); }
+    void flush()
+    {
+        if (b.empty()) return;
+        if (gz) gzwrite(gz, b.data(), (unsigned)b.size()); else fwrite(b.data(), 1, b.size(), fp);
+        b.clear();
+    }
+    void put(const char *s, size_t n) { b.insert(b.end(), s, s + n); if (b.size() > (1 << 22) - 4096) flush(); }
+    void putc_(char c) { b.push_back(c); }
+    void put_int(int v)   // "%d"
+    {
+        char t[16];
+        int n = 0;
+        long long x = v;
+        bool neg = x < 0;
+        if (neg) x = -x;
+        do { t[n++] = (char)('0' + x % 10); x /= 10; } while (x);
+        if (neg) t[n++] = '-';
+        while (n) b.push_back(t[--n]);
+    }
+    void printf_(const char *fmt, double v)
+    {
+        char t[512];
+        int n = snprintf(t, sizeof t, fmt, v);
+        put(t, (size_t)n);
+    }
+};

@@ -1,0 +1,112 @@
+"""The three drop-in CLIs (dekupl-run_b200/host/bin/{joinCounts,computeNF,TtestFilter}): same argv,
+stdout bytes and exit codes as the reference tools."""
+import gzip
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from common import GOLD, load_json
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "dekupl-run_b200", "host", "bin")
+
+
+def run(tool, *args, cwd=None):
+    return subprocess.run([os.path.join(BIN, tool), *args], capture_output=True, text=True, cwd=cwd)
+
+
+# ------------------------------------------------------------------ CPU: argv surface ---
+def test_usage_and_exit_codes_without_arguments():
+    r = run("joinCounts")
+    assert r.returncode == 1 and "Usage:   joinCounts [options] <counts.tsv> [<counts.tsv> ...]" in r.stderr
+    assert "Options: -r INT    min recurrence [1]" in r.stderr and r.stdout == ""
+    r = run("joinCounts", "-r", "3", "-a", "7")
+    assert r.returncode == 1 and "min recurrence [3]" in r.stderr and "abundance [7]" in r.stderr
+    r = run("computeNF")
+    assert r.returncode == 1 and "Usage:   computeNF [options] <counts.tsv>" in r.stderr
+    r = run("TtestFilter", "a", "b", "c")
+    assert r.returncode == 1 and "Usage:   ttestFilter [options] <counts.tsv> <conditions.tsv> <conditionA> <conditionB>" in r.stderr
+    assert "max pvalue [0.05]" in r.stderr
+
+
+def test_missing_input_file_fails_like_the_reference():
+    for tool, args in (("joinCounts", ["/nonexistent/x.txt"]), ("computeNF", ["/nonexistent/x.tsv"]),
+                       ("TtestFilter", ["/nonexistent/x.tsv", "/nonexistent/c.tsv", "A", "B"])):
+        r = run(tool, *args)
+        assert r.returncode != 0 and "Failed to open /nonexistent/x" in r.stderr
+
+
+def test_poisson_mode_is_refused_not_faked(tmp_path):
+    r = run("TtestFilter", "-l", "a", "b", "A", "B")
+    assert r.returncode != 0 and "not implemented" in r.stderr
+
+
+# ------------------------------------------------------------------ GPU: stdout parity ---
+@pytest.mark.gpu
+def test_joinCounts_cli_matches_reference_binary_bytes(tmp_path):
+    for ci, case in enumerate(load_json("join_cases.json")):
+        files = []
+        for i, txt in enumerate(case["inputs"]):
+            p = tmp_path / f"c{ci}_s{i}.txt"
+            if i % 2:                       # mix plain and gz inputs (gzopen is transparent)
+                p = tmp_path / f"c{ci}_s{i}.txt.gz"
+                with gzip.open(p, "wt") as f:
+                    f.write(txt)
+            else:
+                p.write_text(txt)
+            files.append(str(p))
+        r = run("joinCounts", *case["args"], *files)
+        assert r.returncode == 0, r.stderr
+        assert r.stdout == case["stdout"], case["args"]
+
+
+@pytest.mark.gpu
+def test_computeNF_cli_matches_reference_binary_bytes(tmp_path):
+    g = load_json("nf_cases.json")
+    z = np.load(os.path.join(GOLD, "nf_fixture.npz"))
+    p = tmp_path / "raw-counts.tsv.gz"
+    body = "".join("K%d\t" % i + "\t".join(map(str, row)) + "\n" for i, row in enumerate(z["counts"].tolist()))
+    with open(p, "wb") as f:                 # two gzip members: header, then body (Snakefile:594-596)
+        f.write(gzip.compress(("tag\t" + "\t".join(z["names"].tolist()) + "\n").encode()))
+        f.write(gzip.compress(body.encode()))
+    r = run("computeNF", str(p))
+    assert r.returncode == 0, r.stderr
+    assert r.stdout == g["computeNF_fixture"]
+    # ragged row => the reference's message and a failure exit
+    bad = tmp_path / "bad.tsv"
+    bad.write_text("tag\ta\tb\nK1\t1\t2\nK2\t3\nK3\t4\t5\n")
+    r = run("computeNF", str(bad))
+    assert r.returncode != 0 and "inconsistent number of column (line 2)" in r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nm", ["bigger", "small"])
+def test_TtestFilter_cli_fixture(tmp_path, nm):
+    import oracle_lib as orc
+    g = load_json("nf_cases.json")
+    mm = g[f"ttest_{nm}_matrix"]
+    cnts = np.array(mm["counts"], np.int32)
+    counts = tmp_path / "counts.tsv.gz"
+    with gzip.open(counts, "wt") as f:
+        f.write("tag\t" + "\t".join(mm["names"]) + "\n")
+        for k, row in zip(mm["kmers"], mm["counts"]):
+            f.write(k + "\t" + "\t".join(map(str, row)) + "\n")
+    conds = tmp_path / "conds.tsv"
+    conds.write_text(g["ttest_conditions"])
+    raw = tmp_path / "raw_pvals.txt.gz"
+    r = run("TtestFilter", "-p", "0.2", "-r", str(raw), str(counts), str(conds), "A", "B", cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    assert "Group A: sampleA1, sampleA2, sampleA3" in r.stderr and "Adjusting pvalues with Benjamini" in r.stderr
+    assert not os.path.exists(tmp_path / ".TtestFilter.tmp")
+    nf = np.array([float(l.split()[2]) for l in g["ttest_conditions"].strip().split("\n")[1:]])
+    p, mA, mB, fc = orc.ttest_rows(cnts, nf, [0, 1, 2], [3, 4, 5])
+    adj = orc.bh(p)
+    want = "tag\tpvalue\tmeanA\tmeanB\tlog2FC\t" + "\t".join(mm["names"]) + "\n"
+    for i in range(len(cnts)):
+        if adj[i] <= 0.2 and abs(fc[i]) >= 0:
+            want += "%s\t%f\t%f\t%f\t%f" % (mm["kmers"][i], adj[i], mA[i], mB[i], fc[i])
+            want += "".join("\t%.2f" % (cnts[i, j] / nf[j]) for j in range(6)) + "\n"
+    assert r.stdout == want
+    assert gzip.open(raw, "rt").read() == "".join("%s\t%f\n" % (k, v) for k, v in zip(mm["kmers"], p))
