@@ -349,6 +349,8 @@ __global__ void __launch_bounds__(128) k_merge(MergeParams P)
     }
 }
 
+#include "dk_merge2.cuh"
+
 // -------------------------------------------------------- chunk bookkeeping ---
 // totals[0]=R, totals[1]=U, totals[2]=chunks requested, totals[3]=npart
 __global__ void k_join_totals(const uint32_t *part_rows, const uint32_t *part_union, const uint32_t *npart,
@@ -482,6 +484,7 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     k_part_starts<<<NB + 1, 32, 0, st>>>(T, S, NB, range, flag, rank, starts, npart_d); DK_LAUNCHED(ctx);
 
     // ---- K2 launch geometry
+    const bool use_v2 = (S <= M2_S) && !getenv("DK_MERGE_V1");   // v2: thread-per-key-range merge (dk_merge2.cuh)
     MergeCfg cfg = pick_cfg(S);
     size_t stream_bytes = dk_round_up((size_t)S * (cfg.chk * cfg.nslot * 12 + cfg.nslot * 8), 16);
     int gpw = 32 / cfg.gw;
@@ -525,7 +528,15 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
 
         DK_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
         cudaError_t e;
-        if (cfg.gw == 16) e = launch_merge<16, 1, 8, 4>(ctx, P, warps, grid, smem);
+        if (use_v2) {
+            e = cudaFuncSetAttribute(k_merge2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M2Smem));
+            if (e == cudaSuccess) {
+                int per_sm = (int)(budget / (sizeof(M2Smem) + 1024));
+                if (per_sm < 1) per_sm = 1;
+                k_merge2<<<ctx->sm_count * per_sm, M2_NT, sizeof(M2Smem), ctx->stream>>>(P);
+                e = cudaGetLastError();
+            }
+        } else if (cfg.gw == 16) e = launch_merge<16, 1, 8, 4>(ctx, P, warps, grid, smem);
         else if (cfg.spl == 1) e = launch_merge<32, 1, 8, 4>(ctx, P, warps, grid, smem);
         else if (cfg.spl == 2) e = launch_merge<32, 2, 8, 4>(ctx, P, warps, grid, smem);
         else if (cfg.spl == 4) e = launch_merge<32, 4, 8, 2>(ctx, P, warps, grid, smem);

@@ -80,6 +80,11 @@ def test_join_edge_cases(ctx):
                                     np.uint64(123456789) + rng.integers(0, 40000, 30000).astype(np.uint64)]))
     _join_both(ctx, [hot[::2], hot[::3], hot], [np.ones(len(hot[::2]), np.int32) * 6, np.ones(len(hot[::3]), np.int32),
                                                 np.ones(len(hot), np.int32) * 9], 2, 5)
+    # more duplicates of one key inside a dump than one staging window holds (merge v2 fallback path)
+    dup = np.sort(np.concatenate([np.full(700, 5000, np.uint64), rng.integers(0, 10000, 300).astype(np.uint64)]))
+    oth = np.unique(rng.integers(0, 10000, 2000).astype(np.uint64))
+    _join_both(ctx, [dup, oth, oth[::2]], [np.arange(len(dup), dtype=np.int32) % 9, np.full(len(oth), 6, np.int32),
+                                           np.full(len(oth[::2]), 2, np.int32)], 1, 3)
     # large counts up to INT_MAX
     _join_both(ctx, [np.array([1, 2], np.uint64)] * 2, [np.array([2 ** 31 - 1, 5], np.int32), np.array([7, 2 ** 31 - 1], np.int32)], 2, 6)
 
