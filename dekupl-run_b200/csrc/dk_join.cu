@@ -350,11 +350,12 @@ __global__ void __launch_bounds__(128) k_merge(MergeParams P)
 }
 
 #include "dk_merge2.cuh"
+#include "dk_merge3.cuh"
 
 // -------------------------------------------------------- chunk bookkeeping ---
 // totals[0]=R, totals[1]=U, totals[2]=chunks requested, totals[3]=npart
 __global__ void k_join_totals(const uint32_t *part_rows, const uint32_t *part_union, const uint32_t *npart,
-                              const uint32_t *chunk_counter, uint64_t *totals)
+                              const uint32_t *chunk_counter, const uint32_t *overflow, uint64_t *totals)
 {
     __shared__ uint64_t sr[32], su[32];
     uint32_t NP = *npart;
@@ -366,7 +367,7 @@ __global__ void k_join_totals(const uint32_t *part_rows, const uint32_t *part_un
     if (threadIdx.x == 0) {
         r = 0; u = 0;
         for (int w = 0; w < (blockDim.x + 31) / 32; w++) { r += sr[w]; u += su[w]; }
-        totals[0] = r; totals[1] = u; totals[2] = *chunk_counter; totals[3] = NP;
+        totals[0] = r; totals[1] = u; totals[2] = *chunk_counter; totals[3] = NP; totals[4] = *overflow;
     }
 }
 __global__ void k_chunk_order(const uint32_t *chunk_part, const uint32_t *chunk_seq, const uint32_t *part_choff,
@@ -454,8 +455,18 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     T.cnts = (const int32_t *const *)(tab + (size_t)S * 8);
     T.n = (const uint64_t *)(tab + (size_t)S * 16);
 
-    // ---- K1: partitions of ~PART_TARGET records
-    const uint64_t PART_TARGET = 16384;
+    // kernel choice: v3 (merge-path tree, any S) by default; DK_MERGE=1|2 forces the older kernels (profiling)
+    size_t budget = ctx->smem_optin ? ctx->smem_optin : 227 * 1024;
+    int which = 3;
+    if (const char *e = getenv("DK_MERGE")) which = atoi(e);
+    M3Cfg G3;
+    memset(&G3, 0, sizeof G3);
+    if (which == 3 && !m3_make_cfg(S, budget, G3)) which = 1;
+    if (which == 2 && S > M2_S) which = 1;
+
+    // ---- K1: partitions of ~PART_TARGET records (v3 consumes ~4K records per round: longer partitions
+    //      amortise the partial last round)
+    const uint64_t PART_TARGET = which == 3 ? 65536 : 16384;
     uint64_t np_want = total / PART_TARGET + 1;
     int nb_log2 = 4;
     while ((1ull << nb_log2) < np_want * 4 && nb_log2 < 24) nb_log2++;
@@ -473,7 +484,7 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     uint32_t *scal = (uint32_t *)dk_dev_alloc(ctx, sizeof(uint32_t) * (16 + 4 * (size_t)NPmax));
     uint64_t *totals = (uint64_t *)dk_dev_alloc(ctx, 64);
     if (!range || !below || !flag || !rank || !starts || !scal || !totals) return DK_ERR_NOMEM;
-    uint32_t *npart_d = scal, *work_d = scal + 1, *chunkctr_d = scal + 2;
+    uint32_t *npart_d = scal, *work_d = scal + 1, *chunkctr_d = scal + 2, *overflow_d = scal + 3;
     uint32_t *part_nchunks = scal + 16, *part_rows = part_nchunks + NPmax, *part_union = part_rows + NPmax,
              *part_choff = part_union + NPmax;   // NPmax entries (+1 lives in rank reuse below)
 
@@ -484,12 +495,10 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     k_part_starts<<<NB + 1, 32, 0, st>>>(T, S, NB, range, flag, rank, starts, npart_d); DK_LAUNCHED(ctx);
 
     // ---- K2 launch geometry
-    const bool use_v2 = (S <= M2_S) && !getenv("DK_MERGE_V1");   // v2: thread-per-key-range merge (dk_merge2.cuh)
     MergeCfg cfg = pick_cfg(S);
     size_t stream_bytes = dk_round_up((size_t)S * (cfg.chk * cfg.nslot * 12 + cfg.nslot * 8), 16);
     int gpw = 32 / cfg.gw;
     size_t warp_bytes = stream_bytes * gpw;
-    size_t budget = ctx->smem_optin ? ctx->smem_optin : 227 * 1024;
     int warps = 4;
     while (warps > 1 && warp_bytes * warps > budget / 2) warps >>= 1;
     if (warp_bytes * warps > budget) return dk_fail(ctx, DK_ERR_UNSUPPORTED, "join: S=%d needs %zu B smem per warp", S, warp_bytes);
@@ -505,8 +514,8 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     dk_matrix *m = new dk_matrix();
     m->S = S;
     uint32_t *chunk_part = nullptr, *chunk_seq = nullptr;
-    uint64_t h_tot[4] = {0, 0, 0, 0};
-    for (int attempt = 0; attempt < 2; attempt++) {
+    uint64_t h_tot[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int attempt = 0; attempt < 3; attempt++) {
         uint64_t cap = guess + 1;   // +1: room for the stale-tail row
         if (cap >= 0xFFFFFFF0ull) { dk_matrix_release(ctx, m); return dk_fail(ctx, DK_ERR_NOMEM, "join: too many chunks"); }
         m->cap_chunks = cap;
@@ -528,7 +537,16 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
 
         DK_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
         cudaError_t e;
-        if (use_v2) {
+        if (which == 3) {
+            e = cudaFuncSetAttribute(k_merge3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G3.smem_bytes);
+            if (e == cudaSuccess) {
+                int per_sm = (int)((budget + 1024) / ((size_t)G3.smem_bytes + 1024));
+                if (per_sm < 1) per_sm = 1;
+                if (per_sm > 2) per_sm = 2;
+                k_merge3<<<ctx->sm_count * per_sm, M3_NT, G3.smem_bytes, ctx->stream>>>(P, G3, overflow_d);
+                e = cudaGetLastError();
+            }
+        } else if (which == 2) {
             e = cudaFuncSetAttribute(k_merge2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M2Smem));
             if (e == cudaSuccess) {
                 int per_sm = (int)(budget / (sizeof(M2Smem) + 1024));
@@ -544,19 +562,27 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
         ctx->launches++;
         if (e != cudaSuccess) { dk_matrix_release(ctx, m); return dk_fail(ctx, DK_ERR_CUDA, "merge launch: %s", cudaGetErrorString(e)); }
         DK_CUDA(ctx, cudaEventRecord(ctx->ev[3], st));
-        k_join_totals<<<1, 256, 0, st>>>(part_rows, part_union, npart_d, chunkctr_d, totals); DK_LAUNCHED(ctx);
+        k_join_totals<<<1, 256, 0, st>>>(part_rows, part_union, npart_d, chunkctr_d, overflow_d, totals); DK_LAUNCHED(ctx);
         DK_CUDA(ctx, cudaMemcpyAsync(h_tot, totals, sizeof h_tot, cudaMemcpyDeviceToHost, st));
         DK_CUDA(ctx, cudaStreamSynchronize(st));
         float ms = 0;
         cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3]);
         ctx->stage_ms[4] = ms;
+        if (h_tot[4] && which == 3) {
+            // a dump holds one k-mer more than 4 times: v3's copy-index field overflowed; redo with the v1 kernel
+            which = 1;
+            dk_dev_release(ctx, m->keys); dk_dev_release(ctx, m->cnts); dk_dev_release(ctx, m->chunk_rows);
+            dk_dev_release(ctx, chunk_part); dk_dev_release(ctx, chunk_seq);
+            m->keys = nullptr; m->cnts = nullptr; m->chunk_rows = nullptr;
+            continue;
+        }
         if (h_tot[2] <= guess) break;
         // overflow: the counter kept counting, so h_tot[2] is the exact need
         dk_dev_release(ctx, m->keys); dk_dev_release(ctx, m->cnts); dk_dev_release(ctx, m->chunk_rows);
         dk_dev_release(ctx, chunk_part); dk_dev_release(ctx, chunk_seq);
         m->keys = nullptr; m->cnts = nullptr; m->chunk_rows = nullptr;
         guess = h_tot[2];
-        if (attempt == 1) { dk_matrix_release(ctx, m); return dk_fail(ctx, DK_ERR_CUDA, "join: output overflow twice"); }
+        if (attempt == 2) { dk_matrix_release(ctx, m); return dk_fail(ctx, DK_ERR_CUDA, "join: output overflow twice"); }
     }
     g_chunk_hint = h_tot[2];
     m->R = h_tot[0]; m->U = h_tot[1]; m->n_chunks = h_tot[2];

@@ -1,0 +1,406 @@
+// dk_merge3.cuh — K2 v3: tile merge by a balanced pairwise merge-path tree in shared memory
+// (included by dk_join.cu; any S <= 256; reference semantics: share/joinCounts/joinCounts.c:72-115).
+//
+// r01b ncu of v2 (profiles/r01b_ncu_merge_v2.csv): a thread-sequential 16-way merge keeps only
+// 13 of 32 lanes busy (key ranges hold very different numbers of rows) and pays O(S) per row.
+// v3 has no data-dependent trip counts at all. A CTA walks its partition in ROUNDS:
+//   R0  every sample contributes a window of <= caps records (+1 look-ahead), staged by 1-D TMA bulk
+//       copies (cp.async.bulk + mbarrier complete_tx) into bufK / bufC;
+//   R1  pivot = smallest look-ahead key, so every key < pivot is complete in the staged windows;
+//   R2  each staged record becomes ONE 64-bit word  (key - base) << 15 | dup << 13 | slot  — order
+//       by word == order by (key, copy index inside the dump, sample); slot addresses the count in
+//       bufC; the round's key span is clipped to 2^49 so the word is exact (never lossy);
+//   R3  log2(S_pad) merge levels, ping-pong between two buffers: every thread finds its diagonal
+//       by merge-path binary search and emits exactly 17 words (odd => conflict-free blocked stores);
+//       runs are padded with PAD and fenced with GUARD words so the serial merge needs no bounds checks;
+//   R4  rows = runs of equal (key,dup): head flags + block scan give row ids, a scan of the
+//       (count >= a) flags gives each row's recurrence (joinCounts.c:81-83), a scan of the verdicts
+//       (rec >= r, :104) gives in-order output slots;
+//   R5  surviving rows are assembled in shared memory (zero-filled, one 4-byte store per record) and
+//       copied out with coalesced 128-bit stores into the matrix chunks.
+// Duplicate k-mers inside one dump become consecutive rows exactly like the reference; more than
+// 4 copies of one k-mer in one dump (never produced by jellyfish) raise the overflow flag and the
+// host reruns the join with the v1 kernel.
+#pragma once
+
+#define M3_NT 256
+#define M3_VT 17
+#define M3_TP (M3_NT * M3_VT)      // 4352 word slots per round
+#define M3_SB 13                   // slot bits (slot < S_pad*ks < 8192)
+#define M3_DB 2                    // copy-index bits
+#define M3_KSH (M3_SB + M3_DB)
+#define M3_PAD 0xFFFFFFFFFFFFFFFEull
+#define M3_GUARD 0xFFFFFFFFFFFFFFFFull
+#define M3_SPAN ((1ull << (64 - M3_KSH)) - 1ull)   // consumable keys: key - base < M3_SPAN
+
+struct M3Cfg {
+    int S, S_pad, caps, ks, levels, tps_log2, BR, S4;
+    uint32_t divKS, divS, divS4;                  // ceil(2^32 / x): exact floor(q/x) for q < 2^16
+    uint32_t off_A, off_C, off_rowbuf, off_keybuf, off_small, smem_bytes;
+};
+
+struct M3Small {
+    unsigned long long red[2][M3_NT / 32];
+    unsigned long long bar;
+    uint32_t scan[M3_NT / 32];
+    uint32_t part, total_real, any;
+    uint32_t chunk_cur, rowpos, seq, newbase, nnew, have_cur;
+    uint32_t prow, puni;
+    uint16_t lo[256], n[256];
+};
+
+__device__ __forceinline__ uint32_t m3_block_excl_scan(uint32_t v, M3Small &sm, uint32_t &total)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    __syncthreads();                       // protects sm.scan from the previous use
+    if (lane == 31) sm.scan[w] = x;
+    __syncthreads();
+    uint32_t off = 0, tot = 0;
+#pragma unroll
+    for (int i = 0; i < M3_NT / 32; i++) { uint32_t s = sm.scan[i]; if (i < w) off += s; tot += s; }
+    total = tot;
+    return off + x - v;
+}
+
+__device__ __forceinline__ unsigned long long m3_warp_min(unsigned long long v)
+{
+#pragma unroll
+    for (int o = 16; o; o >>= 1) { unsigned long long y = __shfl_xor_sync(0xffffffffu, v, o); v = y < v ? y : v; }
+    return v;
+}
+
+__global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uint32_t *overflow)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    unsigned long long *bufK = reinterpret_cast<unsigned long long *>(smem_raw);                 // staging keys / merge buffer B
+    unsigned long long *bufA = reinterpret_cast<unsigned long long *>(smem_raw + G.off_A);
+    int32_t *bufC = reinterpret_cast<int32_t *>(smem_raw + G.off_C);
+    int32_t *rowbuf = reinterpret_cast<int32_t *>(smem_raw + G.off_rowbuf);
+    unsigned long long *keybuf = reinterpret_cast<unsigned long long *>(smem_raw + G.off_keybuf);
+    M3Small &sm = *reinterpret_cast<M3Small *>(smem_raw + G.off_small);
+
+    const int S = G.S, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int caps = G.caps, ks = G.ks;
+    const uint32_t npart = *P.npart;
+    const uint32_t bar = smem_u32(&sm.bar);
+    const bool owner = tid < S;
+    if (tid == 0) {
+        mbar_init(bar, (uint32_t)S);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    const uint64_t *ksrc = owner ? P.T.keys[tid] : nullptr;
+    const int32_t *csrc = owner ? P.T.cnts[tid] : nullptr;
+    const unsigned long long nsrc = owner ? P.T.n[tid] : 0ull;
+    __syncthreads();
+    uint32_t phase = 0;
+    const int min_ab = P.min_abund, min_rec = P.min_rec;
+
+    for (;;) {
+        if (tid == 0) sm.part = atomicAdd(P.work_counter, 1u);
+        __syncthreads();
+        const uint32_t part = sm.part;
+        if (part >= npart) break;
+        unsigned long long cur = 0, endg = 0;
+        if (owner) { cur = P.starts[(size_t)part * S + tid]; endg = P.starts[(size_t)(part + 1) * S + tid]; }
+        if (tid == 0) { sm.chunk_cur = CHUNK_NONE; sm.rowpos = 0; sm.seq = 0; sm.prow = 0; sm.puni = 0; }
+
+        for (;;) {   // ---- rounds
+            // R0: stage the windows
+            uint32_t lo = 0, L = 0;
+            if (tid == 0) { sm.total_real = 0; }
+            if (owner) {
+                const unsigned long long a0 = cur & ~3ull;
+                lo = (uint32_t)(cur - a0);
+                const unsigned long long left = endg - cur;
+                L = (uint32_t)(left < (unsigned long long)(caps + 1) ? left : (unsigned long long)(caps + 1));
+                uint32_t tq = 0;
+                unsigned long long mend = a0;
+                if (L) {
+                    const uint32_t nq = (lo + L + 3u) >> 2;
+                    const unsigned long long avail = (nsrc - a0) >> 2;
+                    tq = (uint32_t)(avail < nq ? avail : nq);
+                    mend = a0 + 4ull * nq;
+                    if (mend > nsrc) mend = nsrc;
+                }
+                unsigned long long *kd = bufK + (size_t)tid * ks;
+                int32_t *cd = bufC + (size_t)tid * ks;
+                if (tq) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // earlier generic accesses precede the async writes
+                    mbar_expect_tx(bar, tq * 48u);
+                    tma_bulk_g2s(smem_u32(kd), ksrc + a0, tq * 32u, bar);
+                    tma_bulk_g2s(smem_u32(cd), csrc + a0, tq * 16u, bar);
+                } else mbar_arrive(bar);
+                for (unsigned long long g = a0 + 4ull * tq; g < mend; g++) { kd[g - a0] = ksrc[g]; cd[g - a0] = csrc[g]; }   // array tail (< 4 records)
+            }
+            mbar_wait(bar, phase);
+            phase ^= 1u;
+            __syncthreads();
+            // R1: pivot (smallest look-ahead key) and base (smallest first key)
+            unsigned long long candk = DK_SENTINEL, firstk = DK_SENTINEL;
+            uint32_t ncm = 0;
+            if (owner && L) {
+                const unsigned long long *kw = bufK + (size_t)tid * ks + lo;
+                firstk = kw[0];
+                if (L == (uint32_t)(caps + 1)) { candk = kw[caps]; ncm = (uint32_t)caps; } else ncm = L;
+            }
+            candk = m3_warp_min(candk);
+            firstk = m3_warp_min(firstk);
+            if (lane == 0) { sm.red[0][warp] = candk; sm.red[1][warp] = firstk; }
+            __syncthreads();
+            unsigned long long pivot = DK_SENTINEL, base = DK_SENTINEL;
+#pragma unroll
+            for (int i = 0; i < M3_NT / 32; i++) {
+                unsigned long long a = sm.red[0][i], b = sm.red[1][i];
+                pivot = a < pivot ? a : pivot;
+                base = b < base ? b : base;
+            }
+            if (base == DK_SENTINEL) break;                        // every window empty: partition done
+            {
+                unsigned long long lim = base + M3_SPAN;
+                if (lim < base) lim = DK_SENTINEL;                 // saturate
+                pivot = lim < pivot ? lim : pivot;
+            }
+            // R2: consumable prefix of every window
+            uint32_t n = 0;
+            if (owner && ncm) {
+                const unsigned long long *kw = bufK + (size_t)tid * ks + lo;
+                uint32_t a = 0, b = ncm;
+                while (a < b) { uint32_t mid = (a + b) >> 1; if (kw[mid] < pivot) a = mid + 1; else b = mid; }
+                n = a;
+                if (n) atomicAdd(&sm.total_real, n);
+            }
+            if (tid < G.S_pad) { sm.lo[tid] = (uint16_t)lo; sm.n[tid] = (uint16_t)n; }
+            __syncthreads();
+            const uint32_t T = sm.total_real;
+            if (T == 0) {                                          // >= caps copies of one k-mer inside a dump
+                if (tid == 0) atomicExch(overflow, 1u);
+                break;
+            }
+            // R3: pack (key,dup,slot) words into the level-0 runs
+            {
+                const int s = tid >> G.tps_log2, sub = tid & ((1 << G.tps_log2) - 1), tps = 1 << G.tps_log2;
+                const uint32_t slo = sm.lo[s], sn = sm.n[s];
+                const unsigned long long *kw = bufK + (size_t)s * ks + slo;
+                unsigned long long *run = bufA + (size_t)s * (caps + 1);
+                const uint32_t slot0 = (uint32_t)s * ks + slo;
+#pragma unroll 1
+                for (int k = 0; k < M3_VT; k++) {
+                    const uint32_t i = (uint32_t)(sub + k * tps);
+                    unsigned long long w = M3_PAD;
+                    if (i < sn) {
+                        const unsigned long long key = kw[i];
+                        uint32_t d = 0;
+                        if (i > 0 && kw[i - 1] == key) {           // copies of one k-mer inside a dump (rare)
+                            d = 1;
+                            while (d < i && kw[i - 1 - d] == key) d++;
+                            if (d > 3) { atomicExch(overflow, 1u); d = 3; }
+                        }
+                        w = ((key - base) << M3_KSH) | ((unsigned long long)d << M3_SB) | (unsigned long long)(slot0 + i);
+                    }
+                    run[i] = w;
+                }
+                if (sub == 0) run[caps] = M3_GUARD;
+            }
+            __syncthreads();
+            // R4: merge tree
+            unsigned long long *X = bufA, *Y = bufK;
+            {
+                int len = caps;
+                for (int l = 0; l < G.levels; l++) {
+                    const int sh = G.tps_log2 + 1 + l;
+                    const int pair = tid >> sh;
+                    const int d = (tid & ((1 << sh) - 1)) * M3_VT;
+                    const unsigned long long *a_base = X + (size_t)(2 * pair) * (len + 1);
+                    const unsigned long long *b_base = a_base + (len + 1);
+                    int alo = d > len ? d - len : 0, ahi = d < len ? d : len;
+                    while (alo < ahi) {
+                        const int mid = (alo + ahi) >> 1;
+                        if (a_base[mid] <= b_base[d - 1 - mid]) alo = mid + 1; else ahi = mid;
+                    }
+                    int ai = alo, bi = d - alo;
+                    unsigned long long a = a_base[ai], b = b_base[bi];
+                    unsigned long long *out = Y + (size_t)pair * (2 * len + 1) + d;
+#pragma unroll
+                    for (int i = 0; i < M3_VT; i++) {
+                        const bool ta = a <= b;
+                        out[i] = ta ? a : b;
+                        if (ta) a = a_base[++ai]; else b = b_base[++bi];
+                    }
+                    if (d + M3_VT == 2 * len) out[M3_VT] = M3_GUARD;
+                    __syncthreads();
+                    unsigned long long *t = X; X = Y; Y = t;
+                    len *= 2;
+                }
+            }
+            // R5: rows. X = merged words (T real, then PAD); Y is free: rowab u16[TP+1], orow u16[TP]
+            uint16_t *rowab = reinterpret_cast<uint16_t *>(Y);
+            uint16_t *orow = rowab + (M3_TP + 8);
+            const uint32_t j0 = (uint32_t)tid * M3_VT;
+            uint32_t headmask = 0, abmask = 0;
+            {
+                unsigned long long prevkp = (tid == 0) ? ~0ull : (X[j0 - 1] >> M3_SB);
+#pragma unroll
+                for (int i = 0; i < M3_VT; i++) {
+                    const unsigned long long w = X[j0 + i];
+                    const bool real = w < M3_PAD;
+                    const unsigned long long kp = w >> M3_SB;
+                    if (real && kp != prevkp) headmask |= 1u << i;
+                    prevkp = kp;
+                    if (real && bufC[(uint32_t)w & ((1u << M3_SB) - 1u)] >= min_ab) abmask |= 1u << i;      // joinCounts.c:81-83
+                }
+            }
+            uint32_t tot1;
+            const uint32_t ex1 = m3_block_excl_scan((__popc(headmask) << 16) | __popc(abmask), sm, tot1);
+            const uint32_t rowbase = ex1 >> 16, abbase = ex1 & 0xffffu, nrows = tot1 >> 16;
+            {
+                uint32_t hm = headmask;
+                while (hm) {
+                    const int i = __ffs(hm) - 1;
+                    hm &= hm - 1;
+                    const uint32_t below = (1u << i) - 1u;
+                    rowab[rowbase + __popc(headmask & below)] = (uint16_t)(abbase + __popc(abmask & below));
+                }
+                if (tid == M3_NT - 1) rowab[nrows] = (uint16_t)(tot1 & 0xffffu);
+            }
+            __syncthreads();
+            uint32_t passmask = 0;
+#pragma unroll
+            for (int i = 0; i < M3_VT; i++) {
+                const uint32_t r = j0 + i;
+                if (r < nrows && (int)(rowab[r + 1] - rowab[r]) >= min_rec) passmask |= 1u << i;           // joinCounts.c:104
+            }
+            uint32_t nout;
+            const uint32_t obase = m3_block_excl_scan(__popc(passmask), sm, nout);
+#pragma unroll
+            for (int i = 0; i < M3_VT; i++) {
+                const uint32_t r = j0 + i;
+                if (r < nrows) orow[r] = ((passmask >> i) & 1u) ? (uint16_t)(obase + __popc(passmask & ((1u << i) - 1u))) : (uint16_t)0xFFFFu;
+            }
+            // chunk allocation for nout rows appended to the partition's chunk sequence
+            if (tid == 0) {
+                const uint32_t have = (sm.chunk_cur != CHUNK_NONE) ? 1u : 0u;
+                const uint32_t slots = have ? (DK_CH - sm.rowpos) : 0u;
+                const uint32_t nnew = nout > slots ? (nout - slots + DK_CH - 1) / DK_CH : 0u;
+                uint32_t nb = 0;
+                if (nnew) {
+                    nb = atomicAdd(P.chunk_counter, nnew);
+                    for (uint32_t k = 0; k < nnew; k++) {
+                        const uint32_t id = nb + k;
+                        if (id < P.max_chunks) { P.chunk_part[id] = part; P.chunk_seq[id] = sm.seq + k; P.chunk_rows[id] = DK_CH; }
+                    }
+                }
+                sm.have_cur = have; sm.newbase = nb; sm.nnew = nnew;
+            }
+            __syncthreads();
+            // R6: assemble surviving rows in shared memory, copy out coalesced
+            {
+                const uint32_t have = sm.have_cur, nb = sm.newbase, ccur = sm.chunk_cur;
+                const uint32_t rp = have ? sm.rowpos : 0u;
+                for (uint32_t b0 = 0; b0 < nout; b0 += (uint32_t)G.BR) {
+                    const uint32_t nbr = (nout - b0) < (uint32_t)G.BR ? (nout - b0) : (uint32_t)G.BR;
+                    const uint32_t words = nbr * (uint32_t)S;
+                    {
+                        int4 *z = reinterpret_cast<int4 *>(rowbuf);
+                        const uint32_t n4 = (words + 3u) >> 2;
+                        for (uint32_t i = tid; i < n4; i += M3_NT) z[i] = make_int4(0, 0, 0, 0);
+                    }
+                    __syncthreads();
+#pragma unroll
+                    for (int i = 0; i < M3_VT; i++) {
+                        if (j0 + i < T) {
+                            const uint32_t r = rowbase + __popc(headmask & ((2u << i) - 1u)) - 1u;
+                            const uint32_t o = (uint32_t)orow[r] - b0;
+                            if (o < nbr) {
+                                const unsigned long long w = X[j0 + i];
+                                const uint32_t slot = (uint32_t)w & ((1u << M3_SB) - 1u);
+                                const uint32_t s = __umulhi(slot, G.divKS);
+                                rowbuf[o * (uint32_t)S + s] = bufC[slot];
+                                if ((headmask >> i) & 1u) keybuf[o] = base + (w >> M3_KSH);
+                            }
+                        }
+                    }
+                    __syncthreads();
+                    if (G.S4) {
+                        const uint32_t S4 = (uint32_t)G.S4, n4 = nbr * S4;
+                        const int4 *src4 = reinterpret_cast<const int4 *>(rowbuf);
+                        for (uint32_t i = tid; i < n4; i += M3_NT) {
+                            const uint32_t rr = __umulhi(i, G.divS4), c4 = i - rr * S4;
+                            const uint32_t v = rp + b0 + rr, k = v / DK_CH, off = v % DK_CH;
+                            const uint32_t chunk = (have && k == 0) ? ccur : nb + (k - have);
+                            if (chunk < P.max_chunks)
+                                reinterpret_cast<int4 *>(P.out_cnts + ((size_t)chunk * DK_CH + off) * S)[c4] = src4[i];
+                        }
+                    } else {
+                        for (uint32_t i = tid; i < words; i += M3_NT) {
+                            const uint32_t rr = __umulhi(i, G.divS), c = i - rr * (uint32_t)S;
+                            const uint32_t v = rp + b0 + rr, k = v / DK_CH, off = v % DK_CH;
+                            const uint32_t chunk = (have && k == 0) ? ccur : nb + (k - have);
+                            if (chunk < P.max_chunks) P.out_cnts[((size_t)chunk * DK_CH + off) * S + c] = rowbuf[i];
+                        }
+                    }
+                    for (uint32_t rr = tid; rr < nbr; rr += M3_NT) {
+                        const uint32_t v = rp + b0 + rr, k = v / DK_CH, off = v % DK_CH;
+                        const uint32_t chunk = (have && k == 0) ? ccur : nb + (k - have);
+                        if (chunk < P.max_chunks) P.out_keys[(size_t)chunk * DK_CH + off] = keybuf[rr];
+                    }
+                    __syncthreads();
+                }
+            }
+            // R7: advance the partition state
+            cur += n;
+            if (tid == 0) {
+                const uint32_t v = (sm.have_cur ? sm.rowpos : 0u) + nout;
+                if (sm.nnew) {
+                    sm.chunk_cur = sm.newbase + sm.nnew - 1;
+                    sm.seq += sm.nnew;
+                    sm.rowpos = v - (sm.have_cur + sm.nnew - 1) * DK_CH;
+                } else sm.rowpos = v;
+                if (sm.chunk_cur != CHUNK_NONE && sm.rowpos == DK_CH) { sm.chunk_cur = CHUNK_NONE; sm.rowpos = 0; }
+                sm.prow += nout; sm.puni += nrows;
+            }
+            __syncthreads();
+        }
+        __syncthreads();
+        if (tid == 0) {
+            if (sm.chunk_cur != CHUNK_NONE && sm.chunk_cur < P.max_chunks) P.chunk_rows[sm.chunk_cur] = sm.rowpos;
+            P.part_nchunks[part] = sm.seq;
+            P.part_rows[part] = sm.prow;
+            P.part_union[part] = sm.puni;
+        }
+        __syncthreads();
+    }
+}
+
+// host side: geometry for S samples
+static bool m3_make_cfg(int S, size_t smem_budget, M3Cfg &G)
+{
+    if (S < 1 || S > 256) return false;
+    int sp = 1, lv = 0;
+    while (sp < S) { sp <<= 1; lv++; }
+    G.S = S; G.S_pad = sp; G.levels = lv; G.tps_log2 = 8 - lv;
+    G.caps = M3_TP / sp;
+    G.ks = (G.caps + 4 + 3) & ~3;
+    if ((size_t)sp * G.ks >= (1u << M3_SB)) return false;
+    G.S4 = (S % 4 == 0) ? S / 4 : 0;
+    auto cdiv32 = [](uint32_t x) { return (uint32_t)(((1ull << 32) + x - 1) / x); };
+    G.divKS = cdiv32((uint32_t)G.ks); G.divS = cdiv32((uint32_t)S); G.divS4 = G.S4 ? cdiv32((uint32_t)G.S4) : 0;
+    size_t bK = (size_t)sp * G.ks * 8, bM = (size_t)(M3_TP + sp) * 8;
+    if (bK < bM) bK = bM;
+    if (bK < 2 * (size_t)(M3_TP + 8) * 2 + 64) return false;
+    size_t off = dk_round_up(bK, 128);
+    G.off_A = (uint32_t)off; off += dk_round_up(bM, 128);
+    G.off_C = (uint32_t)off; off += dk_round_up((size_t)sp * G.ks * 4, 128);
+    int BR = 16384 / (4 * S);
+    if (BR > 256) BR = 256;
+    if (BR < 8) BR = 8;
+    G.BR = BR;
+    G.off_rowbuf = (uint32_t)off; off += dk_round_up((size_t)BR * S * 4 + 16, 128);
+    G.off_keybuf = (uint32_t)off; off += dk_round_up((size_t)BR * 8, 128);
+    G.off_small = (uint32_t)off; off += dk_round_up(sizeof(M3Small), 128);
+    G.smem_bytes = (uint32_t)off;
+    return off <= smem_budget;
+}
