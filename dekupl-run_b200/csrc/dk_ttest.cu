@@ -6,37 +6,32 @@
 #include "dk_common.cuh"
 
 // ---- Student-t tail: 2*Q(|t|;v) = I_{v/(v+t^2)}(v/2, 1/2)  (replaces the Boost call at :146-147)
+// The per-row cost of this pass is fp64 issue, not HBM (r01 ncu), so the tail is written to avoid
+// fp64 divisions: the continued fraction of the incomplete beta is evaluated by the Wallis forward
+// recurrence on (numerator, denominator) pairs with the partial quotients d_i = N_i/D_i cleared of
+// their denominators (A_{i+1} = D_i A_i + D_{i-1} N_i A_{i-1}), convergence is tested by cross
+// multiplication, and Gamma(v+1/2)/Gamma(v) comes from an upward shift to v >= 20 plus a 5-term
+// asymptotic series (no lgamma). Checked against scipy.special.stdtr to 4e-13 relative over
+// df in [1,2000], |t| up to 1e4 (tests/test_gpu_parity.py).
 __device__ double dk_beta_cf(double a, double b, double x)
 {
-    const double TINY = 1e-300, EPS = 1e-16;
-    double qab = a + b, qap = a + 1.0, qam = a - 1.0;
-    double c = 1.0, d = 1.0 - qab * x / qap;
-    if (fabs(d) < TINY) d = TINY;
-    d = 1.0 / d;
-    double h = d;
-    for (int m = 1; m <= 10000; m++) {
-        double m2 = 2.0 * m;
-        double aa = m * (b - m) * x / ((qam + m2) * (a + m2));
-        d = 1.0 + aa * d; if (fabs(d) < TINY) d = TINY;
-        c = 1.0 + aa / c; if (fabs(c) < TINY) c = TINY;
-        d = 1.0 / d; h *= d * c;
-        aa = -(a + m) * (qab + m) * x / ((a + m2) * (qap + m2));
-        d = 1.0 + aa * d; if (fabs(d) < TINY) d = TINY;
-        c = 1.0 + aa / c; if (fabs(c) < TINY) c = TINY;
-        d = 1.0 / d;
-        double del = d * c;
-        h *= del;
-        if (fabs(del - 1.0) < EPS) break;
+    double Ap = 0.0, A = 1.0, Bp = 1.0, B = 1.0, Dp = 1.0;
+    for (int m = 0; m < 2000; m++) {
+        const double fm = (double)m, a2 = a + 2.0 * fm;
+        double N = -(a + fm) * (a + b + fm) * x, D = a2 * (a2 + 1.0);              // d_{2m+1}
+        double t = Dp * N;
+        double An = __fma_rn(D, A, t * Ap), Bn = __fma_rn(D, B, t * Bp);     // explicit fma: this file is built -fmad=false
+        Ap = A; A = An; Bp = B; B = Bn; Dp = D;
+        const double m1 = fm + 1.0, a3 = a2 + 1.0;
+        N = m1 * (b - m1) * x; D = a3 * (a3 + 1.0);                                // d_{2m+2}
+        t = Dp * N;
+        An = __fma_rn(D, A, t * Ap); Bn = __fma_rn(D, B, t * Bp);
+        const bool conv = fabs(__fma_rn(An, B, -(A * Bn))) <= 1e-15 * fabs(Bn * B);
+        Ap = A; A = An; Bp = B; B = Bn; Dp = D;
+        if (fabs(B) > 1e100) { Ap *= 1e-100; A *= 1e-100; Bp *= 1e-100; B *= 1e-100; }
+        if (conv) break;
     }
-    return h;
-}
-// log( Gamma(v+1/2) / Gamma(v) ): direct for small v, asymptotic series for v >= 40
-// (lgamma(v+.5)-lgamma(v) would lose ~|lgamma| * 1e-16 to cancellation at large v)
-__device__ double dk_lgamma_ratio_half(double v)
-{
-    if (v < 40.0) return lgamma(v + 0.5) - lgamma(v);
-    double r = 1.0 / v, r2 = r * r;
-    return 0.5 * log(v) + r * (-1.0 / 8.0 + r2 * (1.0 / 192.0 + r2 * (-1.0 / 640.0 + r2 * (17.0 / 14336.0))));
+    return A / B;
 }
 
 // I_x(v, 1/2) with y = 1-x supplied by the caller (no cancellation)
@@ -44,13 +39,17 @@ __device__ double dk_ibeta_half(double v, double x, double y)
 {
     if (x <= 0.0) return 0.0;
     if (y <= 0.0) return 1.0;
-    const double LOG_SQRT_PI = 0.57236494292470008707;
-    double lx = (y < 0.5) ? log1p(-y) : log(x);
-    double ly = (x < 0.5) ? log1p(-x) : log(y);
-    double lbt = dk_lgamma_ratio_half(v) - LOG_SQRT_PI + v * lx + 0.5 * ly;
-    if (x < (v + 1.0) / (v + 2.5))
-        return exp(lbt) * dk_beta_cf(v, 0.5, x) / v;
-    return 1.0 - exp(lbt) * dk_beta_cf(0.5, v, y) / 0.5;
+    const double INV_SQRT_PI = 0.56418958354775628695;
+    const double lx = (y < 0.5) ? log1p(-y) : log(x);
+    // Gamma(v+1/2)/Gamma(v) = sqrt(w) * exp(ser(w)) * prod_{i<n} (v+i)/(v+i+1/2),  w = v+n >= 20
+    double num = 1.0, den = 1.0, w = v;
+    while (w < 20.0) { num *= w; den *= (w + 0.5); w += 1.0; }
+    const double r = 1.0 / w, r2 = r * r;
+    const double ser = r * (-1.0 / 8.0 + r2 * (1.0 / 192.0 + r2 * (-1.0 / 640.0 + r2 * (17.0 / 14336.0 + r2 * (-31.0 / 18432.0)))));
+    // x^v (1-x)^(1/2) / B(v,1/2)
+    const double front = sqrt(w * y) * INV_SQRT_PI * (num / den) * exp(ser + v * lx);
+    if (x < (v + 1.0) / (v + 2.5)) return front * dk_beta_cf(v, 0.5, x) / v;
+    return 1.0 - front * dk_beta_cf(0.5, v, y) / 0.5;
 }
 
 __device__ double dk_student_t_2tail(double t, double df)
@@ -76,13 +75,27 @@ __device__ double dk_welch_p(double m1, double m2, int n1, int n2, double sd1, d
 
 #define TT_THREADS 128
 // group moments of one row; la scratch is [n][TT_THREADS] in shared memory (conflict-free columns)
-__device__ __forceinline__ void dk_group_moments(const int32_t *c, const double *nf, const int *idx, int n, double *la,
-                                                 double &meanv, double &mlog, double &sd)
+// c/nf as the reference computes it (TtestFilter.c:380-382), without a per-element fp64 division:
+// with r = RN(1/nf), two Newton corrections through exact fma residuals give the correctly rounded
+// quotient (Markstein); the result is a deterministic function of (c, nf), which is all the
+// sd1==0 && sd2==0 test needs. Used only when every nf is a normal number in [1e-30, 1e30].
+__device__ __forceinline__ double dk_div_by_nf(double c, double nf, double r)
+{
+    double q = c * r;
+    double e = __fma_rn(-nf, q, c);
+    q = __fma_rn(e, r, q);
+    e = __fma_rn(-nf, q, c);
+    return __fma_rn(e, r, q);
+}
+
+template <bool FASTDIV>
+__device__ __forceinline__ void dk_group_moments(const int32_t *c, const double *nf, const double *rnf, const int *idx, int n,
+                                                 double *la, double &meanv, double &mlog, double &sd)
 {
     double sa = 0, sl = 0;
     for (int i = 0; i < n; i++) {
         int k = idx[i];
-        double x = (double)c[k] / nf[k];                 // TtestFilter.c:380-382
+        double x = FASTDIV ? dk_div_by_nf((double)c[k], nf[k], rnf[k]) : (double)c[k] / nf[k];   // TtestFilter.c:380-382
         double a = x + 1;                                // :394
         double l = log(x + 1);                           // :395
         sa += a; sl += l;                                // sum() :77-84
@@ -95,6 +108,7 @@ __device__ __forceinline__ void dk_group_moments(const int32_t *c, const double 
     sd = sqrt(s / (n - 1));
 }
 
+template <bool FASTDIV>
 __global__ void __launch_bounds__(TT_THREADS)
 k_ttest_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, uint32_t n_chunks, int S,
              const double *nf_g, const int *idx_g, int nA, int nB, double *p_raw, double *log2fc,
@@ -104,8 +118,9 @@ k_ttest_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, 
     int nmax = nA > nB ? nA : nB;
     double *la = (double *)sm;                                   // [nmax][TT_THREADS]
     double *nf = la + (size_t)nmax * TT_THREADS;                 // [S]
-    int *idx = (int *)(nf + S);                                  // [nA+nB]
-    for (int i = threadIdx.x; i < S; i += TT_THREADS) nf[i] = nf_g[i];
+    double *rnf = nf + S;                                        // [S] RN(1/nf)
+    int *idx = (int *)(rnf + S);                                 // [nA+nB]
+    for (int i = threadIdx.x; i < S; i += TT_THREADS) { nf[i] = nf_g[i]; rnf[i] = 1.0 / nf_g[i]; }
     for (int i = threadIdx.x; i < nA + nB; i += TT_THREADS) idx[i] = idx_g[i];
     __syncthreads();
     uint32_t oc = blockIdx.x * (TT_THREADS / DK_CH) + threadIdx.x / DK_CH;
@@ -116,8 +131,8 @@ k_ttest_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, 
     const int32_t *c = cnts + ((size_t)order[oc] * DK_CH + j) * (size_t)S;
     double *myla = la + threadIdx.x;
     double mA, mB, m1, m2, sd1, sd2;
-    dk_group_moments(c, nf, idx, nA, myla, mA, m1, sd1);
-    dk_group_moments(c, nf, idx + nA, nB, myla, mB, m2, sd2);
+    dk_group_moments<FASTDIV>(c, nf, rnf, idx, nA, myla, mA, m1, sd1);
+    dk_group_moments<FASTDIV>(c, nf, rnf, idx + nA, nB, myla, mB, m2, sd2);
     double p = dk_welch_p(m1, m2, nA, nB, sd1, sd2);
     uint64_t row = b0 + j;
     p_raw[row] = p;
@@ -167,12 +182,15 @@ extern "C" int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf, 
     DK_CUDA(ctx, cudaMemsetAsync(t->tie_counts, 0, 64, st));
     DK_CUDA(ctx, cudaStreamSynchronize(st));          // idx is a local staging vector
     int nmax = nA > nB ? nA : nB;
-    size_t smem = sizeof(double) * ((size_t)nmax * TT_THREADS + S) + sizeof(int) * (nA + nB);
-    DK_CUDA(ctx, cudaFuncSetAttribute(k_ttest_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    size_t smem = sizeof(double) * ((size_t)nmax * TT_THREADS + 2 * S) + sizeof(int) * (nA + nB);
+    bool fastdiv = true;                                // reciprocal path needs normal, moderate factors
+    for (int s = 0; s < S; s++) if (!(nf[s] >= 1e-30 && nf[s] <= 1e30)) fastdiv = false;
+    auto kfn = fastdiv ? k_ttest_rows<true> : k_ttest_rows<false>;
+    DK_CUDA(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     uint32_t nch = (uint32_t)m->n_chunks;
     if (nch) {
         unsigned grid = (nch + (TT_THREADS / DK_CH) - 1) / (TT_THREADS / DK_CH);
-        k_ttest_rows<<<grid, TT_THREADS, smem, st>>>(m->cnts, m->order, m->lbase, nch, S, t->nf_dev, t->idx_dev, nA, nB,
+        kfn<<<grid, TT_THREADS, smem, st>>>(m->cnts, m->order, m->lbase, nch, S, t->nf_dev, t->idx_dev, nA, nB,
                                                      t->p_raw, t->log2fc, (unsigned long long *)(t->tie_counts + 2));
         DK_LAUNCHED(ctx);
     }
