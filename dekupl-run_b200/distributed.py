@@ -120,9 +120,18 @@ def run_sharded(backend, key_ptrs, cnt_ptrs, n, r, a, idxA, idxB, pmax, fmin, nf
     S = len(key_ptrs)
     nf = torch.zeros(S, dtype=torch.float64, device=device)
     if nf_mode == "reference":
+        ok = torch.ones(1, dtype=torch.int64, device=device)
         if rank == 0:
             v, info = backend.nf_reference(nf_step)
             nf = torch.tensor(v, dtype=torch.float64, device=device)
+            # computeNF.c:138-168 consumes a PREFIX of the sorted matrix; rank 0 can answer alone only if the
+            # early stop fired inside its shard (rows consumed < its rows). Otherwise the reference would have
+            # read rows owned by later ranks: refuse loudly instead of returning a different NF.
+            if world > 1 and not (int(info["consumed"]) < R_loc):
+                ok[0] = 0
+        dist.broadcast(ok, src=0)
+        if int(ok.item()) == 0:
+            raise RuntimeError("reference-mode NF did not stop inside rank 0's shard; use nf_mode='full' or fewer shards")
         dist.broadcast(nf, src=0)
         nf = nf.cpu().numpy()
     else:
