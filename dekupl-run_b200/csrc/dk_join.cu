@@ -538,12 +538,16 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
         DK_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
         cudaError_t e;
         if (which == 3) {
-            e = cudaFuncSetAttribute(k_merge3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G3.smem_bytes);
+            typedef void (*m3_fn)(MergeParams, M3Cfg, uint32_t *);
+            static const m3_fn m3_tab[9] = {k_merge3<0>, k_merge3<1>, k_merge3<2>, k_merge3<3>, k_merge3<4>,
+                                            k_merge3<5>, k_merge3<6>, k_merge3<7>, k_merge3<8>};
+            const m3_fn k3 = m3_tab[G3.levels];
+            e = cudaFuncSetAttribute(k3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G3.smem_bytes);
             if (e == cudaSuccess) {
                 int per_sm = (int)((budget + 1024) / ((size_t)G3.smem_bytes + 1024));
                 if (per_sm < 1) per_sm = 1;
                 if (per_sm > 2) per_sm = 2;
-                k_merge3<<<ctx->sm_count * per_sm, M3_NT, G3.smem_bytes, ctx->stream>>>(P, G3, overflow_d);
+                k3<<<ctx->sm_count * per_sm, M3_NT, G3.smem_bytes, ctx->stream>>>(P, G3, overflow_d);
                 e = cudaGetLastError();
             }
         } else if (which == 2) {

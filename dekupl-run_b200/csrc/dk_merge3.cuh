@@ -72,6 +72,7 @@ __device__ __forceinline__ unsigned long long m3_warp_min(unsigned long long v)
     return v;
 }
 
+template <int LV>
 __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uint32_t *overflow)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -83,7 +84,8 @@ __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uin
     M3Small &sm = *reinterpret_cast<M3Small *>(smem_raw + G.off_small);
 
     const int S = G.S, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int caps = G.caps, ks = G.ks;
+    // geometry is compile-time per level count: S_pad = 2^LV runs of caps words, TPS threads per run in the pack pass
+    constexpr int SP = 1 << LV, caps = M3_TP >> LV, ks = (caps + 4 + 3) & ~3, TPSL = 8 - LV, TPS = 1 << TPSL;
     const uint32_t npart = *P.npart;
     const uint32_t bar = smem_u32(&sm.bar);
     const bool owner = tid < S;
@@ -173,7 +175,7 @@ __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uin
                 n = a;
                 if (n) atomicAdd(&sm.total_real, n);
             }
-            if (tid < G.S_pad) { sm.lo[tid] = (uint16_t)lo; sm.n[tid] = (uint16_t)n; }
+            if (tid < SP) { sm.lo[tid] = (uint16_t)lo; sm.n[tid] = (uint16_t)n; }
             __syncthreads();
             const uint32_t T = sm.total_real;
             if (T == 0) {                                          // >= caps copies of one k-mer inside a dump
@@ -182,14 +184,14 @@ __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uin
             }
             // R3: pack (key,dup,slot) words into the level-0 runs
             {
-                const int s = tid >> G.tps_log2, sub = tid & ((1 << G.tps_log2) - 1), tps = 1 << G.tps_log2;
+                const int s = tid >> TPSL, sub = tid & (TPS - 1);
                 const uint32_t slo = sm.lo[s], sn = sm.n[s];
                 const unsigned long long *kw = bufK + (size_t)s * ks + slo;
                 unsigned long long *run = bufA + (size_t)s * (caps + 1);
                 const uint32_t slot0 = (uint32_t)s * ks + slo;
-#pragma unroll 1
+#pragma unroll
                 for (int k = 0; k < M3_VT; k++) {
-                    const uint32_t i = (uint32_t)(sub + k * tps);
+                    const uint32_t i = (uint32_t)(sub + k * TPS);
                     unsigned long long w = M3_PAD;
                     if (i < sn) {
                         const unsigned long long key = kw[i];
@@ -209,9 +211,10 @@ __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uin
             // R4: merge tree
             unsigned long long *X = bufA, *Y = bufK;
             {
-                int len = caps;
-                for (int l = 0; l < G.levels; l++) {
-                    const int sh = G.tps_log2 + 1 + l;
+#pragma unroll
+                for (int l = 0; l < LV; l++) {
+                    const int len = caps << l;
+                    const int sh = TPSL + 1 + l;
                     const int pair = tid >> sh;
                     const int d = (tid & ((1 << sh) - 1)) * M3_VT;
                     const unsigned long long *a_base = X + (size_t)(2 * pair) * (len + 1);
@@ -233,7 +236,6 @@ __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uin
                     if (d + M3_VT == 2 * len) out[M3_VT] = M3_GUARD;
                     __syncthreads();
                     unsigned long long *t = X; X = Y; Y = t;
-                    len *= 2;
                 }
             }
             // R5: rows. X = merged words (T real, then PAD); Y is free: rowab u16[TP+1], orow u16[TP]
@@ -267,19 +269,21 @@ __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uin
                 if (tid == M3_NT - 1) rowab[nrows] = (uint16_t)(tot1 & 0xffffu);
             }
             __syncthreads();
+            // verdicts: rows are dealt out in blocks of RPT = ceil(nrows/NT) per thread (nrows is usually << TP)
+            const uint32_t RPT = (nrows + M3_NT - 1) / M3_NT, rb = (uint32_t)tid * RPT;
             uint32_t passmask = 0;
-#pragma unroll
-            for (int i = 0; i < M3_VT; i++) {
-                const uint32_t r = j0 + i;
-                if (r < nrows && (int)(rowab[r + 1] - rowab[r]) >= min_rec) passmask |= 1u << i;           // joinCounts.c:104
+            if (rb < nrows) {
+                uint32_t prev = rowab[rb];
+                for (uint32_t i = 0; i < RPT && rb + i < nrows; i++) {
+                    const uint32_t cur_ab = rowab[rb + i + 1];
+                    if ((int)(cur_ab - prev) >= min_rec) passmask |= 1u << i;                              // joinCounts.c:104
+                    prev = cur_ab;
+                }
             }
             uint32_t nout;
             const uint32_t obase = m3_block_excl_scan(__popc(passmask), sm, nout);
-#pragma unroll
-            for (int i = 0; i < M3_VT; i++) {
-                const uint32_t r = j0 + i;
-                if (r < nrows) orow[r] = ((passmask >> i) & 1u) ? (uint16_t)(obase + __popc(passmask & ((1u << i) - 1u))) : (uint16_t)0xFFFFu;
-            }
+            for (uint32_t i = 0; i < RPT && rb + i < nrows; i++)
+                orow[rb + i] = ((passmask >> i) & 1u) ? (uint16_t)(obase + __popc(passmask & ((1u << i) - 1u))) : (uint16_t)0xFFFFu;
             // chunk allocation for nout rows appended to the partition's chunk sequence
             if (tid == 0) {
                 const uint32_t have = (sm.chunk_cur != CHUNK_NONE) ? 1u : 0u;
@@ -309,17 +313,21 @@ __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uin
                         for (uint32_t i = tid; i < n4; i += M3_NT) z[i] = make_int4(0, 0, 0, 0);
                     }
                     __syncthreads();
+                    {   // one pass over this thread's entries: row id by running head count, verdict by orow[]
+                        const uint32_t nreal = T > j0 ? (T - j0 < (uint32_t)M3_VT ? T - j0 : (uint32_t)M3_VT) : 0u;
+                        const uint32_t *Xlo = reinterpret_cast<const uint32_t *>(X);
+                        uint32_t r = rowbase - 1u;
 #pragma unroll
-                    for (int i = 0; i < M3_VT; i++) {
-                        if (j0 + i < T) {
-                            const uint32_t r = rowbase + __popc(headmask & ((2u << i) - 1u)) - 1u;
-                            const uint32_t o = (uint32_t)orow[r] - b0;
-                            if (o < nbr) {
-                                const unsigned long long w = X[j0 + i];
-                                const uint32_t slot = (uint32_t)w & ((1u << M3_SB) - 1u);
-                                const uint32_t s = __umulhi(slot, G.divKS);
-                                rowbuf[o * (uint32_t)S + s] = bufC[slot];
-                                if ((headmask >> i) & 1u) keybuf[o] = base + (w >> M3_KSH);
+                        for (int i = 0; i < M3_VT; i++) {
+                            const uint32_t hd = (headmask >> i) & 1u;
+                            r += hd;
+                            if ((uint32_t)i < nreal) {
+                                const uint32_t o = (uint32_t)orow[r] - b0;
+                                if (o < nbr) {
+                                    const uint32_t slot = Xlo[2 * (j0 + i)] & ((1u << M3_SB) - 1u);
+                                    rowbuf[o * (uint32_t)S + slot / (uint32_t)ks] = bufC[slot];
+                                    if (hd) keybuf[o] = base + (X[j0 + i] >> M3_KSH);
+                                }
                             }
                         }
                     }
