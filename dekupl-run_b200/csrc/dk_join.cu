@@ -546,7 +546,7 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
             if (e == cudaSuccess) {
                 int per_sm = (int)((budget + 1024) / ((size_t)G3.smem_bytes + 1024));
                 if (per_sm < 1) per_sm = 1;
-                if (per_sm > 2) per_sm = 2;
+                if (per_sm > 3) per_sm = 3;
                 k3<<<ctx->sm_count * per_sm, M3_NT, G3.smem_bytes, ctx->stream>>>(P, G3, overflow_d);
                 e = cudaGetLastError();
             }

@@ -4,31 +4,38 @@
 // r01b ncu of v2 (profiles/r01b_ncu_merge_v2.csv): a thread-sequential 16-way merge keeps only
 // 13 of 32 lanes busy (key ranges hold very different numbers of rows) and pays O(S) per row.
 // v3 has no data-dependent trip counts at all. A CTA walks its partition in ROUNDS:
-//   R0  every sample contributes a window of <= caps records (+1 look-ahead), staged by 1-D TMA bulk
-//       copies (cp.async.bulk + mbarrier complete_tx) into bufK / bufC;
+//   R0  every sample contributes a window of <= caps keys (+1 look-ahead), staged by 1-D TMA bulk
+//       copies (cp.async.bulk + mbarrier complete_tx) into bufK; the matching count window is only
+//       pulled into L2 (cp.async.bulk.prefetch.L2) — counts never occupy shared memory, which is what
+//       lets three CTAs share an SM;
 //   R1  pivot = smallest look-ahead key, so every key < pivot is complete in the staged windows;
-//   R2  each staged record becomes ONE 64-bit word  (key - base) << 15 | dup << 13 | slot  — order
-//       by word == order by (key, copy index inside the dump, sample); slot addresses the count in
-//       bufC; the round's key span is clipped to 2^49 so the word is exact (never lossy);
+//   R2  each staged record becomes ONE 64-bit word  (key - base) << 16 | dup << 14 | ab << 13 | slot:
+//       order by word == order by (key, copy index inside the dump, ...); ab = (count >= a) is read
+//       from global memory with consecutive lanes on consecutive records; slot addresses the record;
+//       the round's key span is clipped to 2^48 so the word is exact (never lossy);
 //   R3  log2(S_pad) merge levels, ping-pong between two buffers: every thread finds its diagonal
 //       by merge-path binary search and emits exactly 17 words (odd => conflict-free blocked stores);
 //       runs are padded with PAD and fenced with GUARD words so the serial merge needs no bounds checks;
-//   R4  rows = runs of equal (key,dup): head flags + block scan give row ids, a scan of the
-//       (count >= a) flags gives each row's recurrence (joinCounts.c:81-83), a scan of the verdicts
-//       (rec >= r, :104) gives in-order output slots;
-//   R5  surviving rows are assembled in shared memory (zero-filled, one 4-byte store per record) and
-//       copied out with coalesced 128-bit stores into the matrix chunks.
+//   R4  rows = runs of equal (key,dup): head flags + block scan give row ids, the scan of the ab bits
+//       gives each row's recurrence (joinCounts.c:81-83), a scan of the verdicts (rec >= r, :104) gives
+//       in-order output slots;
+//   R5  surviving rows are assembled in the merge buffer that is free after the last level (zero-filled,
+//       one 4-byte count per record re-read from L2) and copied out with coalesced 128-bit stores.
 // Duplicate k-mers inside one dump become consecutive rows exactly like the reference; more than
 // 4 copies of one k-mer in one dump (never produced by jellyfish) raise the overflow flag and the
 // host reruns the join with the v1 kernel.
+// r01d ncu: the kernel is bound by the shared-memory data pipe (68% of peak wavefronts, half of them
+// bank conflicts of the per-lane LDS.64 in the merge-path search and the serial merge), not by HBM.
 #pragma once
 
 #define M3_NT 256
 #define M3_VT 17
 #define M3_TP (M3_NT * M3_VT)      // 4352 word slots per round
 #define M3_SB 13                   // slot bits (slot < S_pad*ks < 8192)
-#define M3_DB 2                    // copy-index bits
-#define M3_KSH (M3_SB + M3_DB)
+#define M3_ABB M3_SB               // bit 13: count >= min_abund (the verdict needs no second look at the count)
+#define M3_DSH (M3_SB + 1)         // bits 14..15: copy index inside the dump
+#define M3_DB 2
+#define M3_KSH (M3_DSH + M3_DB)    // key - base above bit 16
 #define M3_PAD 0xFFFFFFFFFFFFFFFEull
 #define M3_GUARD 0xFFFFFFFFFFFFFFFFull
 #define M3_SPAN ((1ull << (64 - M3_KSH)) - 1ull)   // consumable keys: key - base < M3_SPAN
@@ -36,7 +43,7 @@
 struct M3Cfg {
     int S, S_pad, caps, ks, levels, tps_log2, BR, S4;
     uint32_t divKS, divS, divS4;                  // ceil(2^32 / x): exact floor(q/x) for q < 2^16
-    uint32_t off_A, off_C, off_rowbuf, off_keybuf, off_small, smem_bytes;
+    uint32_t off_A, off_small, yoff_rowbuf, yoff_keybuf, smem_bytes;
 };
 
 struct M3Small {
@@ -46,7 +53,13 @@ struct M3Small {
     uint32_t part, total_real, any;
     uint32_t chunk_cur, rowpos, seq, newbase, nnew, have_cur;
     uint32_t prow, puni;
-    uint16_t lo[256], n[256];
+};
+// per-sample round state, sized by the padded sample count (follows M3Small in shared memory)
+template <int SP>
+struct M3Samp {
+    unsigned long long a0[SP];        // aligned window start (record index) of the staged keys
+    const int32_t *cptr[SP];          // count arrays stay in global memory / L2
+    uint16_t lo[SP], n[SP];
 };
 
 __device__ __forceinline__ uint32_t m3_block_excl_scan(uint32_t v, M3Small &sm, uint32_t &total)
@@ -73,19 +86,17 @@ __device__ __forceinline__ unsigned long long m3_warp_min(unsigned long long v)
 }
 
 template <int LV>
-__global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uint32_t *overflow)
+__global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uint32_t *overflow)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     unsigned long long *bufK = reinterpret_cast<unsigned long long *>(smem_raw);                 // staging keys / merge buffer B
     unsigned long long *bufA = reinterpret_cast<unsigned long long *>(smem_raw + G.off_A);
-    int32_t *bufC = reinterpret_cast<int32_t *>(smem_raw + G.off_C);
-    int32_t *rowbuf = reinterpret_cast<int32_t *>(smem_raw + G.off_rowbuf);
-    unsigned long long *keybuf = reinterpret_cast<unsigned long long *>(smem_raw + G.off_keybuf);
     M3Small &sm = *reinterpret_cast<M3Small *>(smem_raw + G.off_small);
 
     const int S = G.S, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // geometry is compile-time per level count: S_pad = 2^LV runs of caps words, TPS threads per run in the pack pass
     constexpr int SP = 1 << LV, caps = M3_TP >> LV, ks = (caps + 4 + 3) & ~3, TPSL = 8 - LV, TPS = 1 << TPSL;
+    M3Samp<SP> &ss = *reinterpret_cast<M3Samp<SP> *>(smem_raw + G.off_small + sizeof(M3Small));
     const uint32_t npart = *P.npart;
     const uint32_t bar = smem_u32(&sm.bar);
     const bool owner = tid < S;
@@ -97,6 +108,7 @@ __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uin
     const uint64_t *ksrc = owner ? P.T.keys[tid] : nullptr;
     const int32_t *csrc = owner ? P.T.cnts[tid] : nullptr;
     const unsigned long long nsrc = owner ? P.T.n[tid] : 0ull;
+    if (tid < SP) ss.cptr[tid] = csrc;
     __syncthreads();
     uint32_t phase = 0;
     const int min_ab = P.min_abund, min_rec = P.min_rec;
@@ -129,14 +141,15 @@ __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uin
                     if (mend > nsrc) mend = nsrc;
                 }
                 unsigned long long *kd = bufK + (size_t)tid * ks;
-                int32_t *cd = bufC + (size_t)tid * ks;
+                ss.a0[tid] = a0;
                 if (tq) {
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // earlier generic accesses precede the async writes
-                    mbar_expect_tx(bar, tq * 48u);
+                    mbar_expect_tx(bar, tq * 32u);
                     tma_bulk_g2s(smem_u32(kd), ksrc + a0, tq * 32u, bar);
-                    tma_bulk_g2s(smem_u32(cd), csrc + a0, tq * 16u, bar);
+                    // the counts are not staged: pull their window into L2 now, the pack pass reads it coalesced
+                    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(csrc + a0), "r"(tq * 16u) : "memory");
                 } else mbar_arrive(bar);
-                for (unsigned long long g = a0 + 4ull * tq; g < mend; g++) { kd[g - a0] = ksrc[g]; cd[g - a0] = csrc[g]; }   // array tail (< 4 records)
+                for (unsigned long long g = a0 + 4ull * tq; g < mend; g++) kd[g - a0] = ksrc[g];   // array tail (< 4 records)
             }
             mbar_wait(bar, phase);
             phase ^= 1u;
@@ -175,7 +188,7 @@ __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uin
                 n = a;
                 if (n) atomicAdd(&sm.total_real, n);
             }
-            if (tid < SP) { sm.lo[tid] = (uint16_t)lo; sm.n[tid] = (uint16_t)n; }
+            if (tid < SP) { ss.lo[tid] = (uint16_t)lo; ss.n[tid] = (uint16_t)n; }
             __syncthreads();
             const uint32_t T = sm.total_real;
             if (T == 0) {                                          // >= caps copies of one k-mer inside a dump
@@ -185,10 +198,20 @@ __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uin
             // R3: pack (key,dup,slot) words into the level-0 runs
             {
                 const int s = tid >> TPSL, sub = tid & (TPS - 1);
-                const uint32_t slo = sm.lo[s], sn = sm.n[s];
+                const uint32_t slo = ss.lo[s], sn = ss.n[s];
                 const unsigned long long *kw = bufK + (size_t)s * ks + slo;
                 unsigned long long *run = bufA + (size_t)s * (caps + 1);
                 const uint32_t slot0 = (uint32_t)s * ks + slo;
+                // counts straight from global memory (L2-prefetched in R0), consecutive lanes -> consecutive records
+                uint32_t abm = 0;
+                {
+                    const int32_t *cp = ss.cptr[s] + (ss.a0[s] + slo);
+#pragma unroll
+                    for (int k = 0; k < M3_VT; k++) {
+                        const uint32_t i = (uint32_t)(sub + k * TPS);
+                        if (i < sn && __ldg(cp + i) >= min_ab) abm |= 1u << k;                              // joinCounts.c:81-83
+                    }
+                }
 #pragma unroll
                 for (int k = 0; k < M3_VT; k++) {
                     const uint32_t i = (uint32_t)(sub + k * TPS);
@@ -201,7 +224,8 @@ __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uin
                             while (d < i && kw[i - 1 - d] == key) d++;
                             if (d > 3) { atomicExch(overflow, 1u); d = 3; }
                         }
-                        w = ((key - base) << M3_KSH) | ((unsigned long long)d << M3_SB) | (unsigned long long)(slot0 + i);
+                        w = ((key - base) << M3_KSH) | ((unsigned long long)d << M3_DSH) | (unsigned long long)(((abm >> k) & 1u) << M3_ABB) |
+                            (unsigned long long)(slot0 + i);
                     }
                     run[i] = w;
                 }
@@ -241,18 +265,20 @@ __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uin
             // R5: rows. X = merged words (T real, then PAD); Y is free: rowab u16[TP+1], orow u16[TP]
             uint16_t *rowab = reinterpret_cast<uint16_t *>(Y);
             uint16_t *orow = rowab + (M3_TP + 8);
+            int32_t *rowbuf = reinterpret_cast<int32_t *>(reinterpret_cast<unsigned char *>(Y) + G.yoff_rowbuf);
+            unsigned long long *keybuf = reinterpret_cast<unsigned long long *>(reinterpret_cast<unsigned char *>(Y) + G.yoff_keybuf);
             const uint32_t j0 = (uint32_t)tid * M3_VT;
             uint32_t headmask = 0, abmask = 0;
             {
-                unsigned long long prevkp = (tid == 0) ? ~0ull : (X[j0 - 1] >> M3_SB);
+                unsigned long long prevkp = (tid == 0) ? ~0ull : (X[j0 - 1] >> M3_DSH);
 #pragma unroll
                 for (int i = 0; i < M3_VT; i++) {
                     const unsigned long long w = X[j0 + i];
                     const bool real = w < M3_PAD;
-                    const unsigned long long kp = w >> M3_SB;
+                    const unsigned long long kp = w >> M3_DSH;
                     if (real && kp != prevkp) headmask |= 1u << i;
                     prevkp = kp;
-                    if (real && bufC[(uint32_t)w & ((1u << M3_SB) - 1u)] >= min_ab) abmask |= 1u << i;      // joinCounts.c:81-83
+                    if (real && (((uint32_t)w >> M3_ABB) & 1u)) abmask |= 1u << i;
                 }
             }
             uint32_t tot1;
@@ -325,7 +351,8 @@ __global__ void __launch_bounds__(M3_NT, 2) k_merge3(MergeParams P, M3Cfg G, uin
                                 const uint32_t o = (uint32_t)orow[r] - b0;
                                 if (o < nbr) {
                                     const uint32_t slot = Xlo[2 * (j0 + i)] & ((1u << M3_SB) - 1u);
-                                    rowbuf[o * (uint32_t)S + slot / (uint32_t)ks] = bufC[slot];
+                                    const uint32_t s = slot / (uint32_t)ks;
+                                    rowbuf[o * (uint32_t)S + s] = __ldg(ss.cptr[s] + (ss.a0[s] + (slot - s * (uint32_t)ks)));   // L2 hit
                                     if (hd) keybuf[o] = base + (X[j0 + i] >> M3_KSH);
                                 }
                             }
@@ -398,17 +425,19 @@ static bool m3_make_cfg(int S, size_t smem_budget, M3Cfg &G)
     G.divKS = cdiv32((uint32_t)G.ks); G.divS = cdiv32((uint32_t)S); G.divS4 = G.S4 ? cdiv32((uint32_t)G.S4) : 0;
     size_t bK = (size_t)sp * G.ks * 8, bM = (size_t)(M3_TP + sp) * 8;
     if (bK < bM) bK = bM;
-    if (bK < 2 * (size_t)(M3_TP + 8) * 2 + 64) return false;
+    // the merge buffer that is free after the last level also holds rowab/orow (u16 x TP each), the row
+    // assembly buffer (BR rows x S counts) and BR keys
+    const size_t yrow = dk_round_up((size_t)(M3_TP + 8) * 2 * 2, 16);
+    if (bM < yrow + 64) return false;
+    int BR = (int)((bM - yrow - 32) / ((size_t)4 * S + 8));
+    if (BR > 256) BR = 256;
+    if (BR < 4) return false;
+    G.BR = BR;
+    G.yoff_rowbuf = (uint32_t)yrow;
+    G.yoff_keybuf = (uint32_t)(yrow + dk_round_up((size_t)BR * S * 4, 16));
     size_t off = dk_round_up(bK, 128);
     G.off_A = (uint32_t)off; off += dk_round_up(bM, 128);
-    G.off_C = (uint32_t)off; off += dk_round_up((size_t)sp * G.ks * 4, 128);
-    int BR = 16384 / (4 * S);
-    if (BR > 256) BR = 256;
-    if (BR < 8) BR = 8;
-    G.BR = BR;
-    G.off_rowbuf = (uint32_t)off; off += dk_round_up((size_t)BR * S * 4 + 16, 128);
-    G.off_keybuf = (uint32_t)off; off += dk_round_up((size_t)BR * 8, 128);
-    G.off_small = (uint32_t)off; off += dk_round_up(sizeof(M3Small), 128);
+    G.off_small = (uint32_t)off; off += dk_round_up(sizeof(M3Small) + (size_t)sp * 20 + 16, 128);
     G.smem_bytes = (uint32_t)off;
     return off <= smem_budget;
 }
