@@ -57,9 +57,9 @@ struct M3Small {
 // per-sample round state, sized by the padded sample count (follows M3Small in shared memory)
 template <int SP>
 struct M3Samp {
-    unsigned long long a0[SP];        // aligned window start (record index) of the staged keys
+    unsigned long long cur[SP], endg[SP];   // cursor / partition end of every dump (record indices)
     const int32_t *cptr[SP];          // count arrays stay in global memory / L2
-    uint16_t lo[SP], n[SP];
+    uint16_t n[SP];
 };
 
 __device__ __forceinline__ uint32_t m3_block_excl_scan(uint32_t v, M3Small &sm, uint32_t &total)
@@ -120,6 +120,8 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
         if (part >= npart) break;
         unsigned long long cur = 0, endg = 0;
         if (owner) { cur = P.starts[(size_t)part * S + tid]; endg = P.starts[(size_t)(part + 1) * S + tid]; }
+        if (tid < SP) { ss.cur[tid] = cur; ss.endg[tid] = endg; }
+        __syncthreads();
         if (tid == 0) { sm.chunk_cur = CHUNK_NONE; sm.rowpos = 0; sm.seq = 0; sm.prow = 0; sm.puni = 0; }
 
         for (;;) {   // ---- rounds
@@ -141,15 +143,27 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
                     if (mend > nsrc) mend = nsrc;
                 }
                 unsigned long long *kd = bufK + (size_t)tid * ks;
-                ss.a0[tid] = a0;
                 if (tq) {
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // earlier generic accesses precede the async writes
                     mbar_expect_tx(bar, tq * 32u);
                     tma_bulk_g2s(smem_u32(kd), ksrc + a0, tq * 32u, bar);
-                    // the counts are not staged: pull their window into L2 now, the pack pass reads it coalesced
-                    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(csrc + a0), "r"(tq * 16u) : "memory");
                 } else mbar_arrive(bar);
                 for (unsigned long long g = a0 + 4ull * tq; g < mend; g++) kd[g - a0] = ksrc[g];   // array tail (< 4 records)
+            }
+            // counts are never staged: while the key windows are in flight every thread reads the counts of the
+            // records it will pack (consecutive lanes -> consecutive records) and keeps only the (count >= a) bits
+            const int ps = tid >> TPSL, psub = tid & (TPS - 1);
+            const unsigned long long pcur = ss.cur[ps];
+            uint32_t abm = 0;
+            {
+                const unsigned long long pleft = ss.endg[ps] - pcur;
+                const uint32_t pL = (uint32_t)(pleft < (unsigned long long)caps ? pleft : (unsigned long long)caps);
+                const int32_t *cp = ss.cptr[ps] + pcur;
+#pragma unroll
+                for (int k = 0; k < M3_VT; k++) {
+                    const uint32_t i = (uint32_t)(psub + k * TPS);
+                    if (i < pL && __ldg(cp + i) >= min_ab) abm |= 1u << k;                                  // joinCounts.c:81-83
+                }
             }
             mbar_wait(bar, phase);
             phase ^= 1u;
@@ -188,7 +202,7 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
                 n = a;
                 if (n) atomicAdd(&sm.total_real, n);
             }
-            if (tid < SP) { ss.lo[tid] = (uint16_t)lo; ss.n[tid] = (uint16_t)n; }
+            if (tid < SP) ss.n[tid] = (uint16_t)n;
             __syncthreads();
             const uint32_t T = sm.total_real;
             if (T == 0) {                                          // >= caps copies of one k-mer inside a dump
@@ -197,21 +211,11 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
             }
             // R3: pack (key,dup,slot) words into the level-0 runs
             {
-                const int s = tid >> TPSL, sub = tid & (TPS - 1);
-                const uint32_t slo = ss.lo[s], sn = ss.n[s];
+                const int s = ps, sub = psub;
+                const uint32_t slo = (uint32_t)pcur & 3u, sn = ss.n[s];
                 const unsigned long long *kw = bufK + (size_t)s * ks + slo;
                 unsigned long long *run = bufA + (size_t)s * (caps + 1);
                 const uint32_t slot0 = (uint32_t)s * ks + slo;
-                // counts straight from global memory (L2-prefetched in R0), consecutive lanes -> consecutive records
-                uint32_t abm = 0;
-                {
-                    const int32_t *cp = ss.cptr[s] + (ss.a0[s] + slo);
-#pragma unroll
-                    for (int k = 0; k < M3_VT; k++) {
-                        const uint32_t i = (uint32_t)(sub + k * TPS);
-                        if (i < sn && __ldg(cp + i) >= min_ab) abm |= 1u << k;                              // joinCounts.c:81-83
-                    }
-                }
 #pragma unroll
                 for (int k = 0; k < M3_VT; k++) {
                     const uint32_t i = (uint32_t)(sub + k * TPS);
@@ -352,7 +356,7 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
                                 if (o < nbr) {
                                     const uint32_t slot = Xlo[2 * (j0 + i)] & ((1u << M3_SB) - 1u);
                                     const uint32_t s = slot / (uint32_t)ks;
-                                    rowbuf[o * (uint32_t)S + s] = __ldg(ss.cptr[s] + (ss.a0[s] + (slot - s * (uint32_t)ks)));   // L2 hit
+                                    rowbuf[o * (uint32_t)S + s] = __ldg(ss.cptr[s] + ((ss.cur[s] & ~3ull) + (slot - s * (uint32_t)ks)));   // L2 hit
                                     if (hd) keybuf[o] = base + (X[j0 + i] >> M3_KSH);
                                 }
                             }
@@ -387,6 +391,7 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
             }
             // R7: advance the partition state
             cur += n;
+            if (tid < SP) ss.cur[tid] = cur;                     // read again only after the barrier below
             if (tid == 0) {
                 const uint32_t v = (sm.have_cur ? sm.rowpos : 0u) + nout;
                 if (sm.nnew) {
@@ -437,7 +442,7 @@ static bool m3_make_cfg(int S, size_t smem_budget, M3Cfg &G)
     G.yoff_keybuf = (uint32_t)(yrow + dk_round_up((size_t)BR * S * 4, 16));
     size_t off = dk_round_up(bK, 128);
     G.off_A = (uint32_t)off; off += dk_round_up(bM, 128);
-    G.off_small = (uint32_t)off; off += dk_round_up(sizeof(M3Small) + (size_t)sp * 20 + 16, 128);
+    G.off_small = (uint32_t)off; off += dk_round_up(sizeof(M3Small) + (size_t)sp * 26 + 16, 128);
     G.smem_bytes = (uint32_t)off;
     return off <= smem_budget;
 }
