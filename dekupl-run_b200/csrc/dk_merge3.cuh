@@ -5,9 +5,9 @@
 // 13 of 32 lanes busy (key ranges hold very different numbers of rows) and pays O(S) per row.
 // v3 has no data-dependent trip counts at all. A CTA walks its partition in ROUNDS:
 //   R0  every sample contributes a window of <= caps keys (+1 look-ahead), staged by 1-D TMA bulk
-//       copies (cp.async.bulk + mbarrier complete_tx) into bufK; the matching count window is only
-//       pulled into L2 (cp.async.bulk.prefetch.L2) — counts never occupy shared memory, which is what
-//       lets three CTAs share an SM;
+//       copies (cp.async.bulk + mbarrier complete_tx) into bufK; counts never occupy shared memory
+//       (which is what lets three CTAs share an SM): while the key copies are in flight every thread
+//       reads the counts of the records it will pack and keeps only the (count >= a) bits;
 //   R1  pivot = smallest look-ahead key, so every key < pivot is complete in the staged windows;
 //   R2  each staged record becomes ONE 64-bit word  (key - base) << 16 | dup << 14 | ab << 13 | slot:
 //       order by word == order by (key, copy index inside the dump, ...); ab = (count >= a) is read
