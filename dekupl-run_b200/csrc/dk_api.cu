@@ -34,11 +34,139 @@ static int upload_dumps(dk_ctx *ctx, int S, const uint64_t *const *keys, const i
     return DK_OK;
 }
 
+// ---- pipelined host join ------------------------------------------------------------
+// Large host inputs are cut into key-range slices (rows are independent across key ranges): while slice c
+// is merged on the compute stream, slice c+1 is copied host->device on a second stream into the other half
+// of a double buffer. The per-slice matrices are then spliced into one (chunk tables re-based; reference
+// order == slice order). The H2D copy of 12 B/record is the floor of this entry point; the merge hides under it.
+__global__ void k_concat_tables(const uint32_t *order_c, const uint64_t *lbase_c, uint32_t nch, uint32_t chunk_base,
+                                uint32_t pos_base, uint64_t row_base, uint32_t *order, uint64_t *lbase, int last)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nch) { order[pos_base + i] = order_c[i] + chunk_base; lbase[pos_base + i] = lbase_c[i] + row_base; }
+    if (last && i == 0) lbase[pos_base + nch] = lbase_c[nch] + row_base;
+}
+
+static int concat_matrices(dk_ctx *ctx, std::vector<dk_matrix *> &parts, dk_matrix **out)
+{
+    cudaStream_t st = ctx->stream;
+    const int S = parts[0]->S;
+    uint64_t nch = 0, R = 0, U = 0;
+    for (auto *p : parts) { nch += p->n_chunks; R += p->R; U += p->U; }
+    if (nch >= 0xFFFFFFF0ull) return dk_fail(ctx, DK_ERR_NOMEM, "join: too many chunks");
+    dk_matrix *m = new dk_matrix();
+    m->S = S; m->R = R; m->U = U; m->n_chunks = nch; m->cap_chunks = nch + 1;
+    m->keys = (uint64_t *)dk_dev_alloc(ctx, 8 * m->cap_chunks * DK_CH);
+    m->cnts = (int32_t *)dk_dev_alloc(ctx, 4 * m->cap_chunks * DK_CH * S);
+    m->chunk_rows = (uint32_t *)dk_dev_alloc(ctx, 4 * m->cap_chunks);
+    m->order = (uint32_t *)dk_dev_alloc(ctx, 4 * (nch + 2));
+    m->lbase = (uint64_t *)dk_dev_alloc(ctx, 8 * (nch + 3));
+    if (!m->keys || !m->cnts || !m->chunk_rows || !m->order || !m->lbase) { dk_matrix_release(ctx, m); return DK_ERR_NOMEM; }
+    uint64_t cb = 0, rb = 0;
+    for (size_t c = 0; c < parts.size(); c++) {
+        dk_matrix *p = parts[c];
+        const uint32_t n = (uint32_t)p->n_chunks;
+        const int last = (c + 1 == parts.size());
+        if (n) {
+            DK_CUDA(ctx, cudaMemcpyAsync(m->keys + cb * DK_CH, p->keys, 8 * (size_t)n * DK_CH, cudaMemcpyDeviceToDevice, st));
+            DK_CUDA(ctx, cudaMemcpyAsync(m->cnts + cb * DK_CH * S, p->cnts, 4 * (size_t)n * DK_CH * S, cudaMemcpyDeviceToDevice, st));
+            DK_CUDA(ctx, cudaMemcpyAsync(m->chunk_rows + cb, p->chunk_rows, 4 * (size_t)n, cudaMemcpyDeviceToDevice, st));
+        }
+        k_concat_tables<<<(n + 256) / 256, 256, 0, st>>>(p->order, p->lbase, n, (uint32_t)cb, (uint32_t)cb, rb, m->order, m->lbase, last);
+        DK_LAUNCHED(ctx);
+        cb += n; rb += p->R;
+    }
+    DK_CUDA(ctx, cudaStreamSynchronize(st));
+    for (auto *p : parts) dk_matrix_release(ctx, p);
+    parts.clear();
+    *out = m;
+    return DK_OK;
+}
+
+static int join_host_pipelined(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                               int min_rec, int min_abund, int nslices, dk_matrix **out)
+{
+    // slice edges: quantiles of the longest dump; per dump a binary search on the host arrays
+    int big = 0;
+    for (int s = 1; s < S; s++) if (n[s] > n[big]) big = s;
+    std::vector<std::vector<uint64_t>> cut(S, std::vector<uint64_t>(nslices + 1, 0));
+    for (int s = 0; s < S; s++) cut[s][nslices] = n[s];
+    for (int c = 1; c < nslices; c++) {
+        const uint64_t edge = keys[big][n[big] / nslices * c];
+        for (int s = 0; s < S; s++) {
+            uint64_t lo = cut[s][c - 1], hi = n[s];
+            while (lo < hi) { uint64_t mid = (lo + hi) >> 1; if (keys[s][mid] < edge) lo = mid + 1; else hi = mid; }
+            cut[s][c] = lo;
+        }
+    }
+    size_t slab_bytes = 0;
+    for (int c = 0; c < nslices; c++) {
+        size_t b = 0;
+        for (int s = 0; s < S; s++) { uint64_t k = cut[s][c + 1] - cut[s][c]; b += dk_round_up(k * 8 + 16, 256) + dk_round_up(k * 4 + 16, 256); }
+        if (b > slab_bytes) slab_bytes = b;
+    }
+    unsigned char *slab[2] = {(unsigned char *)dk_dev_alloc(ctx, slab_bytes), (unsigned char *)dk_dev_alloc(ctx, slab_bytes)};
+    if (!slab[0] || !slab[1]) { dk_dev_release(ctx, slab[0]); dk_dev_release(ctx, slab[1]); return DK_ERR_NOMEM; }
+    cudaStream_t cs = nullptr;
+    cudaEvent_t up[2] = {nullptr, nullptr};
+    DK_CUDA(ctx, cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+    DK_CUDA(ctx, cudaEventCreateWithFlags(&up[0], cudaEventDisableTiming));
+    DK_CUDA(ctx, cudaEventCreateWithFlags(&up[1], cudaEventDisableTiming));
+    std::vector<std::vector<const uint64_t *>> kd(2, std::vector<const uint64_t *>(S));
+    std::vector<std::vector<const int32_t *>> cd(2, std::vector<const int32_t *>(S));
+    std::vector<uint64_t> nn(S);
+    auto enqueue = [&](int c) -> int {
+        const int b = c & 1;
+        size_t off = 0;
+        for (int s = 0; s < S; s++) {
+            const uint64_t k0 = cut[s][c], k = cut[s][c + 1] - k0;
+            kd[b][s] = (const uint64_t *)(slab[b] + off);
+            if (k) DK_CUDA(ctx, cudaMemcpyAsync(slab[b] + off, keys[s] + k0, k * 8, cudaMemcpyHostToDevice, cs));
+            off += dk_round_up(k * 8 + 16, 256);
+            cd[b][s] = (const int32_t *)(slab[b] + off);
+            if (k) DK_CUDA(ctx, cudaMemcpyAsync(slab[b] + off, cnts[s] + k0, k * 4, cudaMemcpyHostToDevice, cs));
+            off += dk_round_up(k * 4 + 16, 256);
+        }
+        DK_CUDA(ctx, cudaEventRecord(up[b], cs));
+        return DK_OK;
+    };
+    std::vector<dk_matrix *> parts;
+    int rc = enqueue(0);
+    double ms_join = 0, ms_merge = 0;
+    for (int c = 0; c < nslices && rc == DK_OK; c++) {
+        // slice c+1 goes into the other buffer: its previous user (join c-1) has returned, i.e. finished on the device
+        if (c + 1 < nslices) rc = enqueue(c + 1);
+        if (rc != DK_OK) break;
+        if (cudaStreamWaitEvent(ctx->stream, up[c & 1], 0) != cudaSuccess) { rc = dk_fail(ctx, DK_ERR_CUDA, "join: stream wait failed"); break; }
+        for (int s = 0; s < S; s++) nn[s] = cut[s][c + 1] - cut[s][c];
+        dk_matrix *m = nullptr;
+        rc = dk_join_impl(ctx, S, kd[c & 1].data(), cd[c & 1].data(), nn.data(), min_rec, min_abund, 0, &m);
+        if (rc == DK_OK) { parts.push_back(m); ms_join += ctx->stage_ms[0]; ms_merge += ctx->stage_ms[4]; }
+    }
+    cudaStreamSynchronize(cs);
+    cudaStreamSynchronize(ctx->stream);
+    cudaEventDestroy(up[0]); cudaEventDestroy(up[1]); cudaStreamDestroy(cs);
+    dk_dev_release(ctx, slab[0]); dk_dev_release(ctx, slab[1]);
+    if (rc != DK_OK) { for (auto *p : parts) dk_matrix_release(ctx, p); return rc; }
+    rc = concat_matrices(ctx, parts, out);
+    ctx->stage_ms[0] = ms_join; ctx->stage_ms[4] = ms_merge;
+    return rc;
+}
+
 extern "C" int dk_join_counts(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts,
                               const uint64_t *n, int min_rec, int min_abund, int emit_stale_tail, dk_matrix **out)
 {
     if (!ctx || !keys || !cnts || !n) return dk_fail(ctx, DK_ERR_ARG, "join_counts: NULL argument");
     if (S < 1 || S > DK_MAX_SAMPLES) return dk_fail(ctx, DK_ERR_ARG, "join: S=%d outside [1,%d]", S, DK_MAX_SAMPLES);
+    {   // large inputs: overlap the host->device copies with the merge, slice by slice (DK_JOIN_SLICES=1 disables)
+        uint64_t total = 0;
+        for (int s = 0; s < S; s++) total += n[s];
+        int nslices = total >= (64ull << 20) ? 8 : 1;
+        if (const char *e = getenv("DK_JOIN_SLICES")) nslices = atoi(e);
+        if (nslices > 64) nslices = 64;
+        if (nslices > 1 && !emit_stale_tail && total >= (uint64_t)nslices * 1024)
+            return join_host_pipelined(ctx, S, keys, cnts, n, min_rec, min_abund, nslices, out);
+    }
     unsigned char *slab = nullptr;
     std::vector<const uint64_t *> kd(S);
     std::vector<const int32_t *> cd(S);

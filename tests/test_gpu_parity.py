@@ -265,3 +265,25 @@ def test_bh_heavy_ties_and_large(ctx):
     oadj = orc.bh(p)                                          # BH of the GPU's own raw p: isolates K5
     np.testing.assert_allclose(adj, oadj, rtol=1e-15)
     assert len(np.unique(p)) < R // 100
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("S,slices", [(16, 4), (5, 7), (48, 3)])
+def test_join_host_pipelined_slices_equal_single_pass(ctx, S, slices, monkeypatch):
+    """dk_join_counts on host buffers cut into key-range slices (copy/merge overlap) == oracle, including
+    duplicate k-mers sitting exactly on a slice edge and NF / checksum on the spliced matrix"""
+    rng = np.random.default_rng(S * 31 + slices)
+    keys, cnts = random_dumps(rng, S, 40_000, 62, 0.2, 40, p_core=0.3)
+    big = int(np.argmax([len(k) for k in keys]))
+    edge = keys[big][len(keys[big]) // slices]              # the first slice edge: make it a duplicated k-mer elsewhere
+    j = int(np.searchsorted(keys[1], edge))
+    keys[1] = np.insert(keys[1], j, [edge, edge]); cnts[1] = np.insert(cnts[1], j, [7, 9]).astype(np.int32)
+    monkeypatch.setenv("DK_JOIN_SLICES", str(slices))
+    m = ctx.join_counts(keys, cnts, 2, 3)
+    monkeypatch.setenv("DK_JOIN_SLICES", "1")
+    m1 = ctx.join_counts(keys, cnts, 2, 3)
+    gk, gc = m.export()
+    ok, oc, oU = orc.join(keys, cnts, 2, 3)
+    assert m.union == oU and np.array_equal(gk, ok) and np.array_equal(gc, oc)
+    assert m.checksum() == m1.checksum()
+    m.free(); m1.free()
