@@ -367,7 +367,7 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
                         const uint32_t S4 = (uint32_t)G.S4, n4 = nbr * S4;
                         const int4 *src4 = reinterpret_cast<const int4 *>(rowbuf);
                         for (uint32_t i = tid; i < n4; i += M3_NT) {
-                            const uint32_t rr = __umulhi(i, G.divS4), c4 = i - rr * S4;
+                            const uint32_t rr = S4 == 1 ? i : __umulhi(i, G.divS4), c4 = i - rr * S4;   // ceil(2^32/1) does not fit 32 bits
                             const uint32_t v = rp + b0 + rr, k = v / DK_CH, off = v % DK_CH;
                             const uint32_t chunk = (have && k == 0) ? ccur : nb + (k - have);
                             if (chunk < P.max_chunks)
@@ -375,7 +375,7 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
                         }
                     } else {
                         for (uint32_t i = tid; i < words; i += M3_NT) {
-                            const uint32_t rr = __umulhi(i, G.divS), c = i - rr * (uint32_t)S;
+                            const uint32_t rr = S == 1 ? i : __umulhi(i, G.divS), c = i - rr * (uint32_t)S;
                             const uint32_t v = rp + b0 + rr, k = v / DK_CH, off = v % DK_CH;
                             const uint32_t chunk = (have && k == 0) ? ccur : nb + (k - have);
                             if (chunk < P.max_chunks) P.out_cnts[((size_t)chunk * DK_CH + off) * S + c] = rowbuf[i];

@@ -46,6 +46,10 @@ def test_join_reference_binary_goldens(ctx):
     (17, 30000, 0.3, 0.1, 2, 3), (32, 50000, 0.2, 0.2, 3, 2), (33, 40000, 0.2, 0.2, 4, 2),
     (48, 60000, 0.1, 0.2, 4, 5), (64, 30000, 0.1, 0.1, 5, 3), (100, 20000, 0.1, 0.2, 8, 4),
     (200, 12000, 0.08, 0.2, 12, 5), (256, 6000, 0.1, 0.1, 10, 3), (1, 5000, 1.0, 0.0, 1, 3),
+    # many surviving rows per round: output crosses matrix chunks inside one round (S=4 / S=1 once hit a
+    # reciprocal-division overflow there, found by the config-1 real-data fixture)
+    (4, 300000, 0.6, 0.3, 1, 1), (1, 200000, 1.0, 0.0, 1, 1), (2, 250000, 0.7, 0.2, 1, 2), (3, 150000, 0.6, 0.2, 1, 1),
+    (8, 200000, 0.5, 0.3, 1, 1), (12, 150000, 0.3, 0.3, 2, 2),
 ])
 def test_join_random_vs_oracle(ctx, S, n_union, pp, core, r, a):
     rng = np.random.default_rng(S * 1000 + n_union)
