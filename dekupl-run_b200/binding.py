@@ -18,7 +18,8 @@ class DkError(RuntimeError):
 
 
 def lib_path():
-    return os.path.join(_HERE, "libdekupl_b200.so")
+    # DK_LIB: an alternative build of the SAME library (e.g. the -DDK_M3_PROF phase-timing variant)
+    return os.environ.get("DK_LIB") or os.path.join(_HERE, "libdekupl_b200.so")
 
 
 def declared_symbols():

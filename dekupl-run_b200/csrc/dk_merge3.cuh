@@ -85,6 +85,29 @@ __device__ __forceinline__ unsigned long long m3_warp_min(unsigned long long v)
     return v;
 }
 
+// shared-memory loads by 32-bit shared address: the merge path below selects ONE address per step and issues ONE
+// load for the whole warp (two predicated loads would each replay their own bank conflicts), and the binary search
+// probes the high 32-bit halves first (a 32-bit access conflicts on 32 banks, a 64-bit one on 16 bank pairs)
+__device__ __forceinline__ unsigned long long m3_lds64(uint32_t addr)
+{
+    unsigned long long v;
+    asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ uint32_t m3_lds32(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+
+// -DDK_M3_PROF: thread 0 of every CTA accumulates the cycles between phase marks into prof[1..7] (units of 16 cycles)
+#ifdef DK_M3_PROF
+#define M3_MARK(i) do { if (tid == 0) { long long t__ = clock64(); atomicAdd(&prof[i], (uint32_t)((t__ - tprev) >> 4)); tprev = t__; } } while (0)
+#else
+#define M3_MARK(i) do { } while (0)
+#endif
+
 template <int LV>
 __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uint32_t *overflow)
 {
@@ -112,6 +135,10 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
     __syncthreads();
     uint32_t phase = 0;
     const int min_ab = P.min_abund, min_rec = P.min_rec;
+#ifdef DK_M3_PROF
+    uint32_t *prof = overflow + 1;     // scal[4..11]
+    long long tprev = 0;
+#endif
 
     for (;;) {
         if (tid == 0) sm.part = atomicAdd(P.work_counter, 1u);
@@ -125,6 +152,9 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
         if (tid == 0) { sm.chunk_cur = CHUNK_NONE; sm.rowpos = 0; sm.seq = 0; sm.prow = 0; sm.puni = 0; }
 
         for (;;) {   // ---- rounds
+#ifdef DK_M3_PROF
+            if (tid == 0) tprev = clock64();
+#endif
             // R0: stage the windows
             uint32_t lo = 0, L = 0;
             if (tid == 0) { sm.total_real = 0; }
@@ -168,6 +198,7 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
             mbar_wait(bar, phase);
             phase ^= 1u;
             __syncthreads();
+            M3_MARK(1);
             // R1: pivot (smallest look-ahead key) and base (smallest first key)
             unsigned long long candk = DK_SENTINEL, firstk = DK_SENTINEL;
             uint32_t ncm = 0;
@@ -204,6 +235,7 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
             }
             if (tid < SP) ss.n[tid] = (uint16_t)n;
             __syncthreads();
+            M3_MARK(2);
             const uint32_t T = sm.total_real;
             if (T == 0) {                                          // >= caps copies of one k-mer inside a dump
                 if (tid == 0) atomicExch(overflow, 1u);
@@ -236,6 +268,7 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
                 if (sub == 0) run[caps] = M3_GUARD;
             }
             __syncthreads();
+            M3_MARK(3);
             // R4: merge tree
             unsigned long long *X = bufA, *Y = bufK;
             {
@@ -247,25 +280,35 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
                     const int d = (tid & ((1 << sh) - 1)) * M3_VT;
                     const unsigned long long *a_base = X + (size_t)(2 * pair) * (len + 1);
                     const unsigned long long *b_base = a_base + (len + 1);
+                    const uint32_t xa = smem_u32(a_base), xb = smem_u32(b_base);
                     int alo = d > len ? d - len : 0, ahi = d < len ? d : len;
                     while (alo < ahi) {
                         const int mid = (alo + ahi) >> 1;
-                        if (a_base[mid] <= b_base[d - 1 - mid]) alo = mid + 1; else ahi = mid;
+                        const uint32_t qa = xa + 8u * (uint32_t)mid, qb = xb + 8u * (uint32_t)(d - 1 - mid);
+                        const uint32_t ah = m3_lds32(qa + 4u), bh = m3_lds32(qb + 4u);
+                        bool le = ah < bh;
+                        if (ah == bh) le = m3_lds32(qa) <= m3_lds32(qb);
+                        if (le) alo = mid + 1; else ahi = mid;
                     }
-                    int ai = alo, bi = d - alo;
-                    unsigned long long a = a_base[ai], b = b_base[bi];
+                    uint32_t pa = xa + 8u * (uint32_t)alo, pb = xb + 8u * (uint32_t)(d - alo);
+                    unsigned long long a = m3_lds64(pa), b = m3_lds64(pb);
                     unsigned long long *out = Y + (size_t)pair * (2 * len + 1) + d;
 #pragma unroll
                     for (int i = 0; i < M3_VT; i++) {
                         const bool ta = a <= b;
                         out[i] = ta ? a : b;
-                        if (ta) a = a_base[++ai]; else b = b_base[++bi];
+                        pa += ta ? 8u : 0u;
+                        pb += ta ? 0u : 8u;
+                        const unsigned long long v = m3_lds64(ta ? pa : pb);
+                        a = ta ? v : a;
+                        b = ta ? b : v;
                     }
                     if (d + M3_VT == 2 * len) out[M3_VT] = M3_GUARD;
                     __syncthreads();
                     unsigned long long *t = X; X = Y; Y = t;
                 }
             }
+            M3_MARK(4);
             // R5: rows. X = merged words (T real, then PAD); Y is free: rowab u16[TP+1], orow u16[TP]
             uint16_t *rowab = reinterpret_cast<uint16_t *>(Y);
             uint16_t *orow = rowab + (M3_TP + 8);
@@ -299,6 +342,7 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
                 if (tid == M3_NT - 1) rowab[nrows] = (uint16_t)(tot1 & 0xffffu);
             }
             __syncthreads();
+            M3_MARK(5);
             // verdicts: rows are dealt out in blocks of RPT = ceil(nrows/NT) per thread (nrows is usually << TP)
             const uint32_t RPT = (nrows + M3_NT - 1) / M3_NT, rb = (uint32_t)tid * RPT;
             uint32_t passmask = 0;
@@ -330,6 +374,7 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
                 sm.have_cur = have; sm.newbase = nb; sm.nnew = nnew;
             }
             __syncthreads();
+            M3_MARK(6);
             // R6: assemble surviving rows in shared memory, copy out coalesced
             {
                 const uint32_t have = sm.have_cur, nb = sm.newbase, ccur = sm.chunk_cur;
@@ -403,6 +448,7 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
                 sm.prow += nout; sm.puni += nrows;
             }
             __syncthreads();
+            M3_MARK(7);
         }
         __syncthreads();
         if (tid == 0) {
