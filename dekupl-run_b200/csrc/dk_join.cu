@@ -574,12 +574,12 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
         ctx->stage_ms[4] = ms;
 #ifdef DK_M3_PROF
         if (which == 3) {
-            uint32_t pr[8];
+            uint32_t pr[12];
             cudaMemcpy(pr, scal + 4, sizeof pr, cudaMemcpyDeviceToHost);
             double tot = 0;
-            for (int i = 1; i < 8; i++) tot += pr[i];
-            fprintf(stderr, "[m3 prof] kernel %.3f ms; phase shares: stage+wait %.3f pivot %.3f pack %.3f merge %.3f heads %.3f verdict %.3f assemble %.3f\n",
-                    ms, pr[1] / tot, pr[2] / tot, pr[3] / tot, pr[4] / tot, pr[5] / tot, pr[6] / tot, pr[7] / tot);
+            for (int i = 1; i < 11; i++) tot += pr[i];
+            fprintf(stderr, "[m3 prof] kernel %.3f ms; phase shares: stage+wait %.3f pivot %.3f pack %.3f merge %.3f heads %.3f verdict %.3f | zero %.3f scatter %.3f copyout %.3f advance %.3f\n",
+                    ms, pr[1] / tot, pr[2] / tot, pr[3] / tot, pr[4] / tot, pr[5] / tot, pr[6] / tot, pr[8] / tot, pr[9] / tot, pr[10] / tot, pr[7] / tot);
         }
 #endif
         if (h_tot[4] && which == 3) {

@@ -311,7 +311,9 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
             M3_MARK(4);
             // R5: rows. X = merged words (T real, then PAD); Y is free: rowab u16[TP+1], orow u16[TP]
             uint16_t *rowab = reinterpret_cast<uint16_t *>(Y);
-            uint16_t *orow = rowab + (M3_TP + 8);
+            constexpr int ROWAB_N = (M3_TP + 8) > (SP * ks + 8) ? (M3_TP + 8) : (SP * ks + 8);
+            uint16_t *orow = rowab + ROWAB_N;
+            uint16_t *slot2row = rowab;                      // rowab is dead once the verdicts are out
             int32_t *rowbuf = reinterpret_cast<int32_t *>(reinterpret_cast<unsigned char *>(Y) + G.yoff_rowbuf);
             unsigned long long *keybuf = reinterpret_cast<unsigned long long *>(reinterpret_cast<unsigned char *>(Y) + G.yoff_keybuf);
             const uint32_t j0 = (uint32_t)tid * M3_VT;
@@ -379,6 +381,17 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
             {
                 const uint32_t have = sm.have_cur, nb = sm.newbase, ccur = sm.chunk_cur;
                 const uint32_t rp = have ? sm.rowpos : 0u;
+                // entry sweep (shared memory only): every record learns the output row of its k-mer, by staged slot
+                if (nout) {
+                    const uint32_t nreal = T > j0 ? (T - j0 < (uint32_t)M3_VT ? T - j0 : (uint32_t)M3_VT) : 0u;
+                    const uint32_t *Xlo = reinterpret_cast<const uint32_t *>(X);
+                    uint32_t r = rowbase - 1u;
+#pragma unroll
+                    for (int i = 0; i < M3_VT; i++) {
+                        r += (headmask >> i) & 1u;
+                        if ((uint32_t)i < nreal) slot2row[Xlo[2 * (j0 + i)] & ((1u << M3_SB) - 1u)] = orow[r];
+                    }
+                }
                 for (uint32_t b0 = 0; b0 < nout; b0 += (uint32_t)G.BR) {
                     const uint32_t nbr = (nout - b0) < (uint32_t)G.BR ? (nout - b0) : (uint32_t)G.BR;
                     const uint32_t words = nbr * (uint32_t)S;
@@ -388,26 +401,29 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
                         for (uint32_t i = tid; i < n4; i += M3_NT) z[i] = make_int4(0, 0, 0, 0);
                     }
                     __syncthreads();
-                    {   // one pass over this thread's entries: row id by running head count, verdict by orow[]
-                        const uint32_t nreal = T > j0 ? (T - j0 < (uint32_t)M3_VT ? T - j0 : (uint32_t)M3_VT) : 0u;
-                        const uint32_t *Xlo = reinterpret_cast<const uint32_t *>(X);
-                        uint32_t r = rowbase - 1u;
+                    M3_MARK(8);
+                    {   // sample-major sweep: the same (dump, record) mapping as the pack pass, so the count reads are
+                        // coalesced (consecutive lanes -> consecutive records) and hit L1/L2
+                        const uint32_t sn = ss.n[ps], slot0 = (uint32_t)ps * ks + ((uint32_t)pcur & 3u);
+                        const int32_t *cp = ss.cptr[ps] + pcur;
 #pragma unroll
-                        for (int i = 0; i < M3_VT; i++) {
-                            const uint32_t hd = (headmask >> i) & 1u;
-                            r += hd;
-                            if ((uint32_t)i < nreal) {
-                                const uint32_t o = (uint32_t)orow[r] - b0;
-                                if (o < nbr) {
-                                    const uint32_t slot = Xlo[2 * (j0 + i)] & ((1u << M3_SB) - 1u);
-                                    const uint32_t s = slot / (uint32_t)ks;
-                                    rowbuf[o * (uint32_t)S + s] = __ldg(ss.cptr[s] + ((ss.cur[s] & ~3ull) + (slot - s * (uint32_t)ks)));   // L2 hit
-                                    if (hd) keybuf[o] = base + (X[j0 + i] >> M3_KSH);
-                                }
+                        for (int k = 0; k < M3_VT; k++) {
+                            const uint32_t i = (uint32_t)(psub + k * TPS);
+                            if (i < sn) {
+                                const uint32_t o = (uint32_t)slot2row[slot0 + i] - b0;
+                                if (o < nbr) rowbuf[o * (uint32_t)S + (uint32_t)ps] = __ldg(cp + i);
                             }
+                        }
+                        uint32_t hm = headmask;                  // keys of the surviving rows, from their head records
+                        while (hm) {
+                            const int i = __ffs(hm) - 1;
+                            hm &= hm - 1;
+                            const uint32_t o = (uint32_t)orow[rowbase + __popc(headmask & ((1u << i) - 1u))] - b0;
+                            if (o < nbr) keybuf[o] = base + (X[j0 + i] >> M3_KSH);
                         }
                     }
                     __syncthreads();
+                    M3_MARK(9);
                     if (G.S4) {
                         const uint32_t S4 = (uint32_t)G.S4, n4 = nbr * S4;
                         const int4 *src4 = reinterpret_cast<const int4 *>(rowbuf);
@@ -432,6 +448,7 @@ __global__ void __launch_bounds__(M3_NT, 3) k_merge3(MergeParams P, M3Cfg G, uin
                         if (chunk < P.max_chunks) P.out_keys[(size_t)chunk * DK_CH + off] = keybuf[rr];
                     }
                     __syncthreads();
+                    M3_MARK(10);
                 }
             }
             // R7: advance the partition state
@@ -478,7 +495,8 @@ static bool m3_make_cfg(int S, size_t smem_budget, M3Cfg &G)
     if (bK < bM) bK = bM;
     // the merge buffer that is free after the last level also holds rowab/orow (u16 x TP each), the row
     // assembly buffer (BR rows x S counts) and BR keys
-    const size_t yrow = dk_round_up((size_t)(M3_TP + 8) * 2 * 2, 16);
+    const size_t rowab_n = (size_t)(M3_TP + 8) > (size_t)sp * G.ks + 8 ? (size_t)(M3_TP + 8) : (size_t)sp * G.ks + 8;
+    const size_t yrow = dk_round_up((rowab_n + M3_TP + 8) * 2, 16);
     if (bM < yrow + 64) return false;
     int BR = (int)((bM - yrow - 32) / ((size_t)4 * S + 8));
     if (BR > 256) BR = 256;
