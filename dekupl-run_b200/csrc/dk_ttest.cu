@@ -88,16 +88,28 @@ __device__ __forceinline__ double dk_div_by_nf(double c, double nf, double r)
     return __fma_rn(e, r, q);
 }
 
+// Small counts dominate real and synthetic dumps, and (count, sample) determines x = count/NF exactly, so every
+// persistent block tabulates a = x+1 and l = log(x+1) for count < TN per sample in shared memory, with the SAME
+// device code as the direct path (bit-identical results); larger counts take the direct path.
 template <bool FASTDIV>
-__device__ __forceinline__ void dk_group_moments(const int32_t *c, const double *nf, const double *rnf, const int *idx, int n,
-                                                 double *la, double &meanv, double &mlog, double &sd)
+__device__ __forceinline__ void dk_norm_log(int32_t cc, double nf, double rnf, double &a, double &l)
+{
+    double x = FASTDIV ? dk_div_by_nf((double)cc, nf, rnf) : (double)cc / nf;   // TtestFilter.c:380-382
+    a = x + 1;                                       // :394
+    l = log(x + 1);                                  // :395
+}
+
+template <bool FASTDIV>
+__device__ __noinline__ void dk_group_moments(const int32_t *c, const double *nf, const double *rnf, const int *idx, int n,
+                                              const double2 *tab, uint32_t TN, double *la, double &meanv, double &mlog, double &sd)
 {
     double sa = 0, sl = 0;
     for (int i = 0; i < n; i++) {
-        int k = idx[i];
-        double x = FASTDIV ? dk_div_by_nf((double)c[k], nf[k], rnf[k]) : (double)c[k] / nf[k];   // TtestFilter.c:380-382
-        double a = x + 1;                                // :394
-        double l = log(x + 1);                           // :395
+        const int k = idx[i];
+        const int32_t cc = c[k];
+        double a, l;
+        if ((uint32_t)cc < TN) { const double2 t = tab[(uint32_t)k * TN + (uint32_t)cc]; a = t.x; l = t.y; }
+        else dk_norm_log<FASTDIV>(cc, nf[k], rnf[k], a, l);
         sa += a; sl += l;                                // sum() :77-84
         la[i * TT_THREADS] = l;
     }
@@ -111,36 +123,48 @@ __device__ __forceinline__ void dk_group_moments(const int32_t *c, const double 
 template <bool FASTDIV>
 __global__ void __launch_bounds__(TT_THREADS)
 k_ttest_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, uint32_t n_chunks, int S,
-             const double *nf_g, const int *idx_g, int nA, int nB, double *p_raw, double *log2fc,
+             const double *nf_g, const int *idx_g, int nA, int nB, uint32_t TN, double *p_raw, double *log2fc,
              unsigned long long *tie_sd)
 {
     extern __shared__ __align__(16) unsigned char sm[];
     int nmax = nA > nB ? nA : nB;
-    double *la = (double *)sm;                                   // [nmax][TT_THREADS]
+    double2 *tab = (double2 *)sm;                                // [S][TN] (a, l)
+    double *la = (double *)(tab + (size_t)S * TN);               // [nmax][TT_THREADS]
     double *nf = la + (size_t)nmax * TT_THREADS;                 // [S]
     double *rnf = nf + S;                                        // [S] RN(1/nf)
     int *idx = (int *)(rnf + S);                                 // [nA+nB]
     for (int i = threadIdx.x; i < S; i += TT_THREADS) { nf[i] = nf_g[i]; rnf[i] = 1.0 / nf_g[i]; }
     for (int i = threadIdx.x; i < nA + nB; i += TT_THREADS) idx[i] = idx_g[i];
     __syncthreads();
-    uint32_t oc = blockIdx.x * (TT_THREADS / DK_CH) + threadIdx.x / DK_CH;
-    uint32_t j = threadIdx.x % DK_CH;
-    if (oc >= n_chunks) return;
-    uint64_t b0 = lbase[oc], b1 = lbase[oc + 1];
-    if (j >= b1 - b0) return;
-    const int32_t *c = cnts + ((size_t)order[oc] * DK_CH + j) * (size_t)S;
+    for (uint32_t e = threadIdx.x; e < (uint32_t)S * TN; e += TT_THREADS) {
+        const uint32_t k = e / TN, cc = e - k * TN;
+        double a, l;
+        dk_norm_log<FASTDIV>((int32_t)cc, nf[k], rnf[k], a, l);
+        tab[e] = make_double2(a, l);
+    }
+    __syncthreads();
     double *myla = la + threadIdx.x;
-    double mA, mB, m1, m2, sd1, sd2;
-    dk_group_moments<FASTDIV>(c, nf, rnf, idx, nA, myla, mA, m1, sd1);
-    dk_group_moments<FASTDIV>(c, nf, rnf, idx + nA, nB, myla, mB, m2, sd2);
-    double p = dk_welch_p(m1, m2, nA, nB, sd1, sd2);
-    uint64_t row = b0 + j;
-    p_raw[row] = p;
-    log2fc[row] = log(mB / mA) / log(2.0);                       // TtestFilter.c:72-75,433
-    // libm-sensitive zero test: both sds ~0 but the logs are not all exactly 0
-    const double eps = 1e-12;
-    if (sd1 <= eps * (1 + fabs(m1)) && sd2 <= eps * (1 + fabs(m2)) && (m1 != 0 || m2 != 0))
-        atomicAdd(tie_sd, 1ull);
+    const uint32_t nblk = (n_chunks + (TT_THREADS / DK_CH) - 1) / (TT_THREADS / DK_CH);
+    unsigned long long ties = 0;
+    for (uint32_t blk = blockIdx.x; blk < nblk; blk += gridDim.x) {      // persistent: the tables are built once per CTA
+        const uint32_t oc = blk * (TT_THREADS / DK_CH) + threadIdx.x / DK_CH;
+        const uint32_t j = threadIdx.x % DK_CH;
+        if (oc >= n_chunks) continue;
+        const uint64_t b0 = lbase[oc], b1 = lbase[oc + 1];
+        if (j >= b1 - b0) continue;
+        const int32_t *c = cnts + ((size_t)order[oc] * DK_CH + j) * (size_t)S;
+        double mA, mB, m1, m2, sd1, sd2;
+        dk_group_moments<FASTDIV>(c, nf, rnf, idx, nA, tab, TN, myla, mA, m1, sd1);
+        dk_group_moments<FASTDIV>(c, nf, rnf, idx + nA, nB, tab, TN, myla, mB, m2, sd2);
+        const double p = dk_welch_p(m1, m2, nA, nB, sd1, sd2);
+        const uint64_t row = b0 + j;
+        p_raw[row] = p;
+        log2fc[row] = log(mB / mA) / log(2.0);                   // TtestFilter.c:72-75,433
+        // libm-sensitive zero test: both sds ~0 but the logs are not all exactly 0
+        const double eps = 1e-12;
+        if (sd1 <= eps * (1 + fabs(m1)) && sd2 <= eps * (1 + fabs(m2)) && (m1 != 0 || m2 != 0)) ties++;
+    }
+    if (ties) atomicAdd(tie_sd, ties);
 }
 
 void dk_ttest_release(dk_ctx *ctx, dk_ttest *t)
@@ -182,7 +206,10 @@ extern "C" int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf, 
     DK_CUDA(ctx, cudaMemsetAsync(t->tie_counts, 0, 64, st));
     DK_CUDA(ctx, cudaStreamSynchronize(st));          // idx is a local staging vector
     int nmax = nA > nB ? nA : nB;
-    size_t smem = sizeof(double) * ((size_t)nmax * TT_THREADS + 2 * S) + sizeof(int) * (nA + nB);
+    // (a, l) tables: the largest power of two of entries per sample within 32 KB
+    uint32_t TN = 0;
+    for (uint32_t t = 4; t <= 1024 && (size_t)16 * S * t <= 32768; t <<= 1) TN = t;
+    size_t smem = (size_t)16 * S * TN + sizeof(double) * ((size_t)nmax * TT_THREADS + 2 * S) + sizeof(int) * (nA + nB);
     bool fastdiv = true;                                // reciprocal path needs normal, moderate factors
     for (int s = 0; s < S; s++) if (!(nf[s] >= 1e-30 && nf[s] <= 1e30)) fastdiv = false;
     auto kfn = fastdiv ? k_ttest_rows<true> : k_ttest_rows<false>;
@@ -190,7 +217,11 @@ extern "C" int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf, 
     uint32_t nch = (uint32_t)m->n_chunks;
     if (nch) {
         unsigned grid = (nch + (TT_THREADS / DK_CH) - 1) / (TT_THREADS / DK_CH);
-        kfn<<<grid, TT_THREADS, smem, st>>>(m->cnts, m->order, m->lbase, nch, S, t->nf_dev, t->idx_dev, nA, nB,
+        int per_sm = 1;
+        DK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, TT_THREADS, smem));
+        if (per_sm < 1) per_sm = 1;
+        if (grid > (unsigned)(ctx->sm_count * per_sm)) grid = (unsigned)(ctx->sm_count * per_sm);
+        kfn<<<grid, TT_THREADS, smem, st>>>(m->cnts, m->order, m->lbase, nch, S, t->nf_dev, t->idx_dev, nA, nB, TN,
                                                      t->p_raw, t->log2fc, (unsigned long long *)(t->tie_counts + 2));
         DK_LAUNCHED(ctx);
     }
