@@ -64,6 +64,8 @@ def load_library():
         "dk_ttest_candidates": (i32, [vp, vp, dbl, P(u64), P(vp)]),
         "dk_ttest_adjust_global": (i32, [vp, vp, vp, u64, u64]),
         "dk_ttest_adjust": (i32, [vp, vp, dbl]),
+        "dk_bh_rank_slice": (i32, [vp, vp, u64, u64, u64, vp, vp]),
+        "dk_ttest_apply_adjusted": (i32, [vp, vp, vp, vp, u64]),
         "dk_ttest_filter": (i32, [vp, vp, dbl, dbl, P(u64), P(u64)]),
         "dk_ttest_export_survivors": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp]),
         "dk_ttest_export_rows": (i32, [vp, vp, vp, vp, vp]),
@@ -136,6 +138,9 @@ class TtestResult:
 
     def adjust_global(self, all_p_dev_ptr, n_all, R_global):
         self.ctx._chk(self.ctx.L.dk_ttest_adjust_global(self.ctx.h, self.h, C.c_void_p(all_p_dev_ptr), n_all, R_global))
+
+    def apply_adjusted(self, sorted_p_ptr, F_ptr, n_all):
+        self.ctx._chk(self.ctx.L.dk_ttest_apply_adjusted(self.ctx.h, self.h, C.c_void_p(sorted_p_ptr), C.c_void_p(F_ptr), n_all))
 
     def filter(self, pmax, fmin):
         d, t = C.c_uint64(0), (C.c_uint64 * 3)()

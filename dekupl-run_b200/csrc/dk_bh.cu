@@ -61,13 +61,13 @@ __global__ void k_iota_u32(uint32_t *v, uint64_t n)
     if (i < n) v[i] = (uint32_t)i;
 }
 // v[j] at the last element of each tie run (ascending order), +inf elsewhere (TtestFilter.c:467)
-__global__ void k_bh_v(const uint64_t *sk, uint64_t n, double Rg, double *v)
+__global__ void k_bh_v(const uint64_t *sk, uint64_t n, double Rg, uint64_t n_below, double *v)
 {
     uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
     bool last = (j + 1 == n) || (sk[j + 1] != sk[j]);
     double p = __longlong_as_double((long long)sk[j]);
-    v[j] = last ? (Rg / (double)(j + 1)) * p : __longlong_as_double(0x7FF0000000000000ll);
+    v[j] = last ? (Rg / (double)(n_below + j + 1)) * p : __longlong_as_double(0x7FF0000000000000ll);
 }
 // suffix minimum in three steps: tile minima, suffix over tiles (one block), apply
 #define SM_T 256
@@ -159,34 +159,62 @@ extern "C" int dk_ttest_candidates(dk_ctx *ctx, dk_ttest *t, double p_cut, uint6
     return DK_OK;
 }
 
-extern "C" int dk_ttest_adjust_global(dk_ctx *ctx, dk_ttest *t, const double *all_cand_p_dev, uint64_t n_all, uint64_t R_global)
+// Rank one p-value slice of the (global) candidate list: sorted ascending, then F[j] = min_{i >= j in the slice}
+// R/(n_below+i+1) * p_i taken at the last element of every tie run (TtestFilter.c:459-475 restated on ascending order).
+// n_below = number of candidates (anywhere) smaller than every value of this slice. A multi-GPU caller owns one
+// p-range per rank, then lowers F by the minimum of all higher ranges (the running minimum crosses slice borders).
+extern "C" int dk_bh_rank_slice(dk_ctx *ctx, const double *p_dev, uint64_t n, uint64_t n_below, uint64_t R_global,
+                                double *sorted_p_dev, double *F_dev)
 {
-    if (!ctx || !t) return dk_fail(ctx, DK_ERR_ARG, "ttest_adjust: NULL argument");
+    if (!ctx || (n && (!p_dev || !sorted_p_dev || !F_dev))) return dk_fail(ctx, DK_ERR_ARG, "bh_rank_slice: NULL argument");
+    if (n == 0) return DK_OK;
+    cudaStream_t st = ctx->stream;
+    uint64_t *k0 = (uint64_t *)dk_dev_alloc(ctx, 8 * n), *k1 = (uint64_t *)dk_dev_alloc(ctx, 8 * n);
+    uint32_t *v0 = (uint32_t *)dk_dev_alloc(ctx, 4 * n), *v1 = (uint32_t *)dk_dev_alloc(ctx, 4 * n);
+    const uint64_t nt = (n + SM_T * SM_V - 1) / (SM_T * SM_V);
+    double *tmin = (double *)dk_dev_alloc(ctx, 8 * nt);
+    if (!k0 || !k1 || !v0 || !v1 || !tmin) return DK_ERR_NOMEM;
+    DK_CUDA(ctx, cudaMemcpyAsync(k0, p_dev, 8 * n, cudaMemcpyDeviceToDevice, st));
+    k_iota_u32<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(v0, n); DK_LAUNCHED(ctx);
+    uint64_t *sk; uint32_t *sv;
+    DK_TRY(dk_sort_pairs_u64(ctx, k0, v0, k1, v1, n, &sk, &sv));
+    k_bh_v<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(sk, n, (double)R_global, n_below, F_dev); DK_LAUNCHED(ctx);
+    k_sufmin_tiles<<<(unsigned)nt, SM_T, 0, st>>>(F_dev, n, tmin); DK_LAUNCHED(ctx);
+    k_sufmin_scan_tiles<<<1, 32, 0, st>>>(tmin, nt); DK_LAUNCHED(ctx);
+    k_sufmin_apply<<<(unsigned)nt, SM_T, 0, st>>>(F_dev, n, tmin); DK_LAUNCHED(ctx);
+    DK_CUDA(ctx, cudaMemcpyAsync(sorted_p_dev, sk, 8 * n, cudaMemcpyDeviceToDevice, st));
+    DK_CUDA(ctx, cudaStreamSynchronize(st));
+    dk_dev_release(ctx, k0); dk_dev_release(ctx, k1); dk_dev_release(ctx, v0); dk_dev_release(ctx, v1); dk_dev_release(ctx, tmin);
+    return DK_OK;
+}
+
+// adjusted p of this shard's candidates from the global ascending candidate list and its F values
+extern "C" int dk_ttest_apply_adjusted(dk_ctx *ctx, dk_ttest *t, const double *sorted_p_dev, const double *F_dev, uint64_t n_all)
+{
+    if (!ctx || !t) return dk_fail(ctx, DK_ERR_ARG, "ttest_apply_adjusted: NULL argument");
     cudaStream_t st = ctx->stream;
     dk_dev_release(ctx, t->p_adj);
     t->p_adj = (double *)dk_dev_alloc(ctx, sizeof(double) * (t->R + 1));
     if (!t->p_adj) return DK_ERR_NOMEM;
     if (t->R) { k_fill_nan<<<(unsigned)((t->R + 255) / 256), 256, 0, st>>>(t->p_adj, t->R); DK_LAUNCHED(ctx); }
     if (n_all == 0 || t->n_cand == 0) return DK_OK;
-    uint64_t *k0 = (uint64_t *)dk_dev_alloc(ctx, 8 * n_all), *k1 = (uint64_t *)dk_dev_alloc(ctx, 8 * n_all);
-    uint32_t *v0 = (uint32_t *)dk_dev_alloc(ctx, 4 * n_all), *v1 = (uint32_t *)dk_dev_alloc(ctx, 4 * n_all);
-    double *F = (double *)dk_dev_alloc(ctx, 8 * n_all);
-    uint64_t nt = (n_all + SM_T * SM_V - 1) / (SM_T * SM_V);
-    double *tmin = (double *)dk_dev_alloc(ctx, 8 * nt);
-    if (!k0 || !k1 || !v0 || !v1 || !F || !tmin) return DK_ERR_NOMEM;
-    DK_CUDA(ctx, cudaMemcpyAsync(k0, all_cand_p_dev, 8 * n_all, cudaMemcpyDeviceToDevice, st));
-    k_iota_u32<<<(unsigned)((n_all + 255) / 256), 256, 0, st>>>(v0, n_all); DK_LAUNCHED(ctx);
-    uint64_t *sk; uint32_t *sv;
-    DK_TRY(dk_sort_pairs_u64(ctx, k0, v0, k1, v1, n_all, &sk, &sv));
-    k_bh_v<<<(unsigned)((n_all + 255) / 256), 256, 0, st>>>(sk, n_all, (double)R_global, F); DK_LAUNCHED(ctx);
-    k_sufmin_tiles<<<(unsigned)nt, SM_T, 0, st>>>(F, n_all, tmin); DK_LAUNCHED(ctx);
-    k_sufmin_scan_tiles<<<1, 32, 0, st>>>(tmin, nt); DK_LAUNCHED(ctx);
-    k_sufmin_apply<<<(unsigned)nt, SM_T, 0, st>>>(F, n_all, tmin); DK_LAUNCHED(ctx);
-    k_bh_lookup<<<(unsigned)((t->n_cand + 255) / 256), 256, 0, st>>>(t->cand_p, t->cand_row, t->n_cand, sk, F, n_all, t->p_adj);
+    k_bh_lookup<<<(unsigned)((t->n_cand + 255) / 256), 256, 0, st>>>(t->cand_p, t->cand_row, t->n_cand, (const uint64_t *)sorted_p_dev,
+                                                                   F_dev, n_all, t->p_adj);
     DK_LAUNCHED(ctx);
-    dk_dev_release(ctx, k0); dk_dev_release(ctx, k1); dk_dev_release(ctx, v0); dk_dev_release(ctx, v1);
-    dk_dev_release(ctx, F); dk_dev_release(ctx, tmin);
     return DK_OK;
+}
+
+extern "C" int dk_ttest_adjust_global(dk_ctx *ctx, dk_ttest *t, const double *all_cand_p_dev, uint64_t n_all, uint64_t R_global)
+{
+    if (!ctx || !t) return dk_fail(ctx, DK_ERR_ARG, "ttest_adjust: NULL argument");
+    if (n_all == 0 || t->n_cand == 0) return dk_ttest_apply_adjusted(ctx, t, nullptr, nullptr, 0);
+    double *sp = (double *)dk_dev_alloc(ctx, 8 * n_all), *F = (double *)dk_dev_alloc(ctx, 8 * n_all);
+    if (!sp || !F) return DK_ERR_NOMEM;
+    int rc = dk_bh_rank_slice(ctx, all_cand_p_dev, n_all, 0, R_global, sp, F);
+    if (rc == DK_OK) rc = dk_ttest_apply_adjusted(ctx, t, sp, F, n_all);
+    cudaStreamSynchronize(ctx->stream);
+    dk_dev_release(ctx, sp); dk_dev_release(ctx, F);
+    return rc;
 }
 
 extern "C" int dk_ttest_adjust(dk_ctx *ctx, dk_ttest *t, double p_cut)

@@ -81,6 +81,17 @@ class GpuBackend:
     def adjust_global(self, all_p, R_global):
         self.t.adjust_global(all_p.data_ptr() if all_p.numel() else 0, all_p.numel(), R_global)
 
+    def bh_rank_slice(self, p, n_below, R_global):
+        """-> (sorted p, F) device tensors for one p-range of the global candidate list"""
+        sp, F = torch.empty_like(p), torch.empty_like(p)
+        if p.numel():
+            self.ctx._chk(self.ctx.L.dk_bh_rank_slice(self.ctx.h, p.data_ptr(), p.numel(), int(n_below), int(R_global),
+                                                      sp.data_ptr(), F.data_ptr()))
+        return sp, F
+
+    def apply_adjusted(self, sp, F):
+        self.t.apply_adjusted(sp.data_ptr() if sp.numel() else 0, F.data_ptr() if F.numel() else 0, sp.numel())
+
     def filter(self, pmax, fmin):
         return self.t.filter(pmax, fmin), self.t.ties
 
@@ -148,7 +159,24 @@ def run_sharded(backend, key_ptrs, cnt_ptrs, n, r, a, idxA, idxB, pmax, fmin, nf
     backend.ttest_rows(nf_used, idxA, idxB)
     cand = backend.candidates(pmax)
     all_p = _all_gather_var(cand)
-    backend.adjust_global(all_p, R_glob)
+    if world == 1:
+        backend.adjust_global(all_p, R_glob)
+    else:
+        # BH work is split by p-value range: rank g ranks the candidates in (g*P/world, (g+1)*P/world] (equal values
+        # share a range; under the null p is uniform, so ranges are balanced), instead of every rank sorting the whole list
+        lo = pmax * rank / world if rank else -1.0
+        hi = pmax * (rank + 1) / world if rank + 1 < world else float("inf")
+        below = all_p <= lo
+        mine = all_p[(~below) & (all_p <= hi)]
+        sp, F = backend.bh_rank_slice(mine, int(below.sum().item()), R_glob)
+        # the running minimum crosses range borders: lower F by the smallest F of all higher ranges
+        first = F[:1] if F.numel() else torch.full((1,), float("inf"), dtype=torch.float64, device=all_p.device)
+        mins = [torch.empty_like(first) for _ in range(world)]
+        dist.all_gather(mins, first.contiguous())
+        above = torch.cat(mins[rank + 1:]).min() if rank + 1 < world else None
+        if above is not None and F.numel():
+            F = torch.minimum(F, above)
+        backend.apply_adjusted(_all_gather_var(sp), _all_gather_var(F))
     D_loc, ties = backend.filter(pmax, fmin)
     d = torch.tensor([D_loc, ties[0], ties[1], ties[2]], dtype=torch.int64, device=device)
     dist.all_reduce(d)

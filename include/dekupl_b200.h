@@ -119,6 +119,12 @@ int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf,
 int dk_ttest_candidates(dk_ctx *ctx, dk_ttest *t, double p_cut, uint64_t *n_cand, const double **cand_p_dev);
 int dk_ttest_adjust_global(dk_ctx *ctx, dk_ttest *t, const double *all_cand_p_dev, uint64_t n_all, uint64_t R_global);
 int dk_ttest_adjust(dk_ctx *ctx, dk_ttest *t, double p_cut);
+/* Scalable multi-GPU BH: after the all-gather every rank takes ONE p-value range of the candidates (equal p-values
+ * always share a range), ranks it with dk_bh_rank_slice (n_below = candidates below the range), lowers F by the
+ * minimum F of all higher ranges, all-gathers (sorted p, F) in range order and applies them to its own rows. */
+int dk_bh_rank_slice(dk_ctx *ctx, const double *p_dev, uint64_t n, uint64_t n_below, uint64_t R_global,
+                     double *sorted_p_dev /* out [n] ascending */, double *F_dev /* out [n] running minimum inside the slice */);
+int dk_ttest_apply_adjusted(dk_ctx *ctx, dk_ttest *t, const double *sorted_p_dev, const double *F_dev, uint64_t n_all);
 /* TtestFilter.c:486: survivors = adj_p <= pmax && fabs(log2FC) >= fmin; returns D in *n_keep.
  * ties (may be NULL): ties[0] = rows with adj_p within 1e-9 rel of pmax, ties[1] = rows with
  * fabs(log2FC) within 1e-9 rel of fmin, ties[2] = rows whose sd was within 1e-13 of the sd==0 test */

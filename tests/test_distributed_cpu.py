@@ -103,6 +103,20 @@ class OracleBackend:
         pos = np.searchsorted(sp, self.p[self.cand], side="left")
         self.adj[self.cand] = np.minimum(1.0, F[pos])
 
+    def bh_rank_slice(self, p, n_below, R_global):
+        sp = np.sort(p.numpy())
+        j = np.arange(len(sp))
+        last = np.r_[sp[1:] != sp[:-1], True] if len(sp) else np.zeros(0, bool)
+        v = np.where(last, (float(R_global) / (n_below + j + 1.0)) * sp, np.inf)
+        F = np.minimum.accumulate(v[::-1])[::-1].copy() if len(sp) else v
+        return torch.from_numpy(sp), torch.from_numpy(F)
+
+    def apply_adjusted(self, sp, F):
+        self.adj = np.full(len(self.p), np.nan)
+        if sp.numel():
+            pos = np.searchsorted(sp.numpy(), self.p[self.cand], side="left")
+            self.adj[self.cand] = np.minimum(1.0, F.numpy()[pos])
+
     def filter(self, pmax, fmin):
         keep = (self.adj <= pmax) & (np.abs(self.fc) >= fmin)
         self.keep = np.nonzero(keep)[0]

@@ -291,3 +291,31 @@ def test_join_host_pipelined_slices_equal_single_pass(ctx, S, slices, monkeypatc
     assert m.union == oU and np.array_equal(gk, ok) and np.array_equal(gc, oc)
     assert m.checksum() == m1.checksum()
     m.free(); m1.free()
+
+
+@pytest.mark.gpu
+def test_bh_rank_slices_stitch_to_the_reference_adjustment(ctx):
+    """dk_bh_rank_slice on three p-value ranges + cross-range running minimum == orc.bh on the whole list (heavy ties)"""
+    import torch
+    rng = np.random.default_rng(11)
+    p = np.round(rng.random(50_000) ** 2, 3)                       # many exact ties, some zeros
+    p[:200] = rng.random(200) * 1e-6
+    want = orc.bh(p)
+    dev = torch.device("cuda", 0)
+    tp = torch.from_numpy(p).to(dev)
+    edges = [-1.0, 0.1, 0.5, float("inf")]
+    parts = []
+    for lo, hi in zip(edges[:-1], edges[1:]):
+        mine = tp[(tp > lo) & (tp <= hi)].contiguous()
+        sp, F = torch.empty_like(mine), torch.empty_like(mine)
+        ctx._chk(ctx.L.dk_bh_rank_slice(ctx.h, mine.data_ptr(), mine.numel(), int((tp <= lo).sum().item()), len(p),
+                                        sp.data_ptr(), F.data_ptr()))
+        ctx.sync()
+        parts.append((sp.cpu().numpy(), F.cpu().numpy()))
+    for g in range(len(parts) - 1):                                # lower F by the minimum of all higher ranges
+        above = min(parts[h][1][0] for h in range(g + 1, len(parts)))
+        parts[g] = (parts[g][0], np.minimum(parts[g][1], above))
+    sp = np.concatenate([x[0] for x in parts]); F = np.concatenate([x[1] for x in parts])
+    assert np.all(np.diff(sp) >= 0)
+    got = np.minimum(1.0, F[np.searchsorted(sp, p, side="left")])
+    np.testing.assert_allclose(got, want, rtol=1e-12)
