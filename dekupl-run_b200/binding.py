@@ -61,6 +61,7 @@ def load_library():
         "dk_nf_hist_dev": (i32, [vp, vp, vp]), "dk_nf_advance_dev": (i32, [vp, vp, vp]),
         "dk_nf_result": (i32, [vp, vp, P(dbl)]), "dk_nf_end": (None, [vp, vp]),
         "dk_ttest_rows": (i32, [vp, vp, P(dbl), P(i32), i32, P(i32), i32, P(vp)]),
+        "dk_poisson_rows": (i32, [vp, vp, P(i32), i32, P(i32), i32, P(vp), P(u64)]),
         "dk_ttest_candidates": (i32, [vp, vp, dbl, P(u64), P(vp)]),
         "dk_ttest_adjust_global": (i32, [vp, vp, vp, u64, u64]),
         "dk_ttest_adjust": (i32, [vp, vp, dbl]),
@@ -251,6 +252,13 @@ class Context:
         self._chk(self.L.dk_ttest_rows(self.h, m.h, nf.ctypes.data_as(C.POINTER(C.c_double)), a, len(idxA), b, len(idxB),
                                        C.byref(out)))
         return TtestResult(self, out, m)
+
+    def poisson_rows(self, m, idxA, idxB):
+        """TtestFilter -l; returns (TtestResult, (N1, N2, negative_statistics))"""
+        a, b = (C.c_int * len(idxA))(*idxA), (C.c_int * len(idxB))(*idxB)
+        out, info = C.c_void_p(0), (C.c_uint64 * 3)()
+        self._chk(self.L.dk_poisson_rows(self.h, m.h, a, len(idxA), b, len(idxB), C.byref(out), info))
+        return TtestResult(self, out, m), tuple(int(x) for x in info)
 
     # ---- whole path -----------------------------------------------------------
     def run_path(self, key_ptrs, cnt_ptrs, n, device_inputs, min_rec, min_abund, nf_mode, idxA, idxB, pmax, fmin,

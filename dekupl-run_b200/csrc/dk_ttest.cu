@@ -233,5 +233,106 @@ extern "C" int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf, 
     *out = t;
     return DK_OK;
 }
+// ---- Poisson likelihood-ratio mode (TtestFilter -l; TtestFilter.c:152-185,340-362,419-424) ---------------
+// pass 1 (:340-362): totals of the raw counts over the two groups, all rows
+__global__ void k_group_totals(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, uint32_t n_chunks, int S,
+                               const int *idx_g, int nA, int nB, unsigned long long *tot)
+{
+    unsigned long long a = 0, b = 0;
+    for (uint32_t oc = blockIdx.x; oc < n_chunks; oc += gridDim.x) {
+        const uint32_t rows = (uint32_t)(lbase[oc + 1] - lbase[oc]);
+        const int32_t *base = cnts + (size_t)order[oc] * DK_CH * S;
+        for (uint32_t r = threadIdx.x; r < rows; r += blockDim.x) {
+            const int32_t *c = base + (size_t)r * S;
+            for (int i = 0; i < nA; i++) a += (unsigned long long)(long long)c[idx_g[i]];
+            for (int i = 0; i < nB; i++) b += (unsigned long long)(long long)c[idx_g[nA + i]];
+        }
+    }
+    for (int o = 16; o; o >>= 1) { a += __shfl_down_sync(0xffffffffu, a, o); b += __shfl_down_sync(0xffffffffu, b, o); }
+    if ((threadIdx.x & 31) == 0) { atomicAdd(&tot[0], a); atomicAdd(&tot[1], b); }
+}
+// logpoisson (:152-164): log of lambda^k e^-lambda / Gamma(k+1) through the density itself, like the reference
+// (so an underflowing density gives the reference's constant 0.001)
+__device__ double dk_logpoisson(double lambda, double k)
+{
+    const double t = exp(-lambda + k * log(lambda) - lgamma(k + 1.0));
+    if (t <= 0) return 0.001;
+    return log(t);
+}
+__global__ void __launch_bounds__(TT_THREADS)
+k_poisson_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, uint32_t n_chunks, int S, const int *idx_g,
+               int nA, int nB, const unsigned long long *tot, double *p_raw, double *log2fc, unsigned long long *neg_stat)
+{
+    const uint32_t oc = blockIdx.x * (TT_THREADS / DK_CH) + threadIdx.x / DK_CH, j = threadIdx.x % DK_CH;
+    if (oc >= n_chunks) return;
+    const uint64_t b0 = lbase[oc];
+    if (j >= lbase[oc + 1] - b0) return;
+    const int32_t *c = cnts + ((size_t)order[oc] * DK_CH + j) * (size_t)S;
+    double sa = 0, sb = 0;
+    for (int i = 0; i < nA; i++) sa += (double)c[idx_g[i]] + 1;          // a[i] = count + 1 (:394), counts NOT normalised (:380-382)
+    for (int i = 0; i < nB; i++) sb += (double)c[idx_g[nA + i]] + 1;
+    const double K1 = sa / nA, K2 = sb / nB;                             // "sumA/sumB" are means (:421-422)
+    const long long N1 = (long long)tot[0], N2 = (long long)tot[1];
+    const double ll1 = dk_logpoisson(K1, K1) + dk_logpoisson(K2, K2);    // :175
+    const double theta = (K1 + K2) / (double)(N1 + N2);                  // :176
+    const double ll2 = dk_logpoisson(theta * (double)N1, K1) + dk_logpoisson(theta * (double)N2, K2);
+    const double t_stat = 2 * (ll1 - ll2);
+    double p;
+    if (!(t_stat >= 0)) { p = 1.0; atomicAdd(neg_stat, 1ull); }          // Boost throws here (the reference aborts)
+    else p = 1.0 - erf(sqrt(t_stat / 2.0));                              // 1 - cdf(chi_squared(1), t_stat) (:182-183)
+    p_raw[b0 + j] = p;
+    log2fc[b0 + j] = log(K2 / K1) / log(2.0);                            // :433
+}
+
+extern "C" int dk_poisson_rows(dk_ctx *ctx, const dk_matrix *m, const int *idxA, int nA, const int *idxB, int nB, dk_ttest **out,
+                               uint64_t *info)
+{
+    if (!ctx || !m || !idxA || !idxB || !out) return dk_fail(ctx, DK_ERR_ARG, "poisson_rows: NULL argument");
+    *out = nullptr;
+    const int S = m->S;
+    if (nA < 1 || nB < 1) return dk_fail(ctx, DK_ERR_UNSUPPORTED, "poisson: empty group (%d, %d samples)", nA, nB);
+    for (int i = 0; i < nA; i++) if (idxA[i] < 0 || idxA[i] >= S) return dk_fail(ctx, DK_ERR_ARG, "poisson: idxA[%d] out of range", i);
+    for (int i = 0; i < nB; i++) if (idxB[i] < 0 || idxB[i] >= S) return dk_fail(ctx, DK_ERR_ARG, "poisson: idxB[%d] out of range", i);
+    if (m->R >= 0xFFFFFFFFull) return dk_fail(ctx, DK_ERR_ARG, "poisson: more than 2^32 rows on one GPU; shard by prefix");
+    cudaStream_t st = ctx->stream;
+    DK_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
+    dk_ttest *t = new dk_ttest();
+    t->m = m; t->R = m->R; t->S = S; t->nA = nA; t->nB = nB;
+    t->nf_dev = (double *)dk_dev_alloc(ctx, sizeof(double) * S);
+    t->idx_dev = (int *)dk_dev_alloc(ctx, sizeof(int) * (nA + nB));
+    t->p_raw = (double *)dk_dev_alloc(ctx, sizeof(double) * (t->R + 1));
+    t->log2fc = (double *)dk_dev_alloc(ctx, sizeof(double) * (t->R + 1));
+    t->tie_counts = (uint64_t *)dk_dev_alloc(ctx, 64);
+    if (!t->nf_dev || !t->idx_dev || !t->p_raw || !t->log2fc || !t->tie_counts) { dk_ttest_release(ctx, t); return DK_ERR_NOMEM; }
+    std::vector<int> idx(nA + nB);
+    memcpy(idx.data(), idxA, sizeof(int) * nA);
+    memcpy(idx.data() + nA, idxB, sizeof(int) * nB);
+    std::vector<double> ones(S, 1.0);                      // survivors print the RAW counts in this mode (count / 1.0)
+    DK_CUDA(ctx, cudaMemcpyAsync(t->nf_dev, ones.data(), sizeof(double) * S, cudaMemcpyHostToDevice, st));
+    DK_CUDA(ctx, cudaMemcpyAsync(t->idx_dev, idx.data(), sizeof(int) * (nA + nB), cudaMemcpyHostToDevice, st));
+    DK_CUDA(ctx, cudaMemsetAsync(t->tie_counts, 0, 64, st));
+    DK_CUDA(ctx, cudaStreamSynchronize(st));
+    unsigned long long *tot = (unsigned long long *)(t->tie_counts + 4);      // [4]=N1 [5]=N2 [6]=negative statistics
+    const uint32_t nch = (uint32_t)m->n_chunks;
+    if (nch) {
+        unsigned g1 = nch < (unsigned)ctx->sm_count * 8 ? nch : (unsigned)ctx->sm_count * 8;
+        k_group_totals<<<g1, 256, 0, st>>>(m->cnts, m->order, m->lbase, nch, S, t->idx_dev, nA, nB, tot); DK_LAUNCHED(ctx);
+        unsigned grid = (nch + (TT_THREADS / DK_CH) - 1) / (TT_THREADS / DK_CH);
+        k_poisson_rows<<<grid, TT_THREADS, 0, st>>>(m->cnts, m->order, m->lbase, nch, S, t->idx_dev, nA, nB, tot, t->p_raw, t->log2fc,
+                                                   tot + 2);
+        DK_LAUNCHED(ctx);
+    }
+    uint64_t h[3] = {0, 0, 0};
+    DK_CUDA(ctx, cudaMemcpyAsync(h, tot, sizeof h, cudaMemcpyDeviceToHost, st));
+    DK_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));
+    DK_CUDA(ctx, cudaStreamSynchronize(st));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
+    ctx->stage_ms[2] = ms;
+    if (info) { info[0] = h[0]; info[1] = h[1]; info[2] = h[2]; }
+    *out = t;
+    return DK_OK;
+}
+
 extern "C" uint64_t dk_ttest_rows_count(const dk_ttest *t) { return t ? t->R : 0; }
 extern "C" void dk_ttest_free(dk_ctx *ctx, dk_ttest *t) { if (ctx) dk_ttest_release(ctx, t); }

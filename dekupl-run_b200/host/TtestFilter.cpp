@@ -4,7 +4,8 @@
 //   TtestFilter -p P -f F -r raw_pvals.txt.gz counts.tsv.gz sample_conditions_full.tsv A B | gzip -c > diff-counts.tsv.gz
 // Not reproduced on purpose: the fixed temp file ./.TtestFilter.tmp (TtestFilter.c:22,331,497 — two
 // runs in one directory corrupt each other) and the unused extra pass over the matrix (:340-362).
-// -l (Poisson likelihood ratio, :152-185) is outside the north-star path: refused with a message.
+// -l runs the Poisson likelihood ratio of :152-185 (dk_poisson_rows); where the reference aborts (negative statistic:
+// Boost throws) the row gets p = 1 and a warning is printed.
 #include <math.h>
 #include <unistd.h>
 #include "../../include/dekupl_b200.h"
@@ -33,10 +34,6 @@ int main(int argc, char *argv[])
         fprintf(stderr, "         -l        disregard the program name, do a Poisson likelihood ratio (HAWK model)\n");
         fprintf(stderr, "\n");
         return 1;
-    }
-    if (!use_t_test) {
-        fprintf(stderr, "TtestFilter: -l (Poisson likelihood ratio) is not implemented by the GPU path; refusing rather than running a t-test\n");
-        return EXIT_FAILURE;
     }
     const char *counts_file = argv[optind++], *conditions_file = argv[optind++];
     const char *conditionA = argv[optind++], *conditionB = argv[optind++];
@@ -104,7 +101,15 @@ int main(int argc, char *argv[])
     dk_ttest *t = nullptr;
 #define CHECK(call) if ((call) != DK_OK) { fprintf(stderr, "TtestFilter: %s\n", dk_last_error(ctx)); return EXIT_FAILURE; }
     CHECK(dk_matrix_from_host(ctx, S, mt.R, nullptr, mt.cnts.data(), &m));
-    CHECK(dk_ttest_rows(ctx, m, nf.data(), idxA.data(), (int)idxA.size(), idxB.data(), (int)idxB.size(), &t));
+    if (use_t_test) {
+        CHECK(dk_ttest_rows(ctx, m, nf.data(), idxA.data(), (int)idxA.size(), idxB.data(), (int)idxB.size(), &t));
+    } else {
+        uint64_t pinfo[3] = {0, 0, 0};
+        CHECK(dk_poisson_rows(ctx, m, idxA.data(), (int)idxA.size(), idxB.data(), (int)idxB.size(), &t, pinfo));
+        if (pinfo[2])
+            fprintf(stderr, "TtestFilter: %llu k-mers had a negative likelihood-ratio statistic (the reference aborts inside Boost); p set to 1\n",
+                    (unsigned long long)pinfo[2]);
+    }
     if (raw_pval_file) {   // :335-338,426-430: gz text "kmer\t%f\n" with the RAW p of every row
         gzFile pf = gzopen(raw_pval_file, "w");
         if (!pf) { fprintf(stderr, "Failed to open %s\n", raw_pval_file); exit(EXIT_FAILURE); }

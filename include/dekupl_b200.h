@@ -113,6 +113,13 @@ void dk_nf_end(dk_ctx *ctx, dk_nf_state *st);
  * reference aborts inside Boost). */
 int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf,
                   const int *idxA, int nA, const int *idxB, int nB, dk_ttest **out);
+/* TtestFilter -l: Poisson likelihood ratio of the two group means of (count+1) against the pooled rate
+ * (TtestFilter.c:152-185), group totals N1/N2 over all rows first (:340-362); counts are not normalised. The result
+ * object feeds the same BH / filter / export calls (exported "normalised" counts are the raw counts, as the
+ * reference prints them). info (may be NULL): [0]=N1, [1]=N2, [2]=rows whose statistic was negative (Boost throws
+ * there and the reference aborts; p is set to 1). */
+int dk_poisson_rows(dk_ctx *ctx, const dk_matrix *m, const int *idxA, int nA, const int *idxB, int nB, dk_ttest **out,
+                    uint64_t *info);
 /* BH over candidates p <= p_cut (exact for every row whose adjusted p <= p_cut; p_cut >= 1 => all rows).
  * Single GPU: dk_ttest_adjust(ctx,t,p_cut). Multi GPU: _candidates -> caller all-gathers
  * the candidate p-values and all-reduces R -> _adjust_global. */

@@ -59,6 +59,11 @@ void orc_ttest_rows(const int32_t *cnts, size_t R, int S, const double *nf,
                     const int *idxA, int nA, const int *idxB, int nB,
                     double *p_raw, double *meanA, double *meanB, double *log2fc);
 
+/* Poisson likelihood-ratio mode (-l): TtestFilter.c:152-185 per row, totals of :340-362 in N_out[2]. */
+double orc_poisson_lr(double K1, double K2, int64_t N1, int64_t N2);
+void orc_poisson_rows(const int32_t *cnts, size_t R, int S, const int *idxA, int nA, const int *idxB, int nB,
+                      double *p_raw, double *meanA, double *meanB, double *log2fc, int64_t *N_out);
+
 /* TtestFilter.c:459-476: Benjamini-Hochberg, in place semantic on a copy. */
 void orc_bh(const double *p_raw, size_t R, double *p_adj);
 

@@ -145,3 +145,50 @@ size_t orc_filter(const double *p_adj, const double *log2fc, size_t R,
     }
     return D;
 }
+
+/* ---- Poisson likelihood-ratio mode (-l), TtestFilter.c:152-185,340-362,419-424 -------------------------
+ * logpoisson (:152-164): log of the Poisson density at a NON-integer k. Boost evaluates
+ * pdf(poisson(lambda), k) = lambda^k e^-lambda / Gamma(k+1) (gamma_p_derivative(k+1, lambda)); the reference then
+ * takes log1p(t-1) == log(t), or returns the constant 0.001 when the density underflows to 0 (:157-161). */
+static double o_logpoisson(double lambda, double k)
+{
+    double t = exp(-lambda + k * log(lambda) - lgamma(k + 1.0));
+    if (t <= 0) return 0.001;
+    return log(t);
+}
+/* :173-185. cdf(chi_squared(1), x) = P(1/2, x/2) = erf(sqrt(x/2)); the reference forms 1.0 - cdf (cancellation
+ * included). Boost throws for x < 0 (the reference aborts); the oracle and the product return p = 1 there. */
+double orc_poisson_lr(double K1, double K2, int64_t N1, int64_t N2)
+{
+    double ll1 = o_logpoisson(K1, K1) + o_logpoisson(K2, K2);
+    double theta = (K1 + K2) / (N1 + N2);
+    double ll2 = o_logpoisson(theta * N1, K1) + o_logpoisson(theta * N2, K2);
+    double llr = ll1 - ll2;
+    double t_stat = 2 * llr;
+    if (!(t_stat >= 0)) return 1.0;
+    return 1.0 - erf(sqrt(t_stat / 2.0));
+}
+/* pass 1 (:340-362) totals over all rows, then per row (:392-433) K = mean(count+1) per group (counts are NOT
+ * normalised in this mode, :380-382) */
+void orc_poisson_rows(const int32_t *cnts, size_t R, int S, const int *idxA, int nA, const int *idxB, int nB,
+                      double *p_raw, double *meanA, double *meanB, double *log2fc, int64_t *N_out)
+{
+    uint64_t N1 = 0, N2 = 0;
+    for (size_t r = 0; r < R; r++) {
+        const int32_t *c = cnts + r * S;
+        for (int i = 0; i < nA; i++) N1 += (double)c[idxA[i]];
+        for (int i = 0; i < nB; i++) N2 += (double)c[idxB[i]];
+    }
+    if (N_out) { N_out[0] = (int64_t)N1; N_out[1] = (int64_t)N2; }
+    double *a = (double *)malloc(sizeof(double) * (nA + 1)), *b = (double *)malloc(sizeof(double) * (nB + 1));
+    for (size_t r = 0; r < R; r++) {
+        const int32_t *c = cnts + r * S;
+        for (int i = 0; i < nA; i++) a[i] = (double)c[idxA[i]] + 1;
+        for (int i = 0; i < nB; i++) b[i] = (double)c[idxB[i]] + 1;
+        double mA = o_mean(a, nA), mB = o_mean(b, nB);
+        p_raw[r] = orc_poisson_lr(mA, mB, (int64_t)N1, (int64_t)N2);
+        meanA[r] = mA; meanB[r] = mB;
+        log2fc[r] = log(mB / mA) / log(2);
+    }
+    free(a); free(b);
+}

@@ -28,6 +28,10 @@ def load():
     L.orc_student_t_2tail.argtypes = [dbl, dbl]
     L.orc_ttest_rows.restype = None
     L.orc_ttest_rows.argtypes = [vp, sz, i32, vp, vp, i32, vp, i32, vp, vp, vp, vp]
+    L.orc_poisson_lr.restype = dbl
+    L.orc_poisson_lr.argtypes = [dbl, dbl, C.c_int64, C.c_int64]
+    L.orc_poisson_rows.restype = None
+    L.orc_poisson_rows.argtypes = [vp, sz, i32, vp, i32, vp, i32, vp, vp, vp, vp, vp]
     L.orc_bh.restype = None
     L.orc_bh.argtypes = [vp, sz, vp]
     L.orc_filter.restype = sz
@@ -80,6 +84,23 @@ def ttest_rows(cnts, nf, idxA, idxB):
     L.orc_ttest_rows(cnts.ctypes.data, R, S, nf.ctypes.data, a.ctypes.data, len(a), b.ctypes.data, len(b),
                      p.ctypes.data, mA.ctypes.data, mB.ctypes.data, fc.ctypes.data)
     return p, mA, mB, fc
+
+
+def poisson_rows(cnts, idxA, idxB):
+    """-l mode: (p_raw, meanA, meanB, log2fc, (N1, N2))"""
+    L = load()
+    cnts = np.ascontiguousarray(cnts, dtype=np.int32)
+    R, S = cnts.shape
+    a, b = np.array(idxA, dtype=np.int32), np.array(idxB, dtype=np.int32)
+    p, mA, mB, fc = np.empty(R), np.empty(R), np.empty(R), np.empty(R)
+    N = np.zeros(2, np.int64)
+    L.orc_poisson_rows(cnts.ctypes.data, R, S, a.ctypes.data, len(a), b.ctypes.data, len(b),
+                       p.ctypes.data, mA.ctypes.data, mB.ctypes.data, fc.ctypes.data, N.ctypes.data)
+    return p, mA, mB, fc, (int(N[0]), int(N[1]))
+
+
+def poisson_lr(K1, K2, N1, N2):
+    return load().orc_poisson_lr(float(K1), float(K2), int(N1), int(N2))
 
 
 def bh(p):

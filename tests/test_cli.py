@@ -38,12 +38,11 @@ def test_missing_input_file_fails_like_the_reference():
         assert r.returncode != 0 and "Failed to open /nonexistent/x" in r.stderr
 
 
-def test_poisson_mode_is_refused_not_faked(tmp_path):
-    r = run("TtestFilter", "-l", "a", "b", "A", "B")
-    assert r.returncode != 0 and "not implemented" in r.stderr
+def test_poisson_flag_is_accepted_in_usage():
+    r = run("TtestFilter", "-l")
+    assert r.returncode == 1 and "-l        disregard the program name" in r.stderr
 
 
-# ------------------------------------------------------------------ GPU: stdout parity ---
 @pytest.mark.gpu
 def test_joinCounts_cli_matches_reference_binary_bytes(tmp_path):
     for ci, case in enumerate(load_json("join_cases.json")):
@@ -108,5 +107,34 @@ def test_TtestFilter_cli_fixture(tmp_path, nm):
         if adj[i] <= 0.2 and abs(fc[i]) >= 0:
             want += "%s\t%f\t%f\t%f\t%f" % (mm["kmers"][i], adj[i], mA[i], mB[i], fc[i])
             want += "".join("\t%.2f" % (cnts[i, j] / nf[j]) for j in range(6)) + "\n"
+    assert r.stdout == want
+    assert gzip.open(raw, "rt").read() == "".join("%s\t%f\n" % (k, v) for k, v in zip(mm["kmers"], p))
+
+
+@pytest.mark.gpu
+def test_TtestFilter_cli_poisson_mode(tmp_path):
+    """-l: Poisson likelihood ratio (TtestFilter.c:152-185); survivors print the RAW counts"""
+    import oracle_lib as orc
+    g = load_json("nf_cases.json")
+    mm = g["ttest_bigger_matrix"]
+    cnts = np.array(mm["counts"], np.int32)
+    counts = tmp_path / "counts.tsv.gz"
+    with gzip.open(counts, "wt") as f:
+        f.write("tag\t" + "\t".join(mm["names"]) + "\n")
+        for k, row in zip(mm["kmers"], mm["counts"]):
+            f.write(k + "\t" + "\t".join(map(str, row)) + "\n")
+    conds = tmp_path / "conds.tsv"
+    conds.write_text(g["ttest_conditions"])
+    raw = tmp_path / "raw_pvals.txt.gz"
+    r = run("TtestFilter", "-l", "-p", "0.5", "-r", str(raw), str(counts), str(conds), "A", "B", cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    p, mA, mB, fc, _ = orc.poisson_rows(cnts, [0, 1, 2], [3, 4, 5])
+    adj = orc.bh(p)
+    want = "tag\tpvalue\tmeanA\tmeanB\tlog2FC\t" + "\t".join(mm["names"]) + "\n"
+    for i in range(len(cnts)):
+        if adj[i] <= 0.5:
+            want += "%s\t%f\t%f\t%f\t%f" % (mm["kmers"][i], adj[i], mA[i], mB[i], fc[i])
+            want += "".join("\t%.2f" % float(cnts[i, j]) for j in range(6)) + "\n"
+    assert want.count("\n") > 1, "fixture must have survivors"
     assert r.stdout == want
     assert gzip.open(raw, "rt").read() == "".join("%s\t%f\n" % (k, v) for k, v in zip(mm["kmers"], p))

@@ -319,3 +319,38 @@ def test_bh_rank_slices_stitch_to_the_reference_adjustment(ctx):
     assert np.all(np.diff(sp) >= 0)
     got = np.minimum(1.0, F[np.searchsorted(sp, p, side="left")])
     np.testing.assert_allclose(got, want, rtol=1e-12)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("R,nA,nB", [(20000, 3, 3), (5000, 8, 8), (3000, 2, 5)])
+def test_poisson_rows_vs_oracle(ctx, R, nA, nB):
+    """TtestFilter -l (TtestFilter.c:152-185): raw p, log2FC, group totals, BH and survivors against the restatement,
+    including rows whose density underflows (the reference's 0.001 constant -> negative statistic -> p = 1)"""
+    rng = np.random.default_rng(R + nA)
+    S = nA + nB
+    base = rng.gamma(2.0, 15.0, size=(R, 1))
+    cnts = rng.poisson(base * rng.uniform(0.5, 2.0, size=(1, S))).astype(np.int32)
+    cnts[: R // 50, nA:] *= 6                                   # real effects
+    cnts[R // 50: R // 50 + 20, nA:] += 20000                   # extreme rows: density underflow path
+    cnts[-50:] = 0
+    idxA, idxB = list(range(nA)), list(range(nA, S))
+    m = ctx.matrix_from_host(cnts)
+    t, info = ctx.poisson_rows(m, idxA, idxB)
+    t.adjust(0.05)
+    t.filter(0.05, 0.0)
+    p, fc, adj = t.export_rows()
+    surv = t.export_survivors()
+    t.free(); m.free()
+    op, omA, omB, ofc, (N1, N2) = orc.poisson_rows(cnts, idxA, idxB)
+    assert (info[0], info[1]) == (N1, N2)
+    assert info[2] <= int((op == 1.0).sum())                    # negative statistics are reported as p = 1
+    np.testing.assert_allclose(p, op, rtol=1e-9, atol=1e-14)    # 1 - erf(): absolute accuracy near p = 0
+    np.testing.assert_allclose(fc, ofc, rtol=1e-9, atol=1e-12)
+    oadj = orc.bh(op)
+    near = np.abs(oadj - 0.05) <= 1e-9
+    keep = np.nonzero((oadj <= 0.05) & ~near)[0]
+    rows = surv["row"].astype(np.int64)
+    assert set(keep.tolist()) <= set(rows.tolist()) <= set(np.nonzero((oadj <= 0.05) | near)[0].tolist())
+    sel = np.isin(rows, keep)
+    np.testing.assert_allclose(surv["p_adj"][sel], oadj[rows[sel]], rtol=1e-9, atol=1e-13)
+    np.testing.assert_allclose(surv["norm"][sel], cnts[rows[sel]].astype(np.float64))

@@ -133,3 +133,23 @@ def test_bh_definition_and_ties():
     np.testing.assert_allclose(adj, want, rtol=1e-15)
     for v in np.unique(p):
         assert len(set(adj[p == v].tolist())) == 1
+
+
+def test_poisson_lr_vs_scipy():
+    """-l mode (TtestFilter.c:152-185): log-density at non-integer k, LR statistic, chi-squared(1) upper tail"""
+    from scipy import special, stats
+    rng = np.random.default_rng(3)
+    for _ in range(300):
+        K1, K2 = 1 + rng.gamma(2.0, 20.0), 1 + rng.gamma(2.0, 20.0)
+        N1, N2 = int(rng.integers(10**6, 10**9)), int(rng.integers(10**6, 10**9))
+        lp = lambda lam, k: -lam + k * np.log(lam) - special.gammaln(k + 1)
+        th = (K1 + K2) / (N1 + N2)
+        stat = 2 * ((lp(K1, K1) + lp(K2, K2)) - (lp(th * N1, K1) + lp(th * N2, K2)))
+        got = orc.poisson_lr(K1, K2, N1, N2)
+        want = stats.chi2.sf(max(stat, 0.0), 1)
+        assert abs(got - want) <= 1e-13 + 1e-9 * want * (want > 1e-6), (K1, K2, N1, N2, got, want)
+    # the reference forms 1 - cdf: tiny p-values bottom out at the double spacing near 1
+    assert orc.poisson_lr(5.0, 300.0, 10**8, 10**8) in (0.0, 1.1102230246251565e-16, 2.220446049250313e-16)
+    # density underflow: logpoisson returns the reference's constant 0.001 (TtestFilter.c:157-161), the statistic turns
+    # negative, Boost's chi-squared cdf throws and the reference aborts; the restatement (and the product) give p = 1
+    assert orc.poisson_lr(5.0, 5000.0, 10**8, 10**8) == 1.0
