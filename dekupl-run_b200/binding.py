@@ -56,6 +56,10 @@ def load_library():
         "dk_matrix_export": (i32, [vp, vp, u64, u64, vp, vp]),
         "dk_matrix_export_dev": (i32, [vp, vp, u64, u64, vp, vp]),
         "dk_matrix_checksum": (i32, [vp, vp, P(u64), P(u64)]), "dk_matrix_free": (None, [vp, vp]),
+        "dk_matrix_mask": (i32, [vp, vp, vp, u64, i32, P(vp), P(u64)]),
+        "dk_keys_antijoin": (i32, [vp, vp, u64, vp, u64, vp]),
+        "dk_run_path_masked": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, i32, P(i32), i32, P(i32), i32, dbl, dbl, i32,
+                                     vp, u64, i32, P(PathStats), P(u64), P(vp), P(vp)]),
         "dk_compute_nf": (i32, [vp, vp, i32, u64, P(dbl), P(u64)]),
         "dk_nf_begin": (i32, [vp, vp, P(vp), P(u64)]), "dk_nf_set_rank": (i32, [vp, vp, u64]),
         "dk_nf_hist_dev": (i32, [vp, vp, vp]), "dk_nf_advance_dev": (i32, [vp, vp, vp]),
@@ -237,6 +241,26 @@ class Context:
         self._chk(self.L.dk_matrix_from_host(self.h, S, R, _np_ptr(keys), _np_ptr(cnts), C.byref(out)))
         return Matrix(self, out)
 
+    # ---- reference-transcript mask (bin/diffFilter.pl) ---------------------------
+    def matrix_mask(self, m, mask_keys, mask_on_device=False, n_mask=None):
+        """rows of m whose k-mer is absent from the sorted mask; returns (Matrix, rows_removed).
+        mask_keys: numpy uint64 array, or a device pointer (int) with n_mask when mask_on_device"""
+        if mask_on_device:
+            ptr, n = C.c_void_p(int(mask_keys)), int(n_mask)
+        else:
+            mask_keys = np.ascontiguousarray(mask_keys, dtype=np.uint64)
+            ptr, n = _np_ptr(mask_keys), len(mask_keys)
+        out, removed = C.c_void_p(0), C.c_uint64(0)
+        self._chk(self.L.dk_matrix_mask(self.h, m.h, ptr, n, int(mask_on_device), C.byref(out), C.byref(removed)))
+        return Matrix(self, out), int(removed.value)
+
+    def keys_antijoin(self, keys, mask_keys):
+        keys = np.ascontiguousarray(keys, dtype=np.uint64)
+        mask_keys = np.ascontiguousarray(mask_keys, dtype=np.uint64)
+        keep = np.zeros(len(keys), np.uint8)
+        self._chk(self.L.dk_keys_antijoin(self.h, _np_ptr(keys), len(keys), _np_ptr(mask_keys), len(mask_keys), _np_ptr(keep)))
+        return keep.astype(bool)
+
     # ---- computeNF ------------------------------------------------------------
     def compute_nf(self, m, mode=NF_REFERENCE, step_rows=0):
         S = m.samples
@@ -262,15 +286,29 @@ class Context:
 
     # ---- whole path -----------------------------------------------------------
     def run_path(self, key_ptrs, cnt_ptrs, n, device_inputs, min_rec, min_abund, nf_mode, idxA, idxB, pmax, fmin,
-                 nf_text_roundtrip=True, keep=False):
+                 nf_text_roundtrip=True, keep=False, mask=None, mask_on_device=False, n_mask=None):
+        """mask: sorted uint64 k-mers of the reference transcripts (numpy array, or a device pointer with n_mask when
+        mask_on_device): RNA-Seq mode, NFs from the raw matrix and the test on the masked one (Snakefile:366,654)"""
         S, kp, cp, nn = self._tables(key_ptrs, cnt_ptrs, n)
         a, b = (C.c_int * len(idxA))(*idxA), (C.c_int * len(idxB))(*idxB)
         st = PathStats()
         om, ot = C.c_void_p(0), C.c_void_p(0)
-        self._chk(self.L.dk_run_path(self.h, S, kp, cp, nn, int(device_inputs), min_rec, min_abund, nf_mode, a, len(idxA), b,
-                                     len(idxB), float(pmax), float(fmin), int(nf_text_roundtrip), C.byref(st),
-                                     C.byref(om) if keep else None, C.byref(ot) if keep else None))
-        stats = dict(U=int(st.U), R=int(st.R), R_pos=int(st.R_pos), D=int(st.D), ties=tuple(int(x) for x in st.ties),
+        removed = C.c_uint64(0)
+        if mask is None:
+            self._chk(self.L.dk_run_path(self.h, S, kp, cp, nn, int(device_inputs), min_rec, min_abund, nf_mode, a, len(idxA), b,
+                                         len(idxB), float(pmax), float(fmin), int(nf_text_roundtrip), C.byref(st),
+                                         C.byref(om) if keep else None, C.byref(ot) if keep else None))
+        else:
+            if mask_on_device:
+                mp, mn = C.c_void_p(int(mask)), int(n_mask)
+            else:
+                mask = np.ascontiguousarray(mask, dtype=np.uint64)
+                mp, mn = _np_ptr(mask), len(mask)
+            self._chk(self.L.dk_run_path_masked(self.h, S, kp, cp, nn, int(device_inputs), min_rec, min_abund, nf_mode, a,
+                                                len(idxA), b, len(idxB), float(pmax), float(fmin), int(nf_text_roundtrip), mp, mn,
+                                                int(mask_on_device), C.byref(st), C.byref(removed),
+                                                C.byref(om) if keep else None, C.byref(ot) if keep else None))
+        stats = dict(rows_masked=int(removed.value), U=int(st.U), R=int(st.R), R_pos=int(st.R_pos), D=int(st.D), ties=tuple(int(x) for x in st.ties),
                      nf=np.array(st.nf[:S]), ms_join=st.ms_join, ms_nf=st.ms_nf, ms_ttest=st.ms_ttest, ms_bh=st.ms_bh)
         if keep:
             m = Matrix(self, om)

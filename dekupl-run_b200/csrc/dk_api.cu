@@ -310,12 +310,14 @@ static double nf_text_round(double v)
     return atof(buf);
 }
 
-extern "C" int dk_run_path(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
-                           int device_inputs, int min_rec, int min_abund, int nf_mode, const int *idxA, int nA,
-                           const int *idxB, int nB, double pmax, double fmin_, int nf_text_roundtrip, dk_path_stats *stats,
-                           dk_matrix **out_matrix, dk_ttest **out_test)
+static int run_path_impl(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                         int device_inputs, int min_rec, int min_abund, int nf_mode, const int *idxA, int nA,
+                         const int *idxB, int nB, double pmax, double fmin_, int nf_text_roundtrip, bool masked,
+                         const uint64_t *mask_keys, uint64_t n_mask, int mask_on_device, dk_path_stats *stats,
+                         uint64_t *rows_masked, dk_matrix **out_matrix, dk_ttest **out_test)
 {
     if (!ctx || !keys || !cnts || !n) return dk_fail(ctx, DK_ERR_ARG, "run_path: NULL argument");
+    if (rows_masked) *rows_masked = 0;
     if (out_matrix) *out_matrix = nullptr;
     if (out_test) *out_test = nullptr;
     dk_matrix *m = nullptr;
@@ -331,6 +333,14 @@ extern "C" int dk_run_path(dk_ctx *ctx, int S, const uint64_t *const *keys, cons
     rc = dk_compute_nf(ctx, m, nf_mode, 0, st.nf, info);
     if (rc != DK_OK) goto fail;
     st.R_pos = info[3]; st.ms_nf = ctx->stage_ms[1];
+    if (masked) {                       // NF saw the raw matrix (Snakefile:366); everything after sees the masked one
+        dk_matrix *mm = nullptr;
+        rc = dk_matrix_mask(ctx, m, mask_keys, n_mask, mask_on_device, &mm, rows_masked);
+        if (rc != DK_OK) goto fail;
+        dk_matrix_release(ctx, m);
+        m = mm;
+        if (m->R == 0) { rc = DK_OK; goto finish; }
+    }
     {
         double nf_used[DK_MAX_SAMPLES];
         for (int s = 0; s < S; s++) nf_used[s] = nf_text_roundtrip ? nf_text_round(st.nf[s]) : st.nf[s];
@@ -361,4 +371,24 @@ fail:
     dk_ttest_release(ctx, t);
     dk_matrix_release(ctx, m);
     return rc;
+}
+
+extern "C" int dk_run_path(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                           int device_inputs, int min_rec, int min_abund, int nf_mode, const int *idxA, int nA,
+                           const int *idxB, int nB, double pmax, double fmin_, int nf_text_roundtrip, dk_path_stats *stats,
+                           dk_matrix **out_matrix, dk_ttest **out_test)
+{
+    return run_path_impl(ctx, S, keys, cnts, n, device_inputs, min_rec, min_abund, nf_mode, idxA, nA, idxB, nB, pmax, fmin_,
+                         nf_text_roundtrip, false, nullptr, 0, 0, stats, nullptr, out_matrix, out_test);
+}
+
+extern "C" int dk_run_path_masked(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                                  int device_inputs, int min_rec, int min_abund, int nf_mode, const int *idxA, int nA,
+                                  const int *idxB, int nB, double pmax, double fmin_, int nf_text_roundtrip,
+                                  const uint64_t *mask_keys, uint64_t n_mask, int mask_on_device, dk_path_stats *stats,
+                                  uint64_t *rows_masked, dk_matrix **out_matrix, dk_ttest **out_test)
+{
+    if (n_mask && !mask_keys) return dk_fail(ctx, DK_ERR_ARG, "run_path_masked: NULL mask");
+    return run_path_impl(ctx, S, keys, cnts, n, device_inputs, min_rec, min_abund, nf_mode, idxA, nA, idxB, nB, pmax, fmin_,
+                         nf_text_roundtrip, true, mask_keys, n_mask, mask_on_device, stats, rows_masked, out_matrix, out_test);
 }

@@ -85,6 +85,18 @@ int dk_matrix_export_dev(dk_ctx *ctx, const dk_matrix *m, uint64_t row0, uint64_
 int dk_matrix_checksum(dk_ctx *ctx, const dk_matrix *m, uint64_t *key_xor, uint64_t *cnt_sum);
 void dk_matrix_free(dk_ctx *ctx, dk_matrix *m);
 
+/* ---- reference-transcript mask (replaces bin/diffFilter.pl:50-69, rule Snakefile:634-644) ----
+ * Sorted anti-join: *out = the rows of m whose k-mer does not occur in mask_keys (ascending,
+ * duplicates allowed; host buffer unless mask_on_device). m is left untouched: computeNF reads
+ * the raw matrix (Snakefile:366), TtestFilter the masked one (Snakefile:654). An unsorted mask
+ * or matrix is refused (the Perl script silently mis-joins). n_removed may be NULL. */
+int dk_matrix_mask(dk_ctx *ctx, const dk_matrix *m, const uint64_t *mask_keys, uint64_t n_mask,
+                   int mask_on_device, dk_matrix **out, uint64_t *n_removed);
+/* keys-only form for a caller that keeps the table rows itself (the diffFilter CLI prints the
+ * surviving text lines byte for byte): keep[i] = 1 iff keys[i] is absent from mask_keys. Host buffers. */
+int dk_keys_antijoin(dk_ctx *ctx, const uint64_t *keys, uint64_t n, const uint64_t *mask_keys,
+                     uint64_t n_mask, uint8_t *keep);
+
 /* ---- computeNF (replaces share/computeNF/computeNF.c:109-168) ---------------
  * mode DK_NF_REFERENCE: step_rows = rows per step (0 => the reference's 1,000,000).
  * info (may be NULL): info[0] = rows consumed, info[1] = steps evaluated,
@@ -156,6 +168,15 @@ int dk_run_path(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *
                 const int *idxA, int nA, const int *idxB, int nB, double pmax, double fmin,
                 int nf_text_roundtrip /* round NFs through "%f" like the pipeline does */,
                 dk_path_stats *stats, dk_matrix **out_matrix /* may be NULL */, dk_ttest **out_test /* may be NULL */);
+/* RNA-Seq mode (Snakefile:654): the same path with the mask between computeNF and TtestFilter.
+ * NFs come from the raw matrix; the t-test, BH and the survivors from the masked one, which is
+ * what *out_matrix receives. stats->R stays the raw row count; *rows_masked = rows the mask removed. */
+int dk_run_path_masked(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                       int device_inputs, int min_rec, int min_abund, int nf_mode,
+                       const int *idxA, int nA, const int *idxB, int nB, double pmax, double fmin,
+                       int nf_text_roundtrip, const uint64_t *mask_keys, uint64_t n_mask, int mask_on_device,
+                       dk_path_stats *stats, uint64_t *rows_masked /* may be NULL */,
+                       dk_matrix **out_matrix /* may be NULL */, dk_ttest **out_test /* may be NULL */);
 
 #ifdef __cplusplus
 }

@@ -64,6 +64,10 @@ double orc_poisson_lr(double K1, double K2, int64_t N1, int64_t N2);
 void orc_poisson_rows(const int32_t *cnts, size_t R, int S, const int *idxA, int nA, const int *idxB, int nB,
                       double *p_raw, double *meanA, double *meanB, double *log2fc, int64_t *N_out);
 
+/* bin/diffFilter.pl:50-69 (reference-transcript mask): keep[i] = 1 iff keys[i] is not in mask.
+ * Both ascending; returns the number of rows kept. */
+size_t orc_antijoin(const uint64_t *keys, size_t n, const uint64_t *mask, size_t n_mask, uint8_t *keep);
+
 /* TtestFilter.c:459-476: Benjamini-Hochberg, in place semantic on a copy. */
 void orc_bh(const double *p_raw, size_t R, double *p_adj);
 

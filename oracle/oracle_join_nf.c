@@ -120,3 +120,19 @@ void orc_nf_full(const int32_t *cnts, size_t R, int S, double *nf_out)
     for (int j = 0; j < S; j++) free(v[j].a);
     free(v);
 }
+
+/* bin/diffFilter.pl:50-69 restated on packed keys: one cursor over the (sorted) mask, advanced
+ * while it is below the current table k-mer (:59-66); the row is printed unless the cursor then
+ * sits on an equal k-mer (:67-69). For equal-length ACGT strings Perl's `lt`/`ne` are the integer
+ * compares used here. The cursor never moves back, so an unsorted input mis-joins exactly as the
+ * script does. */
+size_t orc_antijoin(const uint64_t *keys, size_t n, const uint64_t *mask, size_t n_mask, uint8_t *keep)
+{
+    size_t d = 0, kept = 0;
+    for (size_t i = 0; i < n; i++) {
+        while (d < n_mask && mask[d] < keys[i]) d++;
+        keep[i] = !(d < n_mask && mask[d] == keys[i]);
+        kept += keep[i];
+    }
+    return kept;
+}

@@ -12,6 +12,10 @@ Then the UNMODIFIED reference joinCounts and computeNF binaries (oracle/_ref) pr
 normalisation factors, and the oracle restatement of TtestFilter (Boost is absent) produces diff-counts.
 To keep the committed fixture small only the first NPAIRS read pairs of every sample are counted; the k-mer
 distribution is the real one (clustered keys, shared prefixes), which is what this fixture is for.
+The mask (default RNA-Seq mode, Snakefile:603-644) is the sorted `jellyfish count -m 31` dump (no -L, no -C for
+lib_type rf, Snakefile:608-615) of tests/gencode.v24.transcripts.head1000.fa, restated the same way; the UNMODIFIED
+bin/diffFilter.pl (perl is present) then produces masked-counts, and the TtestFilter restatement run on the masked
+matrix with the raw matrix's NFs (Snakefile:366,654) gives diff-counts-masked.
 Run in the build container:  make -C oracle && python tests/golden/make_config1.py"""
 import gzip
 import os
@@ -51,6 +55,36 @@ def count_sample(name):
                     continue
                 cnt[w] = cnt.get(w, 0) + 1
     return sorted((k, c) for k, c in cnt.items() if c >= 2)
+
+
+def count_transcripts(path):
+    seqs, cur = [], []
+    for l in open(path):
+        if l.startswith(">"):
+            if cur:
+                seqs.append("".join(cur))
+                cur = []
+        else:
+            cur.append(l.strip().upper())
+    if cur:
+        seqs.append("".join(cur))
+    cnt = {}
+    for s in seqs:
+        for i in range(len(s) - K + 1):
+            w = s[i:i + K]
+            if w.strip("ACGT"):
+                continue
+            cnt[w] = cnt.get(w, 0) + 1
+    return sorted(cnt.items())
+
+
+def diff_counts_text(names, kmers, cnts, nfa, p_adj, mA, mB, fc, pmax=0.2):
+    want = "tag\tpvalue\tmeanA\tmeanB\tlog2FC\t" + "\t".join(names) + "\n"
+    for i in range(len(cnts)):
+        if p_adj[i] <= pmax and abs(fc[i]) >= 0:
+            want += "%s\t%f\t%f\t%f\t%f" % (kmers[i], p_adj[i], mA[i], mB[i], fc[i])
+            want += "".join("\t%.2f" % (cnts[i, j] / nfa[j]) for j in range(len(names))) + "\n"
+    return want
 
 
 def main():
@@ -94,6 +128,21 @@ def main():
     with gzip.GzipFile(os.path.join(OUT, "raw_pvals.txt.gz"), "wb", mtime=0) as f:
         f.write("".join("%s\t%f\n" % (k, v) for k, v in zip(kmers, p)).encode())
     print("rows", len(cnts), "survivors", want.count("\n") - 1, "NF", nf)
+    # ---- mask: transcript dump -> real diffFilter.pl -> t-test on the masked matrix, NFs of the raw one
+    ref = os.path.join(OUT, "ref_transcripts.txt.gz")
+    with gzip.GzipFile(ref, "wb", mtime=0) as f:
+        f.write("".join(f"{k} {c}\n" for k, c in count_transcripts("/root/reference/tests/gencode.v24.transcripts.head1000.fa")).encode())
+    masked = subprocess.run(["perl", "/root/reference/bin/diffFilter.pl", ref, raw], check=True, capture_output=True).stdout
+    with gzip.GzipFile(os.path.join(OUT, "masked-counts.tsv.gz"), "wb", mtime=0) as f:
+        f.write(masked)
+    mrows = [l.split("\t") for l in masked.decode().strip().split("\n")[1:]]
+    mk = [r[0] for r in mrows]
+    mc = np.array([[int(x) for x in r[1:]] for r in mrows], np.int32)
+    p, mA, mB, fc = orc.ttest_rows(mc, nfa, [0, 1], [2, 3])
+    wantm = diff_counts_text(names, mk, mc, nfa, orc.bh(p), mA, mB, fc)
+    with gzip.GzipFile(os.path.join(OUT, "diff-counts-masked.tsv.gz"), "wb", mtime=0) as f:
+        f.write(wantm.encode())
+    print("masked rows", len(mc), "of", len(cnts), "survivors", wantm.count("\n") - 1)
     _ = enc
 
 

@@ -32,6 +32,8 @@ def load():
     L.orc_poisson_lr.argtypes = [dbl, dbl, C.c_int64, C.c_int64]
     L.orc_poisson_rows.restype = None
     L.orc_poisson_rows.argtypes = [vp, sz, i32, vp, i32, vp, i32, vp, vp, vp, vp, vp]
+    L.orc_antijoin.restype = sz
+    L.orc_antijoin.argtypes = [vp, sz, vp, sz, vp]
     L.orc_bh.restype = None
     L.orc_bh.argtypes = [vp, sz, vp]
     L.orc_filter.restype = sz
@@ -101,6 +103,16 @@ def poisson_rows(cnts, idxA, idxB):
 
 def poisson_lr(K1, K2, N1, N2):
     return load().orc_poisson_lr(float(K1), float(K2), int(N1), int(N2))
+
+
+def antijoin(keys, mask):
+    """keep flags of bin/diffFilter.pl: rows whose k-mer is absent from the sorted mask dump"""
+    L = load()
+    keys = np.ascontiguousarray(keys, dtype=np.uint64)
+    mask = np.ascontiguousarray(mask, dtype=np.uint64)
+    keep = np.zeros(len(keys), np.uint8)
+    L.orc_antijoin(keys.ctypes.data, len(keys), mask.ctypes.data, len(mask), keep.ctypes.data)
+    return keep.astype(bool)
 
 
 def bh(p):

@@ -38,6 +38,18 @@ def test_missing_input_file_fails_like_the_reference():
         assert r.returncode != 0 and "Failed to open /nonexistent/x" in r.stderr
 
 
+def test_diffFilter_argv_surface(tmp_path):
+    r = run("diffFilter")
+    assert r.returncode == 1 and "Usage:   diffFilter" in r.stderr and r.stdout == ""
+    r = run("diffFilter", "/nonexistent/ref.txt.gz", "/nonexistent/x.tsv")
+    assert r.returncode != 0 and "Cannot open /nonexistent/ref.txt.gz" in r.stderr       # diffFilter.pl:35,37
+    ref, tab = tmp_path / "ref.txt", tmp_path / "tab.tsv"
+    ref.write_text("ACGT 1\n")
+    tab.write_text("tag\ts1\nACGTN\t3\n")
+    r = run("diffFilter", str(ref), str(tab))
+    assert r.returncode != 0 and "at most 31 ACGT bases" in r.stderr and r.stdout == ""
+
+
 def test_poisson_flag_is_accepted_in_usage():
     r = run("TtestFilter", "-l")
     assert r.returncode == 1 and "-l        disregard the program name" in r.stderr

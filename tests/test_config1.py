@@ -85,3 +85,112 @@ def test_whole_path_on_real_dumps_matches_oracle(ctx):
     assert np.array_equal(surv["row"].astype(np.int64), keep)
     assert np.allclose(surv["p_adj"], adj[keep], rtol=1e-9)
     t.free(); m.free()
+
+
+# ---- reference-transcript mask (default RNA-Seq mode): bin/diffFilter.pl between computeNF and TtestFilter ----
+def _mask_keys():
+    return parse_dump_text(gzip.open(os.path.join(C1, "ref_transcripts.txt.gz"), "rt").read())[0]
+
+
+def _table(path):
+    rows = [l.split("\t") for l in gzip.open(path, "rt").read().strip().split("\n")[1:]]
+    from common import enc
+    return (np.array([enc(r[0]) for r in rows], np.uint64), np.array([[int(x) for x in r[1:]] for r in rows], np.int32),
+            [r[0] for r in rows])
+
+
+def test_oracle_antijoin_equals_diffFilter_pl_output():
+    """masked-counts.tsv.gz was written by the UNMODIFIED bin/diffFilter.pl (make_config1.py)"""
+    import oracle_lib as orc
+    rk, rc, _ = _table(os.path.join(C1, "raw-counts.tsv.gz"))
+    mk, mc, _ = _table(os.path.join(C1, "masked-counts.tsv.gz"))
+    keep = orc.antijoin(rk, _mask_keys())
+    assert 0 < keep.sum() < len(rk)
+    assert np.array_equal(rk[keep], mk) and np.array_equal(rc[keep], mc)
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/bin/diffFilter.pl"), reason="reference tree absent")
+def test_oracle_antijoin_equals_diffFilter_pl_live(tmp_path):
+    """edge cases through the real script: empty mask, mask past the table's end, duplicates on either side"""
+    import oracle_lib as orc
+    from common import dec
+    rng = np.random.default_rng(5)
+    for trial in range(6):
+        keys = np.sort(rng.integers(0, 400, 120 if trial else 1).astype(np.uint64))
+        mask = np.sort(rng.integers(0, 500, [0, 40, 200, 3, 80, 80][trial]).astype(np.uint64))
+        ref, tab = tmp_path / f"ref{trial}.txt", tmp_path / f"tab{trial}.tsv"
+        ref.write_text("".join(f"{dec(int(k), 9)} 1\n" for k in mask))
+        tab.write_text("tag\ts1\n" + "".join(f"{dec(int(k), 9)}\t{i}\n" for i, k in enumerate(keys)))
+        if len(mask) == 0:
+            continue                    # the script reads an undefined first line (warnings); behaviour covered by keep-all below
+        r = subprocess.run(["perl", "/root/reference/bin/diffFilter.pl", str(ref), str(tab)], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        keep = orc.antijoin(keys, mask)
+        want = "tag\ts1\n" + "".join(f"{dec(int(k), 9)}\t{i}\n" for i, k in enumerate(keys) if keep[i])
+        assert r.stdout == want
+    assert orc.antijoin(np.arange(5, dtype=np.uint64), np.zeros(0, np.uint64)).all()
+
+
+@pytest.mark.gpu
+def test_matrix_mask_and_keys_antijoin_on_config1(ctx):
+    rk, rc, _ = _table(os.path.join(C1, "raw-counts.tsv.gz"))
+    mk, mc, _ = _table(os.path.join(C1, "masked-counts.tsv.gz"))
+    mask = _mask_keys()
+    m = ctx.matrix_from_host(rc, rk)
+    mm, removed = ctx.matrix_mask(m, mask)
+    gk, gc = mm.export()
+    assert removed == len(rk) - len(mk) and np.array_equal(gk, mk) and np.array_equal(gc, mc)
+    gk0, gc0 = m.export()                                                # the raw matrix is untouched (computeNF reads it)
+    assert np.array_equal(gk0, rk) and np.array_equal(gc0, rc)
+    keep = ctx.keys_antijoin(rk, mask)
+    assert np.array_equal(rk[keep], mk)
+    mm.free(); m.free()
+
+
+@pytest.mark.gpu
+def test_diffFilter_cli_reproduces_masked_counts_bytes():
+    r = subprocess.run([os.path.join(BIN, "diffFilter"), os.path.join(C1, "ref_transcripts.txt.gz"),
+                        os.path.join(C1, "raw-counts.tsv.gz")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert r.stdout == gzip.open(os.path.join(C1, "masked-counts.tsv.gz"), "rt").read()
+
+
+@pytest.mark.gpu
+def test_masked_pipeline_clis_reproduce_diff_counts_masked(tmp_path):
+    """Snakefile:634-672: diffFilter.pl | gzip -> TtestFilter on the masked table with the raw table's NFs"""
+    r = subprocess.run([os.path.join(BIN, "diffFilter"), os.path.join(C1, "ref_transcripts.txt.gz"),
+                        os.path.join(C1, "raw-counts.tsv.gz")], capture_output=True)
+    assert r.returncode == 0, r.stderr
+    masked = tmp_path / "masked-counts.tsv.gz"
+    masked.write_bytes(gzip.compress(r.stdout))
+    r = subprocess.run([os.path.join(BIN, "TtestFilter"), "-p", "0.2", "-f", "0", str(masked),
+                        os.path.join(C1, "sample_conditions_full.tsv"), "A", "B"], capture_output=True, text=True, cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    assert r.stdout == gzip.open(os.path.join(C1, "diff-counts-masked.tsv.gz"), "rt").read()
+
+
+@pytest.mark.gpu
+def test_whole_path_masked_on_real_dumps_matches_oracle(ctx):
+    import dekupl_run_b200 as dk
+    import oracle_lib as orc
+    d = _dumps()
+    keys, cnts = [x[0] for x in d], [x[1] for x in d]
+    mask = _mask_keys()
+    stats, m, t = ctx.run_path([k.ctypes.data for k in keys], [c.ctypes.data for c in cnts], [len(k) for k in keys], False, 2, 5,
+                               dk.NF_REFERENCE, [0, 1], [2, 3], 0.2, 0.0, nf_text_roundtrip=True, keep=True, mask=mask)
+    ok, oc, oU = orc.join(keys, cnts, 2, 5)
+    keep = orc.antijoin(ok, mask)
+    gk, gc = m.export()
+    assert stats["R"] == len(ok) and stats["rows_masked"] == int((~keep).sum())
+    assert np.array_equal(gk, ok[keep]) and np.array_equal(gc, oc[keep])
+    nf_raw = orc.nf_reference(oc)[0]                                     # NFs of the RAW matrix (Snakefile:366)
+    assert np.allclose(stats["nf"], nf_raw, rtol=1e-12)
+    nf = np.array([float("%f" % v) for v in nf_raw])
+    p, _, _, fc = orc.ttest_rows(oc[keep], nf, [0, 1], [2, 3])
+    adj = orc.bh(p)
+    surv = t.export_survivors()
+    want = np.nonzero(adj <= 0.2)[0]
+    assert np.array_equal(surv["row"].astype(np.int64), want)
+    assert np.allclose(surv["p_adj"], adj[want], rtol=1e-9)
+    assert np.array_equal(surv["key"], ok[keep][want])
+    t.free(); m.free()

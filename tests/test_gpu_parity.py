@@ -354,3 +354,54 @@ def test_poisson_rows_vs_oracle(ctx, R, nA, nB):
     sel = np.isin(rows, keep)
     np.testing.assert_allclose(surv["p_adj"][sel], oadj[rows[sel]], rtol=1e-9, atol=1e-13)
     np.testing.assert_allclose(surv["norm"][sel], cnts[rows[sel]].astype(np.float64))
+
+
+# ------------------------------------------------- reference-transcript mask (diffFilter.pl) ---
+@pytest.mark.parametrize("S,n_union,frac_mask,extra", [(4, 60000, 0.3, 50000), (16, 200000, 0.1, 400000), (1, 5000, 0.5, 10),
+                                                      (33, 40000, 0.9, 0), (3, 3000, 0.0, 100000)])
+def test_matrix_mask_on_join_output_vs_oracle(ctx, S, n_union, frac_mask, extra):
+    """the join leaves a chunked matrix (physical chunks in arbitrary order); the mask reads it in logical order"""
+    rng = np.random.default_rng(S * 77 + n_union)
+    keys, cnts = random_dumps(rng, S, n_union, 62, 0.4, 12, p_core=0.2)
+    m = ctx.join_counts(keys, cnts, 1, 1)
+    gk, gc = m.export()
+    hit = gk[rng.random(len(gk)) < frac_mask]
+    mask = np.sort(np.concatenate([hit, hit[: len(hit) // 7], rng.integers(0, 1 << 62, extra, dtype=np.uint64)]))  # with duplicates
+    keep = orc.antijoin(gk, mask)
+    mm, removed = ctx.matrix_mask(m, mask)
+    k2, c2 = mm.export()
+    assert removed == int((~keep).sum()) and mm.rows == int(keep.sum())
+    np.testing.assert_array_equal(k2, gk[keep])
+    np.testing.assert_array_equal(c2, gc[keep])
+    np.testing.assert_array_equal(ctx.keys_antijoin(gk, mask), keep)
+    # a masked matrix is an ordinary matrix: NF and the t-test run on it
+    if S >= 4 and mm.rows:
+        nf, _ = ctx.compute_nf(mm, dk.NF_FULL)
+        np.testing.assert_allclose(nf, orc.nf_full(c2), rtol=RTOL)
+    mm.free(); m.free()
+
+
+def test_matrix_mask_edges(ctx):
+    cn = np.arange(12, dtype=np.int32).reshape(6, 2)
+    ks = np.array([1, 5, 5, 9, 2 ** 62 - 1, 2 ** 64 - 1], np.uint64)         # duplicates in the table, an all-ones key
+    m = ctx.matrix_from_host(cn, ks)
+    for mask in ([], [0], [5], [1, 5, 9], [2 ** 64 - 1], [0, 2, 3, 2 ** 63], list(ks)):
+        mask = np.array(mask, np.uint64)
+        keep = orc.antijoin(ks, mask)
+        mm, removed = ctx.matrix_mask(m, mask)
+        k2, c2 = mm.export() if mm.rows else (np.zeros(0, np.uint64), np.zeros((0, 2), np.int32))
+        assert removed == int((~keep).sum())
+        np.testing.assert_array_equal(k2, ks[keep])
+        np.testing.assert_array_equal(c2.reshape(-1, 2), cn[keep])
+        mm.free()
+    with pytest.raises(dk.DkError, match="not sorted"):
+        ctx.matrix_mask(m, np.array([9, 5, 1], np.uint64))
+    m.free()
+    e = ctx.matrix_from_host(np.zeros((0, 2), np.int32), np.zeros(0, np.uint64))
+    mm, removed = ctx.matrix_mask(e, np.array([1, 2], np.uint64))
+    assert mm.rows == 0 and removed == 0
+    mm.free(); e.free()
+    u = ctx.matrix_from_host(cn[:3], np.array([7, 3, 5], np.uint64))
+    with pytest.raises(dk.DkError, match="not sorted"):
+        ctx.matrix_mask(u, np.array([1, 2], np.uint64))
+    u.free()
