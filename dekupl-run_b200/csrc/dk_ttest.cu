@@ -73,8 +73,12 @@ __device__ double dk_welch_p(double m1, double m2, int n1, int n2, double sd1, d
     return dk_student_t_2tail(fabs(t), df);
 }
 
-#define TT_THREADS 128
-// group moments of one row; la scratch is [n][TT_THREADS] in shared memory (conflict-free columns)
+#define TT_THREADS 1024          // launch bound; the host picks the block size (a multiple of DK_CH) per job
+#define TT_PO_THREADS 128        // Poisson rows kernel
+#ifndef TT_TAB_BYTES
+#define TT_TAB_BYTES 65536       // (a, l) tables per CTA
+#endif
+// group moments of one row; la scratch is [n][blockDim.x] in shared memory (conflict-free columns)
 // c/nf as the reference computes it (TtestFilter.c:380-382), without a per-element fp64 division:
 // with r = RN(1/nf), two Newton corrections through exact fma residuals give the correctly rounded
 // quotient (Markstein); the result is a deterministic function of (c, nf), which is all the
@@ -104,6 +108,7 @@ __device__ __noinline__ void dk_group_moments(const int32_t *c, const double *nf
                                               const double2 *tab, uint32_t TN, double *la, double &meanv, double &mlog, double &sd)
 {
     double sa = 0, sl = 0;
+    const uint32_t T = blockDim.x;
     for (int i = 0; i < n; i++) {
         const int k = idx[i];
         const int32_t cc = c[k];
@@ -111,12 +116,12 @@ __device__ __noinline__ void dk_group_moments(const int32_t *c, const double *nf
         if ((uint32_t)cc < TN) { const double2 t = tab[(uint32_t)k * TN + (uint32_t)cc]; a = t.x; l = t.y; }
         else dk_norm_log<FASTDIV>(cc, nf[k], rnf[k], a, l);
         sa += a; sl += l;                                // sum() :77-84
-        la[i * TT_THREADS] = l;
+        la[i * T] = l;
     }
     meanv = sa / n;                                      // mean() :87-89
     mlog = sl / n;
     double s = 0;
-    for (int i = 0; i < n; i++) { double d = la[i * TT_THREADS] - mlog; s += d * d; }   // sd() :91-98, pow(d,2)==d*d
+    for (int i = 0; i < n; i++) { double d = la[i * T] - mlog; s += d * d; }   // sd() :91-98, pow(d,2)==d*d
     sd = sqrt(s / (n - 1));
 }
 
@@ -128,15 +133,16 @@ k_ttest_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, 
 {
     extern __shared__ __align__(16) unsigned char sm[];
     int nmax = nA > nB ? nA : nB;
+    const uint32_t T = blockDim.x, cpb = T / DK_CH;              // block size chosen by the host; chunks per block
     double2 *tab = (double2 *)sm;                                // [S][TN] (a, l)
-    double *la = (double *)(tab + (size_t)S * TN);               // [nmax][TT_THREADS]
-    double *nf = la + (size_t)nmax * TT_THREADS;                 // [S]
+    double *la = (double *)(tab + (size_t)S * TN);               // [nmax][T]
+    double *nf = la + (size_t)nmax * T;                          // [S]
     double *rnf = nf + S;                                        // [S] RN(1/nf)
     int *idx = (int *)(rnf + S);                                 // [nA+nB]
-    for (int i = threadIdx.x; i < S; i += TT_THREADS) { nf[i] = nf_g[i]; rnf[i] = 1.0 / nf_g[i]; }
-    for (int i = threadIdx.x; i < nA + nB; i += TT_THREADS) idx[i] = idx_g[i];
+    for (int i = threadIdx.x; i < S; i += T) { nf[i] = nf_g[i]; rnf[i] = 1.0 / nf_g[i]; }
+    for (int i = threadIdx.x; i < nA + nB; i += T) idx[i] = idx_g[i];
     __syncthreads();
-    for (uint32_t e = threadIdx.x; e < (uint32_t)S * TN; e += TT_THREADS) {
+    for (uint32_t e = threadIdx.x; e < (uint32_t)S * TN; e += T) {
         const uint32_t k = e / TN, cc = e - k * TN;
         double a, l;
         dk_norm_log<FASTDIV>((int32_t)cc, nf[k], rnf[k], a, l);
@@ -144,10 +150,10 @@ k_ttest_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, 
     }
     __syncthreads();
     double *myla = la + threadIdx.x;
-    const uint32_t nblk = (n_chunks + (TT_THREADS / DK_CH) - 1) / (TT_THREADS / DK_CH);
+    const uint32_t nblk = (n_chunks + cpb - 1) / cpb;
     unsigned long long ties = 0;
     for (uint32_t blk = blockIdx.x; blk < nblk; blk += gridDim.x) {      // persistent: the tables are built once per CTA
-        const uint32_t oc = blk * (TT_THREADS / DK_CH) + threadIdx.x / DK_CH;
+        const uint32_t oc = blk * cpb + threadIdx.x / DK_CH;
         const uint32_t j = threadIdx.x % DK_CH;
         if (oc >= n_chunks) continue;
         const uint64_t b0 = lbase[oc], b1 = lbase[oc + 1];
@@ -206,22 +212,34 @@ extern "C" int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf, 
     DK_CUDA(ctx, cudaMemsetAsync(t->tie_counts, 0, 64, st));
     DK_CUDA(ctx, cudaStreamSynchronize(st));          // idx is a local staging vector
     int nmax = nA > nB ? nA : nB;
-    // (a, l) tables: the largest power of two of entries per sample within 32 KB
-    uint32_t TN = 0;
-    for (uint32_t t = 4; t <= 1024 && (size_t)16 * S * t <= 32768; t <<= 1) TN = t;
-    size_t smem = (size_t)16 * S * TN + sizeof(double) * ((size_t)nmax * TT_THREADS + 2 * S) + sizeof(int) * (nA + nB);
+    // Block size and (a, l) table size. The kernel is latency-bound (dependent fp64 chains, scattered count loads:
+    // r01j ncu), so resident warps matter most: take the largest block whose per-thread scratch (nmax doubles) still
+    // leaves room for a useful table (>= 32 counts per sample, up to TT_TAB_BYTES).
+    uint32_t TN = 0, T = 0;
+    size_t smem = 0;
+    const size_t budget = ctx->smem_optin ? ctx->smem_optin : 200 * 1024;
+    for (uint32_t want = 32; want >= 4 && !T; want >>= 3)            // second pass: any table at all (very wide matrices)
+        for (uint32_t tt = 1024; tt >= 64 && !T; tt >>= 1) {
+            const size_t fixed = sizeof(double) * ((size_t)nmax * tt + 2 * S) + sizeof(int) * (nA + nB) + 1024;
+            if (fixed >= budget) continue;
+            size_t tabmax = budget - fixed < TT_TAB_BYTES ? budget - fixed : TT_TAB_BYTES;
+            uint32_t tn = 0;
+            for (uint32_t t = 4; t <= 1024 && (size_t)16 * S * t <= tabmax; t <<= 1) tn = t;
+            if (tn >= want) { T = tt; TN = tn; smem = fixed - 1024 + (size_t)16 * S * tn; }
+        }
+    if (!T) { dk_ttest_release(ctx, t); return dk_fail(ctx, DK_ERR_UNSUPPORTED, "ttest: %d samples per group exceed shared memory", nmax); }
     bool fastdiv = true;                                // reciprocal path needs normal, moderate factors
     for (int s = 0; s < S; s++) if (!(nf[s] >= 1e-30 && nf[s] <= 1e30)) fastdiv = false;
     auto kfn = fastdiv ? k_ttest_rows<true> : k_ttest_rows<false>;
     DK_CUDA(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     uint32_t nch = (uint32_t)m->n_chunks;
     if (nch) {
-        unsigned grid = (nch + (TT_THREADS / DK_CH) - 1) / (TT_THREADS / DK_CH);
+        unsigned grid = (nch + (T / DK_CH) - 1) / (T / DK_CH);
         int per_sm = 1;
-        DK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, TT_THREADS, smem));
+        DK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, (int)T, smem));
         if (per_sm < 1) per_sm = 1;
         if (grid > (unsigned)(ctx->sm_count * per_sm)) grid = (unsigned)(ctx->sm_count * per_sm);
-        kfn<<<grid, TT_THREADS, smem, st>>>(m->cnts, m->order, m->lbase, nch, S, t->nf_dev, t->idx_dev, nA, nB, TN,
+        kfn<<<grid, T, smem, st>>>(m->cnts, m->order, m->lbase, nch, S, t->nf_dev, t->idx_dev, nA, nB, TN,
                                                      t->p_raw, t->log2fc, (unsigned long long *)(t->tie_counts + 2));
         DK_LAUNCHED(ctx);
     }
@@ -259,11 +277,11 @@ __device__ double dk_logpoisson(double lambda, double k)
     if (t <= 0) return 0.001;
     return log(t);
 }
-__global__ void __launch_bounds__(TT_THREADS)
+__global__ void __launch_bounds__(TT_PO_THREADS)
 k_poisson_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, uint32_t n_chunks, int S, const int *idx_g,
                int nA, int nB, const unsigned long long *tot, double *p_raw, double *log2fc, unsigned long long *neg_stat)
 {
-    const uint32_t oc = blockIdx.x * (TT_THREADS / DK_CH) + threadIdx.x / DK_CH, j = threadIdx.x % DK_CH;
+    const uint32_t oc = blockIdx.x * (TT_PO_THREADS / DK_CH) + threadIdx.x / DK_CH, j = threadIdx.x % DK_CH;
     if (oc >= n_chunks) return;
     const uint64_t b0 = lbase[oc];
     if (j >= lbase[oc + 1] - b0) return;
@@ -317,8 +335,8 @@ extern "C" int dk_poisson_rows(dk_ctx *ctx, const dk_matrix *m, const int *idxA,
     if (nch) {
         unsigned g1 = nch < (unsigned)ctx->sm_count * 8 ? nch : (unsigned)ctx->sm_count * 8;
         k_group_totals<<<g1, 256, 0, st>>>(m->cnts, m->order, m->lbase, nch, S, t->idx_dev, nA, nB, tot); DK_LAUNCHED(ctx);
-        unsigned grid = (nch + (TT_THREADS / DK_CH) - 1) / (TT_THREADS / DK_CH);
-        k_poisson_rows<<<grid, TT_THREADS, 0, st>>>(m->cnts, m->order, m->lbase, nch, S, t->idx_dev, nA, nB, tot, t->p_raw, t->log2fc,
+        unsigned grid = (nch + (TT_PO_THREADS / DK_CH) - 1) / (TT_PO_THREADS / DK_CH);
+        k_poisson_rows<<<grid, TT_PO_THREADS, 0, st>>>(m->cnts, m->order, m->lbase, nch, S, t->idx_dev, nA, nB, tot, t->p_raw, t->log2fc,
                                                    tot + 2);
         DK_LAUNCHED(ctx);
     }
