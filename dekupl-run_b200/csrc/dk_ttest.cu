@@ -73,7 +73,12 @@ __device__ double dk_welch_p(double m1, double m2, int n1, int n2, double sd1, d
     return dk_student_t_2tail(fabs(t), df);
 }
 
+#ifndef TT_THREADS
 #define TT_THREADS 1024          // launch bound; the host picks the block size (a multiple of DK_CH) per job
+#endif
+#ifndef TT_MINB
+#define TT_MINB 1
+#endif
 #define TT_PO_THREADS 128        // Poisson rows kernel
 #ifndef TT_TAB_BYTES
 #define TT_TAB_BYTES 65536       // (a, l) tables per CTA
@@ -126,7 +131,7 @@ __device__ __noinline__ void dk_group_moments(const int32_t *c, const double *nf
 }
 
 template <bool FASTDIV>
-__global__ void __launch_bounds__(TT_THREADS)
+__global__ void __launch_bounds__(TT_THREADS, TT_MINB)
 k_ttest_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, uint32_t n_chunks, int S,
              const double *nf_g, const int *idx_g, int nA, int nB, uint32_t TN, double *p_raw, double *log2fc,
              unsigned long long *tie_sd)
@@ -217,9 +222,10 @@ extern "C" int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf, 
     // leaves room for a useful table (>= 32 counts per sample, up to TT_TAB_BYTES).
     uint32_t TN = 0, T = 0;
     size_t smem = 0;
-    const size_t budget = ctx->smem_optin ? ctx->smem_optin : 200 * 1024;
+    size_t budget = ctx->smem_optin ? ctx->smem_optin : 200 * 1024;
+    if (TT_MINB > 1) budget = (budget + 1024) / TT_MINB - 1024;      // TT_MINB blocks share the SM (1 KB reserved per block)
     for (uint32_t want = 32; want >= 4 && !T; want >>= 3)            // second pass: any table at all (very wide matrices)
-        for (uint32_t tt = 1024; tt >= 64 && !T; tt >>= 1) {
+        for (uint32_t tt = TT_THREADS; tt >= 64 && !T; tt = tt > 1024 ? 1024 : (tt & (tt - 1)) ? 512 : tt >> 1) {
             const size_t fixed = sizeof(double) * ((size_t)nmax * tt + 2 * S) + sizeof(int) * (nA + nB) + 1024;
             if (fixed >= budget) continue;
             size_t tabmax = budget - fixed < TT_TAB_BYTES ? budget - fixed : TT_TAB_BYTES;
