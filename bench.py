@@ -281,7 +281,7 @@ def run_ours(args):
                    "gen_s": round(t_gen, 1), "ties": list(stats["ties"])},
         "gpu_launches": int(launches),
         "stage_ms": {"join": stage_avg[0], "merge_kernel": mk, "nf": stage_avg[1], "ttest": stage_avg[2],
-                     "bh_filter": stage_avg[3], **({"note": "rank 0; bh_filter = step - other stages (includes the collectives)"}
+                     "bh_filter": stage_avg[3], **({"note": "rank 0; bh_filter = step - other stages (includes the collectives" + (" and the all-reduced NF select)" if args.nf == "full" else ")")}
                                                    if world > 1 else {})},
         "roofline": {"bound": "hbm", "kernel": "k_merge3 (k-way merge + recurrence filter, joinCounts.c:72-115)", "achieved": ach, "peak": peak,
                      "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)",
