@@ -55,6 +55,7 @@ def load_library():
         "dk_matrix_rows": (u64, [vp]), "dk_matrix_union": (u64, [vp]), "dk_matrix_samples": (i32, [vp]),
         "dk_matrix_export": (i32, [vp, vp, u64, u64, vp, vp]),
         "dk_matrix_export_dev": (i32, [vp, vp, u64, u64, vp, vp]),
+        "dk_matrix_format_rows": (i32, [vp, vp, u64, u64, i32, vp, u64, P(u64)]),
         "dk_matrix_checksum": (i32, [vp, vp, P(u64), P(u64)]), "dk_matrix_free": (None, [vp, vp]),
         "dk_matrix_mask": (i32, [vp, vp, vp, u64, i32, P(vp), P(u64)]),
         "dk_keys_antijoin": (i32, [vp, vp, u64, vp, u64, vp]),
@@ -111,6 +112,15 @@ class Matrix:
         c = np.empty((n, self.samples), dtype=np.int32)
         self.ctx._chk(self.ctx.L.dk_matrix_export(self.ctx.h, self.h, row0, n, _np_ptr(k), _np_ptr(c)))
         return k, c
+
+    def format_rows(self, k, row0=0, nrows=None):
+        """the text joinCounts prints for these rows (joinCounts.c:105-109), formatted on the device"""
+        n = self.rows - row0 if nrows is None else nrows
+        cap = n * (k + 1 + 12 * self.samples) + 16
+        buf = np.empty(cap, dtype=np.uint8)
+        ln = C.c_uint64(0)
+        self.ctx._chk(self.ctx.L.dk_matrix_format_rows(self.ctx.h, self.h, row0, n, k, _np_ptr(buf), cap, C.byref(ln)))
+        return buf[: ln.value].tobytes()
 
     def checksum(self):
         x, s = C.c_uint64(0), C.c_uint64(0)

@@ -5,6 +5,9 @@
 // reference accepts any string); an empty input file is an empty sample (the reference
 // segfaults, joinCounts.c:59-61). No CPU fallback: without a GPU the tool exits non-zero.
 #include <unistd.h>
+#include <algorithm>
+#include <atomic>
+#include <thread>
 #include "../../include/dekupl_b200.h"
 #include "dk_text.h"
 
@@ -29,29 +32,39 @@ int main(int argc, char *argv[])
     if (S > DK_MAX_SAMPLES) { fprintf(stderr, "joinCounts: at most %d input files are supported\n", DK_MAX_SAMPLES); return EXIT_FAILURE; }
     std::vector<std::vector<uint64_t>> keys(S);
     std::vector<std::vector<int32_t>> cnts(S);
-    int k = 0;
-    for (int i = 0; i < S; i++) {
+    // every dump is inflated and parsed on its own thread (the text side is the CLI's bottleneck);
+    // diagnostics are reported afterwards for the first failing file in argv order, as a sequential reader would
+    std::vector<int> kk(S, 0), status(S, 0);              // status: 0 ok, 1 cannot open, 2 parse error (message in err)
+    std::vector<std::string> err(S);
+    auto parse_one = [&](int i) {
         const char *path = argv[optind + i];
         DkFile f;
-        if (!f.load(path)) { fprintf(stderr, "Failed to open %s\n", path); exit(EXIT_FAILURE); }   // joinCounts.c:52
+        if (!f.load(path)) { status[i] = 1; return; }     // joinCounts.c:52
         DkCursor cur(f);
         const char *s;
         size_t len;
         bool first = true;
+        int k = 0;
         keys[i].reserve(f.size() / 34 + 16);
         cnts[i].reserve(f.size() / 34 + 16);
         // joinCounts.c:55-68 (first record: skip the rest of its line) and :86-92 (then strictly token pairs)
         while (cur.token(s, len)) {
             if (len == 0 && cur.eof()) break;
-            if (len == 0) { if (!first) break; }        // ks_getuntil(...) > 0 fails on an empty token: input ends (:86)
+            if (len == 0) { if (!first) break; }          // ks_getuntil(...) > 0 fails on an empty token: input ends (:86)
             uint64_t key;
+            char msg[256];
             if (!dk_encode(s, len, key)) {
-                fprintf(stderr, "joinCounts: %s: record %zu: k-mer '%.*s' is not 1..31 ACGT bases (unsupported by the GPU path)\n", path,
-                        keys[i].size() + 1, (int)len, s);
-                return EXIT_FAILURE;
+                snprintf(msg, sizeof msg, "joinCounts: %s: record %zu: k-mer '%.*s' is not 1..31 ACGT bases (unsupported by the GPU path)",
+                         path, keys[i].size() + 1, (int)(len > 64 ? 64 : len), s);
+                status[i] = 2; err[i] = msg;
+                return;
             }
             if (k == 0) k = (int)len;
-            if ((int)len != k) { fprintf(stderr, "joinCounts: %s: mixed k-mer lengths (%d and %zu)\n", path, k, len); return EXIT_FAILURE; }
+            if ((int)len != k) {
+                snprintf(msg, sizeof msg, "joinCounts: %s: mixed k-mer lengths (%d and %zu)", path, k, len);
+                status[i] = 2; err[i] = msg;
+                return;
+            }
             const char *cs = "";
             size_t cl = 0;
             if (cur.dret != 0) cur.token(cs, cl);
@@ -59,6 +72,23 @@ int main(int argc, char *argv[])
             cnts[i].push_back(dk_atoi(cs, cl));
             if (first) { cur.skip_line(); first = false; }
         }
+        kk[i] = k;
+    };
+    {
+        unsigned hw = std::thread::hardware_concurrency();
+        const int nthr = std::max(1, std::min(S, (int)(hw ? hw : 4)));
+        std::atomic<int> next(0);
+        std::vector<std::thread> pool;
+        for (int t = 0; t < nthr; t++)
+            pool.emplace_back([&] { for (int i; (i = next.fetch_add(1)) < S;) parse_one(i); });
+        for (auto &t : pool) t.join();
+    }
+    int k = 0;
+    for (int i = 0; i < S; i++) {
+        if (status[i] == 1) { fprintf(stderr, "Failed to open %s\n", argv[optind + i]); exit(EXIT_FAILURE); }
+        if (status[i] == 2) { fprintf(stderr, "%s\n", err[i].c_str()); return EXIT_FAILURE; }
+        if (kk[i] && k == 0) k = kk[i];
+        if (kk[i] && kk[i] != k) { fprintf(stderr, "joinCounts: %s: mixed k-mer lengths (%d and %d)\n", argv[optind + i], k, kk[i]); return EXIT_FAILURE; }
     }
     dk_ctx *ctx = nullptr;
     if (dk_init(&ctx, 0) != DK_OK) { fprintf(stderr, "joinCounts: %s\n", dk_last_error(nullptr)); return EXIT_FAILURE; }
@@ -74,20 +104,17 @@ int main(int argc, char *argv[])
     uint64_t R = dk_matrix_rows(m);
     DkOut out;
     out.fp = stdout;
+    // rows are formatted on the device (dk_matrix_format_rows), one block at a time; the host only writes bytes
     const uint64_t BLK = 1 << 20;
-    std::vector<uint64_t> rk(BLK);
-    std::vector<int32_t> rc(BLK * (size_t)S);
-    char kbuf[32];
+    std::vector<char> text((size_t)BLK * ((size_t)k + 2 + 12 * (size_t)S) + 64);
     for (uint64_t r0 = 0; r0 < R; r0 += BLK) {
-        uint64_t nr = R - r0 < BLK ? R - r0 : BLK;
-        if (dk_matrix_export(ctx, m, r0, nr, rk.data(), rc.data()) != DK_OK) { fprintf(stderr, "joinCounts: %s\n", dk_last_error(ctx)); return EXIT_FAILURE; }
-        for (uint64_t r = 0; r < nr; r++) {               // joinCounts.c:105-109
-            dk_decode(rk[r], k, kbuf);
-            out.put(kbuf, (size_t)k);
-            for (int s = 0; s < S; s++) { out.putc_('\t'); out.put_int(rc[r * S + s]); }
-            out.putc_('\n');
-            if (out.b.size() > (1 << 22) - 8192) out.flush();
+        uint64_t nr = R - r0 < BLK ? R - r0 : BLK, len = 0;
+        if (dk_matrix_format_rows(ctx, m, r0, nr, k, text.data(), text.size(), &len) != DK_OK) {   // joinCounts.c:105-109
+            fprintf(stderr, "joinCounts: %s\n", dk_last_error(ctx));
+            return EXIT_FAILURE;
         }
+        out.flush();
+        fwrite(text.data(), 1, (size_t)len, stdout);
     }
     out.flush();
     dk_matrix_free(ctx, m);

@@ -81,6 +81,11 @@ int dk_matrix_export(dk_ctx *ctx, const dk_matrix *m, uint64_t row0, uint64_t nr
                      uint64_t *keys, int32_t *cnts);
 int dk_matrix_export_dev(dk_ctx *ctx, const dk_matrix *m, uint64_t row0, uint64_t nrows,
                          uint64_t *keys_dev, int32_t *cnts_dev);
+/* text of rows [row0,row0+nrows) exactly as joinCounts prints them (joinCounts.c:105-109: "%s" k-mer of k bases,
+ * "\t%d" per sample, "\n"), formatted on the device into the host buffer out (capacity cap). *len = bytes written;
+ * when cap is too small nothing is copied, *len = bytes needed and DK_ERR_ARG is returned. */
+int dk_matrix_format_rows(dk_ctx *ctx, const dk_matrix *m, uint64_t row0, uint64_t nrows, int k,
+                          char *out, uint64_t cap, uint64_t *len);
 /* order-independent checksums over all rows: xor of keys, sum of all counts (mod 2^64) */
 int dk_matrix_checksum(dk_ctx *ctx, const dk_matrix *m, uint64_t *key_xor, uint64_t *cnt_sum);
 void dk_matrix_free(dk_ctx *ctx, dk_matrix *m);

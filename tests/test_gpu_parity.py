@@ -405,3 +405,40 @@ def test_matrix_mask_edges(ctx):
     with pytest.raises(dk.DkError, match="not sorted"):
         ctx.matrix_mask(u, np.array([1, 2], np.uint64))
     u.free()
+
+
+# ------------------------------------------------- device text formatter (joinCounts.c:105-109) ---
+@pytest.mark.parametrize("S,R,k", [(4, 5000, 31), (16, 40000, 31), (1, 300, 9), (100, 3000, 25), (256, 700, 31), (7, 129, 1)])
+def test_format_rows_equals_printf(ctx, S, R, k):
+    rng = np.random.default_rng(S + R)
+    keys = np.sort(rng.integers(0, 1 << (2 * k), R, dtype=np.uint64))
+    cnts = rng.integers(0, 50, (R, S)).astype(np.int32)
+    big = rng.random((R, S)) < 0.05                                     # every digit count, both signs, the int limits
+    cnts[big] = rng.integers(-2 ** 31, 2 ** 31, int(big.sum()), dtype=np.int64).astype(np.int32)
+    cnts[0, 0], cnts[-1, -1] = -2 ** 31, 2 ** 31 - 1
+    for d in range(10):
+        cnts[min(R - 1, 1 + d), 0] = 10 ** d
+        cnts[min(R - 1, 1 + d), S - 1] = 10 ** d - 1
+    m = ctx.matrix_from_host(cnts, keys)
+    want = format_join(keys, cnts, k).encode()
+    assert m.format_rows(k) == want
+    lines = want.split(b"\n")
+    assert m.format_rows(k, 3, 100) == b"\n".join(lines[3:103]) + b"\n"  # a window of rows
+    assert m.format_rows(k, R, 0) == b""
+    m.free()
+
+
+def test_format_rows_on_chunked_join_output(ctx):
+    rng = np.random.default_rng(99)
+    keys, cnts = random_dumps(rng, 8, 120000, 62, 0.4, 5000, p_core=0.3)
+    m = ctx.join_counts(keys, cnts, 2, 3)
+    gk, gc = m.export()
+    assert m.format_rows(31) == format_join(gk, gc, 31).encode()
+    with pytest.raises(dk.DkError):
+        ctx.L.dk_matrix_format_rows.restype                             # keep the symbol referenced
+        buf = np.empty(8, np.uint8)
+        import ctypes as C
+        ln = C.c_uint64(0)
+        ctx._chk(ctx.L.dk_matrix_format_rows(ctx.h, m.h, 0, m.rows, 31, buf.ctypes.data, 8, C.byref(ln)))
+    assert ln.value == len(format_join(gk, gc, 31))                     # too-small buffer: size needed is reported
+    m.free()
