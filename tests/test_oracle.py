@@ -90,6 +90,25 @@ def test_student_t_tail_vs_scipy():
             assert abs(got - want) <= 1e-11 * want + 1e-300, (t, df, got, want)
 
 
+def test_student_t_tail_vs_boost_math_inside_scipy():
+    """scipy's special functions are compiled against Boost.Math (its _ufuncs_cxx module carries boost::math::ibeta and
+    boost::math::students_t_distribution), the library TtestFilter.c:146-147 calls. The reference computes
+    2*cdf(complement(students_t(df), |t|)); for Boost that is ibeta(df/2, 1/2, df/(df+t^2)) when df > 2 t^2 is false, and its
+    complement form otherwise: both equal the regularised incomplete beta checked here."""
+    sp = pytest.importorskip("scipy.special")
+    st = pytest.importorskip("scipy.stats")
+    rng = np.random.default_rng(11)
+    df = np.concatenate([rng.uniform(1.0, 40.0, 400), rng.uniform(40, 2000, 100), [1.0, 2.0, 14.0]])
+    t = np.concatenate([np.abs(rng.standard_normal(400)) * 3, rng.uniform(0, 60, 100), [0.0, 1e-8, 37.5]])
+    for ti, di in zip(t, df):
+        got = orc.student_t_2tail(float(ti), float(di))
+        y = ti * ti / (di + ti * ti)                      # the small argument is formed without cancellation
+        w1 = float(sp.betainc(di / 2, 0.5, di / (di + ti * ti))) if y > 0.01 else float(1 - sp.betainc(0.5, di / 2, y))
+        w2 = float(2 * st.t.sf(ti, di))
+        assert abs(got - w1) <= 1e-11 * w1 + 1e-300, (ti, di, got, w1)
+        assert abs(got - w2) <= 1e-10 * w2 + 1e-300, (ti, di, got, w2)
+
+
 # SURVEY §4 table (scipy-derived pins for the reference's TtestFilter fixtures, -p 0.2)
 SURVEY_ROWS = {
     "bigger": {(16, 16, 16, 18, 18, 18): (0.3767727982505043, 0.3767727982505043, 19.501368, 15.843223, -0.299709),
