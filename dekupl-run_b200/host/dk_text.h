@@ -41,6 +41,7 @@ struct DkCursor {
     const char *p, *end;
     int dret = 0;
     DkCursor(const DkFile &f) : p(f.buf.data()), end(f.buf.data() + f.size()) {}
+    DkCursor(const char *b, const char *e) : p(b), end(e) {}
     bool eof() const { return p >= end; }
     // returns false when no token could be read (EOF before any byte)
     bool token(const char *&s, size_t &len)

@@ -13,8 +13,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BIN = os.path.join(ROOT, "dekupl-run_b200", "host", "bin")
 
 
-def run(tool, *args, cwd=None):
-    return subprocess.run([os.path.join(BIN, tool), *args], capture_output=True, text=True, cwd=cwd)
+def run(tool, *args, cwd=None, env=None):
+    return subprocess.run([os.path.join(BIN, tool), *args], capture_output=True, text=True, cwd=cwd,
+                          env=None if env is None else {**os.environ, **env})
 
 
 # ------------------------------------------------------------------ CPU: argv surface ---
@@ -48,6 +49,20 @@ def test_diffFilter_argv_surface(tmp_path):
     tab.write_text("tag\ts1\nACGTN\t3\n")
     r = run("diffFilter", str(ref), str(tab))
     assert r.returncode != 0 and "at most 31 ACGT bases" in r.stderr and r.stdout == ""
+
+
+def test_table_parser_threads_report_the_same_ragged_line(tmp_path):
+    """the parallel parser falls back to the sequential reader whenever a part does not hold one row per line"""
+    rows = ["K%d\t%d\t%d" % (i, i, 2 * i) for i in range(400)]
+    rows[257] = "K257\t5"                                                 # ragged: swallows the next line's tag
+    bad = tmp_path / "bad.tsv"
+    bad.write_text("tag\ta\tb\n" + "\n".join(rows) + "\n")
+    msgs = set()
+    for nt in ("1", "2", "5", "32"):
+        r = run("computeNF", str(bad), env={"DK_PARSE_THREADS": nt})
+        assert r.returncode != 0
+        msgs.add(r.stderr.strip())
+    assert msgs == {"inconsistent number of column (line 258)"}, msgs
 
 
 def test_poisson_flag_is_accepted_in_usage():
@@ -90,6 +105,10 @@ def test_computeNF_cli_matches_reference_binary_bytes(tmp_path):
     bad.write_text("tag\ta\tb\nK1\t1\t2\nK2\t3\nK3\t4\t5\n")
     r = run("computeNF", str(bad))
     assert r.returncode != 0 and "inconsistent number of column (line 2)" in r.stderr
+    # the multi-threaded table parser (forced on this small file) gives the same bytes as the sequential one
+    for nt in ("1", "3", "16"):
+        r = run("computeNF", str(p), env={"DK_PARSE_THREADS": nt})
+        assert r.returncode == 0 and r.stdout == g["computeNF_fixture"], nt
 
 
 @pytest.mark.gpu
