@@ -38,6 +38,7 @@ int main(int argc, char *argv[])
     const char *counts_file = argv[optind++], *conditions_file = argv[optind++];
     const char *conditionA = argv[optind++], *conditionB = argv[optind++];
 
+    dk_async_init_start();                      // CUDA context comes up while the table is inflated and parsed
     DkFile f;
     if (!f.load(counts_file)) { fprintf(stderr, "Failed to open %s\n", counts_file); exit(EXIT_FAILURE); }
     DkMatrixText mt;
@@ -96,7 +97,7 @@ int main(int argc, char *argv[])
     if (S < 1 || S > DK_MAX_SAMPLES) { fprintf(stderr, "TtestFilter: %d samples unsupported (1..%d)\n", S, DK_MAX_SAMPLES); return EXIT_FAILURE; }
 
     dk_ctx *ctx = nullptr;
-    if (dk_init(&ctx, 0) != DK_OK) { fprintf(stderr, "TtestFilter: %s\n", dk_last_error(nullptr)); return EXIT_FAILURE; }
+    if (!(ctx = dk_async_init_obj.wait())) { fprintf(stderr, "TtestFilter: %s\n", dk_async_init_obj.err.c_str()); return EXIT_FAILURE; }
     dk_matrix *m = nullptr;
     dk_ttest *t = nullptr;
 #define CHECK(call) if ((call) != DK_OK) { fprintf(stderr, "TtestFilter: %s\n", dk_last_error(ctx)); return EXIT_FAILURE; }

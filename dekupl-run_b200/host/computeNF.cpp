@@ -15,6 +15,7 @@ int main(int argc, char *argv[])
         return 1;
     }
     const char *path = argv[optind];
+    dk_async_init_start();                      // CUDA context comes up while the table is inflated and parsed
     DkFile f;
     if (!f.load(path)) { fprintf(stderr, "Failed to open %s\n", path); exit(EXIT_FAILURE); }
     DkMatrixText mt;
@@ -22,7 +23,7 @@ int main(int argc, char *argv[])
     if (bad) { fprintf(stderr, "inconsistent number of column (line %zu)\n", bad); exit(EXIT_FAILURE); }
     if (mt.S < 1 || mt.S > DK_MAX_SAMPLES) { fprintf(stderr, "computeNF: %d samples unsupported (1..%d)\n", mt.S, DK_MAX_SAMPLES); return EXIT_FAILURE; }
     dk_ctx *ctx = nullptr;
-    if (dk_init(&ctx, 0) != DK_OK) { fprintf(stderr, "computeNF: %s\n", dk_last_error(nullptr)); return EXIT_FAILURE; }
+    if (!(ctx = dk_async_init_obj.wait())) { fprintf(stderr, "computeNF: %s\n", dk_async_init_obj.err.c_str()); return EXIT_FAILURE; }
     dk_matrix *m = nullptr;
     if (dk_matrix_from_host(ctx, mt.S, mt.R, nullptr, mt.cnts.data(), &m) != DK_OK) { fprintf(stderr, "computeNF: %s\n", dk_last_error(ctx)); return EXIT_FAILURE; }
     const char *mode_env = getenv("DK_NF_MODE");

@@ -47,6 +47,7 @@ int main(int argc, char *argv[])
         fprintf(stderr, "Usage:   diffFilter <ref_kmers.tsv[.gz]> <counts.tsv[.gz]>\n");
         return 1;
     }
+    dk_async_init_start();                      // CUDA context comes up while the two files are inflated and parsed
     DkFile diff, counts;
     if (!diff.load(argv[1])) { fprintf(stderr, "Cannot open %s\n", argv[1]); return 2; }       // diffFilter.pl:35,37
     if (!counts.load(argv[2])) { fprintf(stderr, "Cannot open %s\n", argv[2]); return 2; }
@@ -58,7 +59,7 @@ int main(int argc, char *argv[])
     pack_column(diff, false, argv[1], mask, nullptr, nullptr, k);
     std::vector<uint8_t> keep(keys.size());
     dk_ctx *ctx = nullptr;
-    if (dk_init(&ctx, 0) != DK_OK) { fprintf(stderr, "diffFilter: %s\n", dk_last_error(nullptr)); return EXIT_FAILURE; }
+    if (!(ctx = dk_async_init_obj.wait())) { fprintf(stderr, "diffFilter: %s\n", dk_async_init_obj.err.c_str()); return EXIT_FAILURE; }
     if (dk_keys_antijoin(ctx, keys.data(), keys.size(), mask.data(), mask.size(), keep.data()) != DK_OK) {
         fprintf(stderr, "diffFilter: %s\n", dk_last_error(ctx));
         return EXIT_FAILURE;

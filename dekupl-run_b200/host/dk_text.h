@@ -10,6 +10,7 @@
 #include <string.h>
 #include <zlib.h>
 #include <string>
+#include <thread>
 #include <vector>
 
 struct DkFile {
@@ -136,3 +137,24 @@ struct DkOut {   // buffered stdout/gz writer
         put(t, (size_t)n);
     }
 };
+
+// Creating the CUDA context takes about a second on a fresh process, as long as inflating and parsing a mid-sized
+// input: the CLIs start it on a helper thread first thing and pick the context up when the text is ready.
+#ifdef DEKUPL_B200_H
+struct DkAsyncInit {
+    dk_ctx *ctx = nullptr;
+    int rc = DK_OK;
+    std::string err;
+    std::thread th;
+    void start() { th = std::thread([this] { rc = dk_init(&ctx, 0); if (rc != DK_OK) err = dk_last_error(nullptr); }); }
+    dk_ctx *wait() { if (th.joinable()) th.join(); return rc == DK_OK ? ctx : nullptr; }
+    ~DkAsyncInit() { if (th.joinable()) th.join(); }
+};
+static DkAsyncInit dk_async_init_obj;
+// exit() from any depth stays safe: the helper thread is joined before the C++ runtime tears the process down
+static inline void dk_async_init_start()
+{
+    dk_async_init_obj.start();
+    atexit([] { dk_async_init_obj.wait(); });
+}
+#endif

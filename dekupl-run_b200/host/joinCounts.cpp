@@ -29,6 +29,7 @@ int main(int argc, char *argv[])
         return 1;
     }
     int S = argc - optind;
+    dk_async_init_start();                      // CUDA context comes up while the dumps are inflated and parsed
     if (S > DK_MAX_SAMPLES) { fprintf(stderr, "joinCounts: at most %d input files are supported\n", DK_MAX_SAMPLES); return EXIT_FAILURE; }
     std::vector<std::vector<uint64_t>> keys(S);
     std::vector<std::vector<int32_t>> cnts(S);
@@ -91,7 +92,7 @@ int main(int argc, char *argv[])
         if (kk[i] && kk[i] != k) { fprintf(stderr, "joinCounts: %s: mixed k-mer lengths (%d and %d)\n", argv[optind + i], k, kk[i]); return EXIT_FAILURE; }
     }
     dk_ctx *ctx = nullptr;
-    if (dk_init(&ctx, 0) != DK_OK) { fprintf(stderr, "joinCounts: %s\n", dk_last_error(nullptr)); return EXIT_FAILURE; }
+    if (!(ctx = dk_async_init_obj.wait())) { fprintf(stderr, "joinCounts: %s\n", dk_async_init_obj.err.c_str()); return EXIT_FAILURE; }
     std::vector<const uint64_t *> kp(S);
     std::vector<const int32_t *> cp(S);
     std::vector<uint64_t> n(S);

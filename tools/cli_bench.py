@@ -58,6 +58,9 @@ def main():
     with open(raw, "wb") as f:
         f.write(gzip.compress(("tag\t" + "\t".join(f"s{i}" for i in range(S)) + "\n").encode()))
         f.write(gzip.compress(open(os.path.join(d, "ref.tsv"), "rb").read(), compresslevel=1))
+    tiny = os.path.join(d, "tiny.tsv")
+    open(tiny, "w").write("tag\ta\tb\nACGT\t1\t2\nACGG\t3\t4\n")
+    res["computeNF ours, 2-row table (start-up floor)"] = timed([os.path.join(BIN, "computeNF"), tiny], os.path.join(d, "nf_tiny.tsv"))
     res["computeNF ours"] = timed([os.path.join(BIN, "computeNF"), raw], os.path.join(d, "nf_ours.tsv"))
     res["computeNF ours (1 parse thread)"] = None
     os.environ["DK_PARSE_THREADS"] = "1"
@@ -67,7 +70,7 @@ def main():
     same_nf = open(os.path.join(d, "nf_ours.tsv")).read() == open(os.path.join(d, "nf_ref.tsv")).read()
     print(f"# rows {rows}; joinCounts bytes identical: {same}; computeNF bytes identical: {same_nf}")
     for k, v in res.items():
-        print(f"{k:36s} {v:8.2f} s")
+        print(f"{k:48s} {v:8.2f} s")
 
 
 if __name__ == "__main__":
