@@ -364,6 +364,17 @@ def run_mask(args, cfg, ctx, kp, cp, n, peak):
                                "sample": f"first {nc} rows and the mask below their last key; keys only (no row copy), "
                                          f"{int((~keep).sum())} rows removed"}
     del keys, mask
+    # ---- §8(f)#2: joinCounts rows printed on the device (dk_matrix_format_rows), through the C ABI into a host buffer
+    try:
+        nfmt = min(R, 4_000_000)
+        m.format_rows(31, 0, min(nfmt, 1000))
+        t0 = time.time()
+        txt = m.format_rows(31, 0, nfmt)
+        dt = time.time() - t0
+        res["format"] = {"rows": nfmt, "bytes": len(txt), "seconds": dt, "rows_per_s": nfmt / dt, "text_GBps": len(txt) / dt / 1e9,
+                         "note": "dk_matrix_format_rows incl. the D2H copy into a pageable host buffer; joinCounts.c:105-109 bytes"}
+    except Exception as e:                               # the mask numbers above stand on their own
+        res["format"] = {"error": str(e)}
     m.free()
     return res
 

@@ -10,7 +10,7 @@ The directory name has a hyphen (it is the name the build contract asks for), so
 import it through `dekupl_run_b200.py` at the repo root.
 """
 from .binding import (  # noqa: F401
-    DkError, Context, Matrix, TtestResult, lib_path, load_library, declared_symbols,
+    DkError, Context, Matrix, Dump, TtestResult, lib_path, load_library, declared_symbols,
     NF_REFERENCE, NF_FULL,
 )
 from .kmer import encode_kmer, decode_kmer, encode_kmers, decode_kmers  # noqa: F401

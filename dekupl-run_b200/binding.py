@@ -57,6 +57,10 @@ def load_library():
         "dk_matrix_export_dev": (i32, [vp, vp, u64, u64, vp, vp]),
         "dk_matrix_format_rows": (i32, [vp, vp, u64, u64, i32, vp, u64, P(u64)]),
         "dk_matrix_checksum": (i32, [vp, vp, P(u64), P(u64)]), "dk_matrix_free": (None, [vp, vp]),
+        "dk_count_kmers": (i32, [vp, vp, vp, u64, vp, i32, i32, C.c_uint32, P(vp)]),
+        "dk_dump_size": (u64, [vp]), "dk_dump_keys_dev": (vp, [vp]), "dk_dump_cnts_dev": (vp, [vp]),
+        "dk_dump_stats": (None, [vp, P(u64), P(u64), P(u64)]), "dk_dump_export": (i32, [vp, vp, vp, vp]),
+        "dk_dump_free": (None, [vp, vp]),
         "dk_matrix_mask": (i32, [vp, vp, vp, u64, i32, P(vp), P(u64)]),
         "dk_keys_antijoin": (i32, [vp, vp, u64, vp, u64, vp]),
         "dk_run_path_masked": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, i32, P(i32), i32, P(i32), i32, dbl, dbl, i32,
@@ -130,6 +134,41 @@ class Matrix:
     def free(self):
         if self.h:
             self.ctx.L.dk_matrix_free(self.ctx.h, self.h)
+            self.h = None
+
+
+class Dump:
+    """one sample's sorted (k-mer, count) table on the device (dk_count_kmers)"""
+
+    def __init__(self, ctx, handle):
+        self.ctx, self.h = ctx, handle
+
+    @property
+    def size(self):
+        return int(self.ctx.L.dk_dump_size(self.h))
+
+    @property
+    def keys_ptr(self):
+        return int(self.ctx.L.dk_dump_keys_dev(self.h) or 0)
+
+    @property
+    def cnts_ptr(self):
+        return int(self.ctx.L.dk_dump_cnts_dev(self.h) or 0)
+
+    def stats(self):
+        w, v, d = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+        self.ctx.L.dk_dump_stats(self.h, C.byref(w), C.byref(v), C.byref(d))
+        return dict(windows=int(w.value), valid=int(v.value), distinct=int(d.value))
+
+    def export(self):
+        n = self.size
+        k, c = np.empty(n, np.uint64), np.empty(n, np.int32)
+        self.ctx._chk(self.ctx.L.dk_dump_export(self.ctx.h, self.h, _np_ptr(k), _np_ptr(c)))
+        return k, c
+
+    def free(self):
+        if self.h:
+            self.ctx.L.dk_dump_free(self.ctx.h, self.h)
             self.h = None
 
 
@@ -250,6 +289,20 @@ class Context:
         out = C.c_void_p(0)
         self._chk(self.L.dk_matrix_from_host(self.h, S, R, _np_ptr(keys), _np_ptr(cnts), C.byref(out)))
         return Matrix(self, out)
+
+    # ---- k-mer counting (jellyfish count | dump | sort) -------------------------
+    def count_kmers(self, reads, k=31, rc_flags=None, canonical=False, min_count=2):
+        """reads: list of bytes/str sequence lines; rc_flags: per-read 0/1 (reads the pipeline reverse-complements)"""
+        seqs = [r.encode() if isinstance(r, str) else r for r in reads]
+        lens = np.fromiter((len(x) for x in seqs), dtype=np.uint64, count=len(seqs))
+        off = np.zeros(len(seqs) + 1, np.uint64)
+        np.cumsum(lens, out=off[1:])
+        bases = np.frombuffer(b"".join(seqs), dtype=np.uint8) if seqs else np.zeros(0, np.uint8)
+        rc = None if rc_flags is None else np.ascontiguousarray(rc_flags, dtype=np.uint8)
+        out = C.c_void_p(0)
+        self._chk(self.L.dk_count_kmers(self.h, _np_ptr(bases), _np_ptr(off), len(seqs), _np_ptr(rc), k, int(canonical),
+                                        int(min_count), C.byref(out)))
+        return Dump(self, out)
 
     # ---- reference-transcript mask (bin/diffFilter.pl) ---------------------------
     def matrix_mask(self, m, mask_keys, mask_on_device=False, n_mask=None):

@@ -1,4 +1,4 @@
-// dk_sort.cu — stable LSD radix sort of (uint64 key, uint32 value) pairs, 8 bits per pass.
+// dk_sort.cu — stable LSD radix sort of (uint64 key, uint32 value) pairs, 8 bits per pass (vals may be NULL: keys only).
 // Used for the BH candidate p-values (positive doubles order like their bit patterns)
 // and for ordering survivor row indices. Passes whose digit is constant are skipped.
 #include "dk_common.cuh"
@@ -54,7 +54,7 @@ __global__ void k_rs_scatter(const uint64_t *keys, const uint32_t *vals, size_t 
         size_t k = base + (size_t)i * RS_THREADS + threadIdx.x;
         bool valid = k < n;
         uint64_t key = valid ? keys[k] : 0;
-        uint32_t val = valid ? vals[k] : 0;
+        uint32_t val = (valid && vals) ? vals[k] : 0;
         unsigned dg = valid ? (unsigned)((key >> shift) & 255u) : 256u;   // 256 = "invalid" class
         unsigned peers = __match_any_sync(0xffffffffu, dg);
         unsigned rank = __popc(peers & ((1u << lane) - 1u));
@@ -71,7 +71,7 @@ __global__ void k_rs_scatter(const uint64_t *keys, const uint32_t *vals, size_t 
             for (int q = 0; q < RS_THREADS / 32; q++) t += wcnt[q][threadIdx.x];
             run[threadIdx.x] += t;
         }
-        if (valid) { okeys[pos] = key; ovals[pos] = val; }
+        if (valid) { okeys[pos] = key; if (ovals) ovals[pos] = val; }
         __syncthreads();
     }
 }

@@ -69,6 +69,23 @@ int dk_join_counts_dev(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, cons
                        const uint64_t *n, int min_rec, int min_abund, int emit_stale_tail,
                        dk_matrix **out);
 
+/* ---- k-mer counting of one sample (replaces `jellyfish count -L L -m K [-C]` on the two mates with
+ * bin/revCompFastq.pl:33-44 on one of them, `jellyfish dump -c` and `sort -k1`: Snakefile:523-582) ----
+ * bases: the sequence lines of all reads back to back (host); read r is bases[offsets[r] .. offsets[r+1]).
+ * rc_flag (may be NULL): 1 for reads the pipeline reverse-complements first (mate 1 of an "rf" library, mate 2 of
+ * "fr"). canonical != 0 is -C (unstranded). Windows holding a byte other than ACGTacgt are skipped. The result is
+ * the sorted (k-mer, count >= min_count) table on the device, in the layout dk_join_counts_dev takes.
+ * One call handles < 2^32-2 windows (about 55 M reads of 100 bases at k = 31). */
+typedef struct dk_dump dk_dump;
+int dk_count_kmers(dk_ctx *ctx, const char *bases, const uint64_t *offsets, uint64_t n_reads, const uint8_t *rc_flag,
+                   int k, int canonical, uint32_t min_count, dk_dump **out);
+uint64_t dk_dump_size(const dk_dump *d);
+const uint64_t *dk_dump_keys_dev(const dk_dump *d);       /* 16-byte aligned device pointers, valid until dk_dump_free */
+const int32_t  *dk_dump_cnts_dev(const dk_dump *d);
+void dk_dump_stats(const dk_dump *d, uint64_t *windows, uint64_t *valid, uint64_t *distinct);
+int dk_dump_export(dk_ctx *ctx, const dk_dump *d, uint64_t *keys, int32_t *cnts);   /* host copies; either may be NULL */
+void dk_dump_free(dk_ctx *ctx, dk_dump *d);
+
 /* ---- matrix ----------------------------------------------------------------*/
 /* wrap an existing row-major matrix (what computeNF / TtestFilter read from raw-counts.tsv) */
 int dk_matrix_from_host(dk_ctx *ctx, int S, uint64_t R, const uint64_t *keys /* may be NULL */,

@@ -68,6 +68,11 @@ void orc_poisson_rows(const int32_t *cnts, size_t R, int S, const int *idxA, int
  * Both ascending; returns the number of rows kept. */
 size_t orc_antijoin(const uint64_t *keys, size_t n, const uint64_t *mask, size_t n_mask, uint8_t *keep);
 
+/* Snakefile:523-582 (jellyfish count -L -m [-C] | dump -c | sort -k1, revCompFastq.pl on flagged reads) on packed k-mers.
+ * Returns the number of pairs written, -1 when cap is too small. Not pinned by the binary (jellyfish absent). */
+long long orc_count_kmers(const char *bases, const uint64_t *offsets, size_t n_reads, const uint8_t *rc_flag, int k, int canonical,
+                          uint32_t min_count, uint64_t *out_keys, int32_t *out_cnts, size_t cap);
+
 /* TtestFilter.c:459-476: Benjamini-Hochberg, in place semantic on a copy. */
 void orc_bh(const double *p_raw, size_t R, double *p_adj);
 

@@ -136,3 +136,65 @@ size_t orc_antijoin(const uint64_t *keys, size_t n, const uint64_t *mask, size_t
     }
     return kept;
 }
+
+/* k-mer counting of one sample as the pipeline does it (Snakefile:523-582): `jellyfish count -L min_count -m k [-C]`
+ * over the reads (those flagged rc first pass through bin/revCompFastq.pl:33-44: reversed and complemented),
+ * `jellyfish dump -c`, `sort -k1`. Restated on packed k-mers: every window of k bases without a byte outside
+ * ACGTacgt is one occurrence; -C counts min(k-mer, reverse complement). jellyfish is not in this image, so this
+ * restatement follows its documented behaviour and is not pinned by the binary.
+ * Returns the number of (k-mer, count) pairs written (ascending k-mers); -1 when cap is too small. */
+static int cmp_u64(const void *a, const void *b)
+{
+    uint64_t x = *(const uint64_t *)a, y = *(const uint64_t *)b;
+    return x < y ? -1 : x > y;
+}
+static uint64_t revcomp_k(uint64_t v, int k)
+{
+    uint64_t r = 0;
+    for (int i = 0; i < k; i++) { r = (r << 2) | (3 - (v & 3)); v >>= 2; }
+    return r;
+}
+long long orc_count_kmers(const char *bases, const uint64_t *offsets, size_t n_reads, const uint8_t *rc_flag, int k, int canonical,
+                          uint32_t min_count, uint64_t *out_keys, int32_t *out_cnts, size_t cap)
+{
+    size_t W = 0, n = 0;
+    for (size_t r = 0; r < n_reads; r++) { size_t len = offsets[r + 1] - offsets[r]; if (len >= (size_t)k) W += len - k + 1; }
+    uint64_t *v = (uint64_t *)malloc(sizeof(uint64_t) * (W ? W : 1));
+    for (size_t r = 0; r < n_reads; r++) {
+        const char *s = bases + offsets[r];
+        size_t len = offsets[r + 1] - offsets[r];
+        for (size_t i = 0; i + k <= len; i++) {
+            uint64_t key = 0;
+            int ok = 1;
+            for (int j = 0; j < k && ok; j++) {
+                int c;
+                switch (s[i + j]) {
+                    case 'A': case 'a': c = 0; break;
+                    case 'C': case 'c': c = 1; break;
+                    case 'G': case 'g': c = 2; break;
+                    case 'T': case 't': c = 3; break;
+                    default: c = -1;
+                }
+                if (c < 0) ok = 0; else key = (key << 2) | (uint64_t)c;
+            }
+            if (!ok) continue;
+            uint64_t rc = revcomp_k(key, k);
+            if (canonical) key = key < rc ? key : rc;
+            else if (rc_flag && rc_flag[r]) key = rc;            /* the k-mers of revcomp(read) */
+            v[n++] = key;
+        }
+    }
+    qsort(v, n, sizeof(uint64_t), cmp_u64);
+    size_t o = 0;
+    for (size_t i = 0; i < n;) {
+        size_t j = i;
+        while (j < n && v[j] == v[i]) j++;
+        if (j - i >= min_count) {
+            if (o >= cap) { free(v); return -1; }
+            out_keys[o] = v[i]; out_cnts[o] = (int32_t)(j - i); o++;
+        }
+        i = j;
+    }
+    free(v);
+    return (long long)o;
+}

@@ -94,6 +94,11 @@ def main():
     names = ["sample1", "sample2", "sample3", "sample4"]
     files = []
     for nm in names:
+        # the reads themselves (sequence lines only, "mate<TAB>sequence"), for the device k-mer counter's parity test
+        with gzip.GzipFile(os.path.join(OUT, f"reads_{nm}.txt.gz"), "wb", mtime=0) as f:
+            for mate in (1, 2):
+                for sq in reads(f"{DATA}/{nm}_{mate}.fastq.gz", NPAIRS, False):
+                    f.write(f"{mate}\t{sq}\n".encode())
         recs = count_sample(nm)
         p = os.path.join(OUT, nm + ".txt.gz")
         with gzip.GzipFile(p, "wb", mtime=0) as f:

@@ -34,6 +34,8 @@ def load():
     L.orc_poisson_rows.argtypes = [vp, sz, i32, vp, i32, vp, i32, vp, vp, vp, vp, vp]
     L.orc_antijoin.restype = sz
     L.orc_antijoin.argtypes = [vp, sz, vp, sz, vp]
+    L.orc_count_kmers.restype = C.c_longlong
+    L.orc_count_kmers.argtypes = [vp, vp, sz, vp, i32, i32, C.c_uint32, vp, vp, sz]
     L.orc_bh.restype = None
     L.orc_bh.argtypes = [vp, sz, vp]
     L.orc_filter.restype = sz
@@ -113,6 +115,22 @@ def antijoin(keys, mask):
     keep = np.zeros(len(keys), np.uint8)
     L.orc_antijoin(keys.ctypes.data, len(keys), mask.ctypes.data, len(mask), keep.ctypes.data)
     return keep.astype(bool)
+
+
+def count_kmers(reads, k=31, rc_flags=None, canonical=False, min_count=2):
+    """sorted (k-mer, count) table of one sample: jellyfish count -L -m [-C] | dump | sort on packed k-mers"""
+    L = load()
+    seqs = [r.encode() if isinstance(r, str) else r for r in reads]
+    off = np.zeros(len(seqs) + 1, np.uint64)
+    np.cumsum([len(x) for x in seqs], out=off[1:])
+    bases = np.frombuffer(b"".join(seqs) + b"\0", dtype=np.uint8)
+    rc = None if rc_flags is None else np.ascontiguousarray(rc_flags, dtype=np.uint8)
+    cap = int(off[-1]) + 1
+    keys, cnts = np.empty(cap, np.uint64), np.empty(cap, np.int32)
+    n = L.orc_count_kmers(bases.ctypes.data, off.ctypes.data, len(seqs), rc.ctypes.data if rc is not None else None, k,
+                          int(canonical), int(min_count), keys.ctypes.data, cnts.ctypes.data, cap)
+    assert n >= 0
+    return keys[:n].copy(), cnts[:n].copy()
 
 
 def bh(p):
