@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-mask", action="store_true", help="skip the reference-transcript mask measurement")
+    ap.add_argument("--no-ingest", action="store_true", help="skip the k-mer counting measurement")
     ap.add_argument("--cpu-rows", type=int, default=6_000_000, help="union rows of the CPU-baseline sample")
     return ap.parse_args()
 
@@ -292,6 +293,9 @@ def run_ours(args):
     # ---- §8(f)#1, the RNA-Seq mask (bin/diffFilter.pl): not part of the headline metric, measured beside it at N=1
     if world == 1 and not args.no_mask:
         out["mask"] = run_mask(args, cfg, ctx, kp, cp, n, peak)
+    # ---- §8(f)#4, k-mer counting of one sample from its reads (jellyfish count | dump | sort): measured beside the headline
+    if world == 1 and not args.no_ingest:
+        out["ingest"] = run_ingest(args, ctx)
     # ---- e2e: host buffers through the C ABI, H2D of all dumps + D2H of the survivors inside the timed region
     if not args.no_e2e and world == 1:
         out["e2e"] = run_e2e(args, cfg, ctx, keys, cnts, n, idxA, idxB, nf_mode)
@@ -307,6 +311,52 @@ def run_ours(args):
         print(json.dumps(out))
     if dist:
         dist.destroy_process_group()
+
+
+def run_ingest(args, ctx):
+    """dk_count_kmers on synthetic reads: a 2 Mb random genome sampled by 100-base reads (about 150x), one base in 200
+    replaced by N, half of the reads flagged for reverse complement; host bases in, sorted (k-mer, count >= 2) table on
+    the device out. CPU side: the oracle restatement (emit, qsort, run lengths) on a bounded subset of the same reads."""
+    import numpy as np
+    import torch
+    n_reads, L, k = int(3_000_000 * min(1.0, max(args.scale, 0.05) * 4)), 100, 31
+    rng = np.random.default_rng(5)
+    genome = rng.integers(0, 4, 2_000_000, dtype=np.uint8)
+    start = rng.integers(0, len(genome) - L, n_reads)
+    idx = start[:, None] + np.arange(L)[None, :]
+    codes = genome[idx]
+    bases = np.frombuffer(b"ACGT", np.uint8)[codes]
+    bases[rng.random(bases.shape) < 0.005] = ord("N")
+    bases = np.ascontiguousarray(bases.reshape(-1))
+    off = (np.arange(n_reads + 1, dtype=np.uint64) * np.uint64(L))
+    rc = (rng.random(n_reads) < 0.5).astype(np.uint8)
+    import ctypes as C
+    times, size, st = [], 0, {}
+    for i in range(1 + 3):
+        torch.cuda.synchronize()
+        t0 = time.time()
+        h = C.c_void_p(0)
+        ctx._chk(ctx.L.dk_count_kmers(ctx.h, bases.ctypes.data, off.ctypes.data, n_reads, rc.ctypes.data, k, 0, 2, C.byref(h)))
+        dt = time.time() - t0
+        d = __import__("dekupl_run_b200").Dump(ctx, h)
+        size, st = d.size, d.stats()
+        d.free()
+        if i >= 1:
+            times.append(dt)
+    dt = sum(times) / len(times)
+    res = {"metric": "read k-mers/s counted", "value": st["windows"] / dt, "unit": "k-mers/s", "seconds": dt, "reads": n_reads,
+           "read_length": L, "windows": st["windows"], "valid": st["valid"], "distinct": st["distinct"], "dump_records": size,
+           "h2d_bytes": int(bases.nbytes + off.nbytes + rc.nbytes),
+           "note": "dk_count_kmers through the C ABI with pageable host reads (H2D inside); radix sort of 8-byte keys dominates"}
+    if not args.no_cpu:
+        import oracle_lib as orc
+        ns = min(n_reads, 300_000)
+        t0 = time.time()
+        ok, oc = orc.count_kmers([bases[i * L:(i + 1) * L].tobytes() for i in range(ns)], k, rc[:ns], False, 2)
+        dtc = time.time() - t0
+        res["cpu_baseline"] = {"value": ns * (L - k + 1) / dtc, "unit": "k-mers/s", "cores": 1, "kind": "port", "seconds": dtc,
+                               "sample": f"first {ns} reads, oracle restatement (emit + qsort + run lengths), {len(ok)} records"}
+    return res
 
 
 def run_mask(args, cfg, ctx, kp, cp, n, peak):

@@ -120,10 +120,12 @@ class Matrix:
     def format_rows(self, k, row0=0, nrows=None):
         """the text joinCounts prints for these rows (joinCounts.c:105-109), formatted on the device"""
         n = self.rows - row0 if nrows is None else nrows
-        cap = n * (k + 1 + 12 * self.samples) + 16
-        buf = np.empty(cap, dtype=np.uint8)
         ln = C.c_uint64(0)
-        self.ctx._chk(self.ctx.L.dk_matrix_format_rows(self.ctx.h, self.h, row0, n, k, _np_ptr(buf), cap, C.byref(ln)))
+        if n == 0:
+            return b""
+        self.ctx.L.dk_matrix_format_rows(self.ctx.h, self.h, row0, n, k, None, 0, C.byref(ln))      # sizes only: *len = bytes needed
+        buf = np.empty(int(ln.value) + 16, dtype=np.uint8)
+        self.ctx._chk(self.ctx.L.dk_matrix_format_rows(self.ctx.h, self.h, row0, n, k, _np_ptr(buf), len(buf), C.byref(ln)))
         return buf[: ln.value].tobytes()
 
     def checksum(self):
