@@ -60,7 +60,7 @@ def load_library():
         "dk_count_kmers": (i32, [vp, vp, vp, u64, vp, i32, i32, C.c_uint32, P(vp)]),
         "dk_dump_size": (u64, [vp]), "dk_dump_keys_dev": (vp, [vp]), "dk_dump_cnts_dev": (vp, [vp]),
         "dk_dump_stats": (None, [vp, P(u64), P(u64), P(u64)]), "dk_dump_export": (i32, [vp, vp, vp, vp]),
-        "dk_dump_free": (None, [vp, vp]),
+        "dk_dump_free": (None, [vp, vp]), "dk_dump_merge": (i32, [vp, P(vp), i32, C.c_uint32, P(vp)]),
         "dk_matrix_mask": (i32, [vp, vp, vp, u64, i32, P(vp), P(u64)]),
         "dk_keys_antijoin": (i32, [vp, vp, u64, vp, u64, vp]),
         "dk_run_path_masked": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, i32, P(i32), i32, P(i32), i32, dbl, dbl, i32,
@@ -304,6 +304,13 @@ class Context:
         out = C.c_void_p(0)
         self._chk(self.L.dk_count_kmers(self.h, _np_ptr(bases), _np_ptr(off), len(seqs), _np_ptr(rc), k, int(canonical),
                                         int(min_count), C.byref(out)))
+        return Dump(self, out)
+
+    def merge_dumps(self, dumps, min_count=2):
+        """sum of tables counted with min_count=1 over read batches of one sample"""
+        arr = (C.c_void_p * len(dumps))(*[d.h for d in dumps])
+        out = C.c_void_p(0)
+        self._chk(self.L.dk_dump_merge(self.h, arr, len(dumps), int(min_count), C.byref(out)))
         return Dump(self, out)
 
     # ---- reference-transcript mask (bin/diffFilter.pl) ---------------------------

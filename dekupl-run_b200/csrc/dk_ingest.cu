@@ -217,3 +217,92 @@ extern "C" int dk_dump_export(dk_ctx *ctx, const dk_dump *d, uint64_t *keys, int
     return DK_OK;
 }
 extern "C" void dk_dump_free(dk_ctx *ctx, dk_dump *d) { if (ctx) dump_release(ctx, d); }
+
+// ---- samples larger than one call: count read batches with min_count = 1, then add the tables up ----------------
+// one thread per row of the joined batch tables: total count, keep flag
+__global__ void k_dump_rowsum(const int32_t *cnts, const uint64_t *lbase, const uint32_t *order, uint32_t n_chunks, int S, uint64_t R,
+                              uint32_t min_count, uint32_t *total, uint32_t *keep)
+{
+    const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= R) return;
+    uint32_t lo = 0, hi = n_chunks;
+    while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (lbase[mid] <= r) lo = mid; else hi = mid; }
+    const int32_t *c = cnts + ((size_t)order[lo] * DK_CH + (size_t)(r - lbase[lo])) * (size_t)S;
+    unsigned long long s = 0;
+    for (int j = 0; j < S; j++) s += (unsigned long long)(uint32_t)c[j];
+    const uint32_t t = s > 0x7fffffffull ? 0x7fffffffu : (uint32_t)s;
+    total[r] = t;
+    keep[r] = t >= min_count ? 1u : 0u;
+}
+__global__ void k_dump_compact(const uint64_t *keys, const uint64_t *lbase, const uint32_t *order, uint32_t n_chunks, uint64_t R,
+                               const uint32_t *total, const uint32_t *keep, const uint32_t *kidx, uint64_t *okeys, int32_t *ocnts)
+{
+    const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= R || !keep[r]) return;
+    uint32_t lo = 0, hi = n_chunks;
+    while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (lbase[mid] <= r) lo = mid; else hi = mid; }
+    okeys[kidx[r]] = keys[(size_t)order[lo] * DK_CH + (size_t)(r - lbase[lo])];
+    ocnts[kidx[r]] = (int32_t)total[r];
+}
+
+void dk_matrix_release(dk_ctx *ctx, dk_matrix *m);
+
+// Sum of n_parts tables counted with min_count = 1 (read batches of one sample): the k-way merge is dk_join_counts_dev
+// (every k-mer kept), the row sums are the sample's counts, -L is applied to the sums.
+extern "C" int dk_dump_merge(dk_ctx *ctx, dk_dump *const *parts, int n_parts, uint32_t min_count, dk_dump **out)
+{
+    if (!ctx || !parts || !out || n_parts < 1) return dk_fail(ctx, DK_ERR_ARG, "dump_merge: bad argument");
+    if (n_parts > DK_MAX_SAMPLES) return dk_fail(ctx, DK_ERR_ARG, "dump_merge: at most %d tables per call", DK_MAX_SAMPLES);
+    *out = nullptr;
+    std::vector<const uint64_t *> kp(n_parts);
+    std::vector<const int32_t *> cp(n_parts);
+    std::vector<uint64_t> nn(n_parts);
+    dk_dump *d = new dk_dump();
+    for (int i = 0; i < n_parts; i++) {
+        if (!parts[i]) { delete d; return dk_fail(ctx, DK_ERR_ARG, "dump_merge: NULL table %d", i); }
+        kp[i] = parts[i]->keys; cp[i] = parts[i]->cnts; nn[i] = parts[i]->n;
+        d->windows += parts[i]->windows; d->valid += parts[i]->valid;
+    }
+    dk_matrix *m = nullptr;
+    int rc = dk_join_impl(ctx, n_parts, kp.data(), cp.data(), nn.data(), 1, 1, 0, &m);
+    if (rc != DK_OK) { delete d; return rc; }
+    const uint64_t R = m->R;
+    d->distinct = R;
+    cudaStream_t st = ctx->stream;
+    uint32_t K = 0;
+    uint32_t *total = nullptr, *keep = nullptr, *kidx = nullptr;
+    if (R) {
+        total = (uint32_t *)dk_dev_alloc(ctx, 4 * (R + 1)); keep = (uint32_t *)dk_dev_alloc(ctx, 4 * (R + 1));
+        kidx = (uint32_t *)dk_dev_alloc(ctx, 4 * (R + 2));
+        if (!total || !keep || !kidx) rc = DK_ERR_NOMEM;
+        if (rc == DK_OK) {
+            k_dump_rowsum<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(m->cnts, m->lbase, m->order, (uint32_t)m->n_chunks, m->S, R, min_count,
+                                                                     total, keep);
+            ctx->launches++;
+            rc = dk_scan_excl_u32(ctx, keep, kidx, R);
+        }
+        if (rc == DK_OK) {
+            cudaError_t e = cudaMemcpyAsync(&K, kidx + R, 4, cudaMemcpyDeviceToHost, st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+            if (e != cudaSuccess) rc = dk_fail(ctx, DK_ERR_CUDA, "dump_merge: %s", cudaGetErrorString(e));
+        }
+        if (rc == DK_OK && K) {
+            d->keys = (uint64_t *)dk_dev_alloc(ctx, 8 * ((size_t)K + 4));
+            d->cnts = (int32_t *)dk_dev_alloc(ctx, 4 * ((size_t)K + 4));
+            if (!d->keys || !d->cnts) rc = DK_ERR_NOMEM;
+            if (rc == DK_OK) {
+                k_dump_compact<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(m->keys, m->lbase, m->order, (uint32_t)m->n_chunks, R, total, keep,
+                                                                          kidx, d->keys, d->cnts);
+                ctx->launches++;
+                cudaError_t e = cudaStreamSynchronize(st);
+                if (e != cudaSuccess) rc = dk_fail(ctx, DK_ERR_CUDA, "dump_merge: %s", cudaGetErrorString(e));
+            }
+            d->n = K;
+        }
+    }
+    dk_dev_release(ctx, total); dk_dev_release(ctx, keep); dk_dev_release(ctx, kidx);
+    dk_matrix_release(ctx, m);
+    if (rc != DK_OK) { dump_release(ctx, d); return rc; }
+    *out = d;
+    return DK_OK;
+}

@@ -85,6 +85,9 @@ const int32_t  *dk_dump_cnts_dev(const dk_dump *d);
 void dk_dump_stats(const dk_dump *d, uint64_t *windows, uint64_t *valid, uint64_t *distinct);
 int dk_dump_export(dk_ctx *ctx, const dk_dump *d, uint64_t *keys, int32_t *cnts);   /* host copies; either may be NULL */
 void dk_dump_free(dk_ctx *ctx, dk_dump *d);
+/* a sample too large for one call: count its reads in batches with min_count = 1, then add the tables up
+ * (k-way merge = dk_join_counts, row sums = the sample's counts, min_count applied to the sums); <= DK_MAX_SAMPLES tables */
+int dk_dump_merge(dk_ctx *ctx, dk_dump *const *parts, int n_parts, uint32_t min_count, dk_dump **out);
 
 /* ---- matrix ----------------------------------------------------------------*/
 /* wrap an existing row-major matrix (what computeNF / TtestFilter read from raw-counts.tsv) */

@@ -122,3 +122,23 @@ def test_reads_to_diff_counts_without_text_dumps(ctx):
     for d in dumps:
         d.free()
     _ = orc
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nbatch,canonical", [(3, False), (7, True), (1, False)])
+def test_batched_counting_adds_up(ctx, nbatch, canonical):
+    """a sample counted in read batches (min_count 1) and summed equals the single-call table (-L on the sums)"""
+    rng = np.random.default_rng(nbatch)
+    reads = _random_reads(rng, 4000)
+    rc = (rng.random(len(reads)) < 0.5).astype(np.uint8)
+    whole = ctx.count_kmers(reads, 21, rc, canonical, 3)
+    wk, wc = whole.export()
+    cuts = np.linspace(0, len(reads), nbatch + 1).astype(int)
+    parts = [ctx.count_kmers(reads[a:b], 21, rc[a:b], canonical, 1) for a, b in zip(cuts[:-1], cuts[1:])]
+    merged = ctx.merge_dumps(parts, 3)
+    mk, mc = merged.export()
+    np.testing.assert_array_equal(mk, wk)
+    np.testing.assert_array_equal(mc, wc)
+    assert merged.stats()["windows"] == whole.stats()["windows"] and merged.stats()["valid"] == whole.stats()["valid"]
+    for d in parts + [merged, whole]:
+        d.free()
