@@ -61,6 +61,9 @@ def load_library():
         "dk_dump_size": (u64, [vp]), "dk_dump_keys_dev": (vp, [vp]), "dk_dump_cnts_dev": (vp, [vp]),
         "dk_dump_stats": (None, [vp, P(u64), P(u64), P(u64)]), "dk_dump_export": (i32, [vp, vp, vp, vp]),
         "dk_dump_free": (None, [vp, vp]), "dk_dump_merge": (i32, [vp, P(vp), i32, C.c_uint32, P(vp)]),
+        "dk_merge_tags": (i32, [vp, vp, u64, i32, vp, vp, i32, P(vp)]),
+        "dk_contigs_count": (u64, [vp]), "dk_contigs_chars": (u64, [vp]), "dk_contigs_rings": (u64, [vp]),
+        "dk_contigs_export": (i32, [vp, vp, vp, vp, vp]), "dk_contigs_free": (None, [vp]),
         "dk_matrix_mask": (i32, [vp, vp, vp, u64, i32, P(vp), P(u64)]),
         "dk_keys_antijoin": (i32, [vp, vp, u64, vp, u64, vp]),
         "dk_run_path_masked": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, i32, P(i32), i32, P(i32), i32, dbl, dbl, i32,
@@ -312,6 +315,24 @@ class Context:
         out = C.c_void_p(0)
         self._chk(self.L.dk_dump_merge(self.h, arr, len(dumps), int(min_count), C.byref(out)))
         return Dump(self, out)
+
+    # ---- mergeTags -----------------------------------------------------------------
+    def merge_tags(self, kmers, pvalues, rep_ids=None, k=None, min_k=15):
+        """contigs of one regulation direction; returns list of (rep_id, nb_merged, sequence) and the ring-member count"""
+        kmers = [s.encode() if isinstance(s, str) else s for s in kmers]
+        n = len(kmers)
+        k = k if k is not None else (len(kmers[0]) if n else 31)
+        seqs = np.frombuffer(b"".join(kmers), dtype=np.uint8) if n else np.zeros(0, np.uint8)
+        p = np.ascontiguousarray(pvalues, dtype=np.float64)
+        rid = np.arange(n, dtype=np.uint32) if rep_ids is None else np.ascontiguousarray(rep_ids, dtype=np.uint32)
+        out = C.c_void_p(0)
+        self._chk(self.L.dk_merge_tags(self.h, _np_ptr(seqs), n, k, _np_ptr(p), _np_ptr(rid), min_k, C.byref(out)))
+        m, nch, rings = int(self.L.dk_contigs_count(out)), int(self.L.dk_contigs_chars(out)), int(self.L.dk_contigs_rings(out))
+        rep, nb, off, ch = np.empty(m, np.uint32), np.empty(m, np.uint32), np.empty(m + 1, np.uint64), np.empty(nch, np.uint8)
+        self.L.dk_contigs_export(out, _np_ptr(rep), _np_ptr(nb), _np_ptr(off), _np_ptr(ch))
+        self.L.dk_contigs_free(out)
+        txt = ch.tobytes()
+        return [(int(rep[j]), int(nb[j]), txt[int(off[j]):int(off[j + 1])].decode()) for j in range(m)], rings
 
     # ---- reference-transcript mask (bin/diffFilter.pl) ---------------------------
     def matrix_mask(self, m, mask_keys, mask_on_device=False, n_mask=None):

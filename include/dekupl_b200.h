@@ -181,6 +181,24 @@ int dk_ttest_export_rows(dk_ctx *ctx, const dk_ttest *t, double *p_raw, double *
 uint64_t dk_ttest_rows_count(const dk_ttest *t);
 void dk_ttest_free(dk_ctx *ctx, dk_ttest *t);
 
+/* ---- mergeTags (replaces share/mergeTags/mergeTags.c:68-212, stranded mode) -----------------
+ * Contigs of the k-mers of ONE regulation direction (the caller splits by log2FC > 0, mergeTags.c:296-301): for
+ * every overlap i = k-1 .. min_k, contigs whose i-base right end equals another contig's i-base left end are joined,
+ * an end shared by two contigs on the same side being unusable (:56-66). seqs: n k-mers of k upper-case ACGT bases
+ * back to back; rep_id[n]: the caller's id of each k-mer (its line number); a contig reports the id of its member
+ * with the lowest p-value (the rightmost such member on ties, :147-153) and the number of k-mers merged into it.
+ * Contigs linked in a ring are left unmerged at that level (the reference's result there depends on hash order);
+ * dk_contigs_rings counts them. The unstranded procedure (-n) is not provided. */
+typedef struct dk_contigs dk_contigs;
+int dk_merge_tags(dk_ctx *ctx, const char *seqs, uint64_t n, int k, const double *pvalue, const uint32_t *rep_id,
+                  int min_k, dk_contigs **out);
+uint64_t dk_contigs_count(const dk_contigs *c);
+uint64_t dk_contigs_chars(const dk_contigs *c);
+uint64_t dk_contigs_rings(const dk_contigs *c);
+/* rep[n], nb[n], off[n+1] (contig j = chars[off[j] .. off[j+1])), chars[dk_contigs_chars]; any may be NULL */
+int dk_contigs_export(const dk_contigs *c, uint32_t *rep, uint32_t *nb, uint64_t *off, char *chars);
+void dk_contigs_free(dk_contigs *c);
+
 /* ---- whole path, host buffers in, survivors out (what bench.py's e2e times) ---- */
 typedef struct {
     uint64_t U, R, R_pos, D;          /* union rows, filtered rows, all-positive rows used by NF, survivors */
