@@ -68,7 +68,21 @@ def main():
     del os.environ["DK_PARSE_THREADS"]
     res["computeNF reference"] = timed([os.path.join(REF, "computeNF"), raw], os.path.join(d, "nf_ref.tsv"))
     same_nf = open(os.path.join(d, "nf_ours.tsv")).read() == open(os.path.join(d, "nf_ref.tsv")).read()
-    print(f"# rows {rows}; joinCounts bytes identical: {same}; computeNF bytes identical: {same_nf}")
+    # mergeTags: the k-mers of a random 400 kb sequence (70% kept), random p-values with ties
+    import random
+    rnd = random.Random(1)
+    g = "".join(rnd.choice("ACGT") for _ in range(400_000))
+    kms = [g[i:i + 31] for i in range(len(g) - 30) if rnd.random() < 0.7]
+    tab = os.path.join(d, "diff-counts.tsv.gz")
+    with gzip.open(tab, "wt", compresslevel=1) as f:
+        f.write("tag\tpvalue\tmeanA\tmeanB\tlog2FC\ts1\ts2\n")
+        for km in kms:
+            f.write("%s\t%f\t1.000000\t2.000000\t%f\t1.00\t2.00\n" % (km, rnd.choice([0.0, 0.01, round(rnd.random() * 0.05, 6)]),
+                                                                   rnd.choice([1.0, 1.0, -1.0])))
+    res[f"mergeTags ours ({len(kms)} k-mers)"] = timed([os.path.join(BIN, "mergeTags"), "-k", "31", tab], os.path.join(d, "mt_ours.tsv"))
+    res["mergeTags reference"] = timed([os.path.join(REF, "mergeTags"), "-k", "31", tab], os.path.join(d, "mt_ref.tsv"))
+    same_mt = open(os.path.join(d, "mt_ours.tsv")).read() == open(os.path.join(d, "mt_ref.tsv")).read()
+    print(f"# rows {rows}; joinCounts bytes identical: {same}; computeNF bytes identical: {same_nf}; mergeTags bytes identical: {same_mt}")
     for k, v in res.items():
         print(f"{k:48s} {v:8.2f} s")
 
