@@ -466,7 +466,8 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
 
     // ---- K1: partitions of ~PART_TARGET records (v3 consumes ~4K records per round: longer partitions
     //      amortise the partial last round)
-    const uint64_t PART_TARGET = which == 3 ? 65536 : 16384;
+    uint64_t PART_TARGET = which == 3 ? 65536 : 16384;
+    if (const char *e = getenv("DK_PART_TARGET")) { long v = atol(e); if (v >= 4096) PART_TARGET = (uint64_t)v; }   // tuning runs
     uint64_t np_want = total / PART_TARGET + 1;
     int nb_log2 = 4;
     while ((1ull << nb_log2) < np_want * 4 && nb_log2 < 24) nb_log2++;
