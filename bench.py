@@ -474,6 +474,18 @@ def run_e2e(args, cfg, ctx, keys, cnts, n, idxA, idxB, nf_mode):
 
 if __name__ == "__main__":
     a = parse()
+    # exactly ONE line on stdout: libraries (NCCL prints its version banner there) write to stderr from here on, the JSON
+    # line goes to the saved descriptor
+    sys.stdout.flush()
+    _real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    _builtin_print = print
+
+    def print(*args, **kw):                                  # noqa: A001  (only the result lines are printed in this file)
+        if kw.get("file") is None:
+            os.write(_real_stdout, (" ".join(str(x) for x in args) + "\n").encode())
+        else:
+            _builtin_print(*args, **kw)
     if a.impl == "reference":
         run_reference(a)
     else:
