@@ -8,8 +8,10 @@ concatenation of the ranks' outputs is the reference's sorted output). Global pi
                          then one broadcast of S doubles.
   * NF, full mode      : exact global median per sample by radix select; per round one all-reduce
                          of S*256 uint64 histogram bins (8 rounds).
-  * BH                 : all-reduce of R, all-gather of the candidate p-values (p <= P); every rank
-                         ranks the global candidate list and adjusts its own rows.
+  * BH                 : all-reduce of R; the candidate p-values (p <= P) are routed by value range to the
+                         rank that ranks that range (all-to-all), which answers with the adjusted values
+                         (all-to-all back); one all-gather of a scalar per rank carries the running minimum
+                         across range borders.
 The per-rank compute is behind a small backend interface so the collective logic can be tested on
 CPU with gloo (tests/test_distributed_cpu.py drives it with an oracle-backed backend)."""
 import numpy as np
@@ -103,6 +105,30 @@ class GpuBackend:
         self.t = self.m = None
 
 
+def _exchange(x, send_n, recv_n):
+    """personalised exchange of 1-D tensors: x holds the pieces for rank 0, 1, ... back to back (send_n elements each);
+    returns the pieces received from rank 0, 1, ... back to back. NCCL: one all-to-all. gloo has none, so the CPU tests
+    gather everything and keep the slices addressed to this rank (same result, test-sized data only)."""
+    rank, world = dist.get_rank(), dist.get_world_size()
+    if dist.get_backend() == "nccl":
+        out = x.new_empty(int(sum(recv_n)))
+        dist.all_to_all_single(out, x.contiguous(), output_split_sizes=recv_n, input_split_sizes=send_n)
+        return out
+    sizes = torch.tensor(send_n, dtype=torch.int64, device=x.device)
+    all_sizes = [torch.zeros_like(sizes) for _ in range(world)]
+    dist.all_gather(all_sizes, sizes)
+    mx = max(int(s.sum().item()) for s in all_sizes)
+    pad = torch.zeros(max(mx, 1), dtype=x.dtype, device=x.device)
+    pad[: x.numel()] = x
+    bufs = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(bufs, pad)
+    parts = []
+    for src in range(world):
+        off = int(all_sizes[src][:rank].sum().item())
+        parts.append(bufs[src][off: off + int(all_sizes[src][rank].item())])
+    return torch.cat(parts) if parts else x.new_empty(0)
+
+
 def _all_gather_var(x, group=None):
     """all-gather of 1-D tensors of different lengths (sizes first, then padded payload)"""
     world = dist.get_world_size(group)
@@ -158,27 +184,42 @@ def run_sharded(backend, key_ptrs, cnt_ptrs, n, r, a, idxA, idxB, pmax, fmin, nf
     nf_used = nf_text_round(nf) if nf_text_roundtrip else nf
     backend.ttest_rows(nf_used, idxA, idxB)
     cand = backend.candidates(pmax)
-    all_p = _all_gather_var(cand)
     if world == 1:
-        backend.adjust_global(all_p, R_glob)
+        backend.adjust_global(cand, R_glob)
+        n_cand = int(cand.numel())
     else:
-        # BH work is split by p-value range: rank g ranks the candidates in (g*P/world, (g+1)*P/world] (equal values
-        # share a range; under the null p is uniform, so ranges are balanced), instead of every rank sorting the whole list
-        lo = pmax * rank / world if rank else -1.0
-        hi = pmax * (rank + 1) / world if rank + 1 < world else float("inf")
-        below = all_p <= lo
-        mine = all_p[(~below) & (all_p <= hi)]
-        sp, F = backend.bh_rank_slice(mine, int(below.sum().item()), R_glob)
+        # BH is split by p-value range: rank g owns the candidates in (g*P/world, (g+1)*P/world] (equal values share a
+        # range; under the null p is uniform, so the ranges are balanced). Every rank ROUTES its candidates to their
+        # owners (all-to-all), the owner ranks its range and answers with the adjusted values (all-to-all back): the
+        # traffic and the sort per rank stay those of one shard however many ranks there are.
+        edges = torch.tensor([pmax * g / world for g in range(1, world)], dtype=torch.float64, device=cand.device)
+        send, _ = torch.sort(cand)                                    # ranges become contiguous: edges[g-1] < p <= edges[g] -> g
+        cuts = torch.searchsorted(send, edges, right=True)            # elements <= edges[g]
+        zero = torch.zeros(1, dtype=cuts.dtype, device=cand.device)
+        full = torch.full((1,), send.numel(), dtype=cuts.dtype, device=cand.device)
+        counts = torch.diff(torch.cat([zero, cuts, full])).to(torch.int64)
+        table = [torch.zeros_like(counts) for _ in range(world)]
+        dist.all_gather(table, counts)
+        table = torch.stack(table).cpu()                              # table[src][dst]
+        send_n = [int(x) for x in table[rank].tolist()]
+        recv_n = [int(x) for x in table[:, rank].tolist()]
+        n_below = int(table[:, :rank].sum().item())
+        n_cand = int(table.sum().item())
+        mine = _exchange(send, send_n, recv_n)
+        sp, F = backend.bh_rank_slice(mine, n_below, R_glob)
         # the running minimum crosses range borders: lower F by the smallest F of all higher ranges
-        first = F[:1] if F.numel() else torch.full((1,), float("inf"), dtype=torch.float64, device=all_p.device)
+        first = F[:1] if F.numel() else torch.full((1,), float("inf"), dtype=torch.float64, device=cand.device)
         mins = [torch.empty_like(first) for _ in range(world)]
         dist.all_gather(mins, first.contiguous())
         above = torch.cat(mins[rank + 1:]).min() if rank + 1 < world else None
         if above is not None and F.numel():
             F = torch.minimum(F, above)
-        backend.apply_adjusted(_all_gather_var(sp), _all_gather_var(F))
+        # adjusted value of every routed candidate: adj depends on the value only, so any member of a tie run will do
+        adj_mine = F[torch.searchsorted(sp, mine)] if mine.numel() else mine
+        adj_send = _exchange(adj_mine.contiguous(), recv_n, send_n)   # back to the senders, in `send` order
+        backend.apply_adjusted(send, adj_send)                        # `send` is this rank's candidate list, sorted
     D_loc, ties = backend.filter(pmax, fmin)
     d = torch.tensor([D_loc, ties[0], ties[1], ties[2]], dtype=torch.int64, device=device)
     dist.all_reduce(d)
     return dict(U=U_glob, R=R_glob, D=int(d[0].item()), ties=tuple(int(x) for x in d[1:].tolist()), nf=nf,
-                R_local=R_loc, U_local=U_loc, D_local=D_loc, n_cand=int(all_p.numel()))
+                R_local=R_loc, U_local=U_loc, D_local=D_loc, n_cand=n_cand)
