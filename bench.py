@@ -133,7 +133,9 @@ def cpu_path(keys, cnts, cfg, idxA, idxB, threads):
         p, fc = np.concatenate([r[0] for r in res]), np.concatenate([r[3] for r in res])
     adj = orc.bh(p)
     D = int(((adj <= PMAX) & (np.abs(fc) >= FMIN)).sum())
-    return U, R, D, time.perf_counter() - t0
+    dt = time.perf_counter() - t0
+    cpu_path.checksum = (int(np.bitwise_xor.reduce(mk)) if R else 0, int(mc.astype(np.uint32).astype(np.uint64).sum()) if R else 0)
+    return U, R, D, dt
 
 
 def make_cpu_sample(cfg, rows):
@@ -304,6 +306,18 @@ def run_ours(args):
     if rank == 0 and not args.no_cpu:
         ck, cc = make_cpu_sample(cfg, args.cpu_rows)
         cU, cR, cD, dt = cpu_path(ck, cc, cfg, idxA, idxB, 1)
+        # the same sample through the CUDA path: U, R, D and the order-independent matrix checksums must agree
+        st_s, m_s, t_s = ctx.run_path([k.ctypes.data for k in ck], [c.ctypes.data for c in cc], [len(k) for k in ck], False,
+                                      cfg["r"], cfg["a"], nf_mode, idxA, idxB, PMAX, FMIN, nf_text_roundtrip=True, keep=True)
+        gsum = m_s.checksum()
+        out["parity_check"] = {"sample_rows": args.cpu_rows, "cpu": {"U": cU, "R": cR, "D": cD, "key_xor": cpu_path.checksum[0],
+                                                                   "count_sum": cpu_path.checksum[1]},
+                               "gpu": {"U": st_s["U"], "R": st_s["R"], "D": st_s["D"], "key_xor": int(gsum[0]), "count_sum": int(gsum[1])},
+                               "equal": bool(cU == st_s["U"] and cR == st_s["R"] and cD == st_s["D"]
+                                             and cpu_path.checksum == (int(gsum[0]), int(gsum[1])))}
+        if t_s is not None:
+            t_s.free()
+        m_s.free()
         out["cpu_baseline"] = {"value": cU / dt, "unit": "k-mers/s", "cores": 1, "kind": "port", "seconds": dt,
                                "sample": f"first {args.cpu_rows} of {cfg['U']} rows of the same generator ({cU} union k-mers), "
                                          "oracle C port of the three single-threaded reference tools"}
