@@ -351,6 +351,7 @@ __global__ void __launch_bounds__(128) k_merge(MergeParams P)
 
 #include "dk_merge2.cuh"
 #include "dk_merge3.cuh"
+#include "dk_merge4.cuh"
 
 // -------------------------------------------------------- chunk bookkeeping ---
 // totals[0]=R, totals[1]=U, totals[2]=chunks requested, totals[3]=npart
@@ -455,19 +456,24 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     T.cnts = (const int32_t *const *)(tab + (size_t)S * 8);
     T.n = (const uint64_t *)(tab + (size_t)S * 16);
 
-    // kernel choice: v3 (merge-path tree, any S) by default; DK_MERGE=1|2 forces the older kernels (profiling)
+    // kernel choice: v4 (bucket join, S <= 64) by default, v3 (merge-path tree, any S) otherwise and whenever a dump
+    // holds copies of a k-mer; DK_MERGE=1|2|3 forces the older kernels (profiling)
     size_t budget = ctx->smem_optin ? ctx->smem_optin : 227 * 1024;
-    int which = 3;
+    int which = 4;
     if (const char *e = getenv("DK_MERGE")) which = atoi(e);
     M3Cfg G3;
+    M4Cfg G4;
     memset(&G3, 0, sizeof G3);
-    if (which == 3 && !m3_make_cfg(S, budget, G3)) which = 1;
+    memset(&G4, 0, sizeof G4);
+    if (which == 4 && !m4_make_cfg(S, budget, G4)) which = 3;
+    const bool have3 = m3_make_cfg(S, budget, G3);
+    if (which == 3 && !have3) which = 1;
     if (which == 2 && S > M2_S) which = 1;
 
     // ---- K1: partitions of ~PART_TARGET records (v3 consumes ~4K records per round: longer partitions
     //      amortise the partial last round)
-    uint64_t PART_TARGET = which == 3 ? 65536 : 16384;
-    if (which == 3) {       // big joins: fewer, longer partitions (less partition bookkeeping, fewer partly filled chunks) while
+    uint64_t PART_TARGET = which >= 3 ? 65536 : 16384;
+    if (which >= 3) {       // big joins: fewer, longer partitions (less partition bookkeeping, fewer partly filled chunks) while
                             // every CTA still gets >= 32 of them (A/B at cfg 2: 65536 -> 262144 = 104.3 -> 102.7 ms per step)
         const uint64_t per_cta = total / ((uint64_t)ctx->sm_count * 3 * 32);
         if (per_cta > PART_TARGET) PART_TARGET = per_cta < 262144 ? per_cta : 262144;
@@ -521,7 +527,7 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     m->S = S;
     uint32_t *chunk_part = nullptr, *chunk_seq = nullptr;
     uint64_t h_tot[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int attempt = 0; attempt < 3; attempt++) {
+    for (int attempt = 0; attempt < 5; attempt++) {
         uint64_t cap = guess + 1;   // +1: room for the stale-tail row
         if (cap >= 0xFFFFFFF0ull) { dk_matrix_release(ctx, m); return dk_fail(ctx, DK_ERR_NOMEM, "join: too many chunks"); }
         m->cap_chunks = cap;
@@ -543,7 +549,19 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
 
         DK_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
         cudaError_t e;
-        if (which == 3) {
+        if (which == 4) {
+            typedef void (*m4_fn)(MergeParams, M4Cfg, uint32_t *);
+            static const m4_fn m4_tab[7] = {k_merge4<0>, k_merge4<1>, k_merge4<2>, k_merge4<3>, k_merge4<4>, k_merge4<5>, k_merge4<6>};
+            const m4_fn k4 = m4_tab[G4.levels];
+            e = cudaFuncSetAttribute(k4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G4.smem_bytes);
+            if (e == cudaSuccess) {
+                int per_sm = (int)((budget + 1024) / ((size_t)G4.smem_bytes + 1024));
+                if (per_sm < 1) per_sm = 1;
+                if (per_sm > 2) per_sm = 2;
+                k4<<<ctx->sm_count * per_sm, M4_NT, G4.smem_bytes, ctx->stream>>>(P, G4, overflow_d);
+                e = cudaGetLastError();
+            }
+        } else if (which == 3) {
             typedef void (*m3_fn)(MergeParams, M3Cfg, uint32_t *);
             static const m3_fn m3_tab[9] = {k_merge3<0>, k_merge3<1>, k_merge3<2>, k_merge3<3>, k_merge3<4>,
                                             k_merge3<5>, k_merge3<6>, k_merge3<7>, k_merge3<8>};
@@ -588,9 +606,10 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
                     ms, pr[1] / tot, pr[2] / tot, pr[3] / tot, pr[4] / tot, pr[5] / tot, pr[6] / tot, pr[8] / tot, pr[9] / tot, pr[10] / tot, pr[7] / tot);
         }
 #endif
-        if (h_tot[4] && which == 3) {
-            // a dump holds one k-mer more than 4 times: v3's copy-index field overflowed; redo with the v1 kernel
-            which = 1;
+        if (h_tot[4] && which >= 3) {
+            // v4: a dump holds copies of a k-mer -> redo with v3 (copies become separate rows, as in the reference);
+            // v3: a dump holds one k-mer more than 4 times (its copy-index field overflowed) -> redo with the v1 kernel
+            which = (which == 4 && have3) ? 3 : 1;
             dk_dev_release(ctx, m->keys); dk_dev_release(ctx, m->cnts); dk_dev_release(ctx, m->chunk_rows);
             dk_dev_release(ctx, chunk_part); dk_dev_release(ctx, chunk_seq);
             m->keys = nullptr; m->cnts = nullptr; m->chunk_rows = nullptr;
@@ -602,7 +621,7 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
         dk_dev_release(ctx, chunk_part); dk_dev_release(ctx, chunk_seq);
         m->keys = nullptr; m->cnts = nullptr; m->chunk_rows = nullptr;
         guess = h_tot[2];
-        if (attempt == 2) { dk_matrix_release(ctx, m); return dk_fail(ctx, DK_ERR_CUDA, "join: output overflow twice"); }
+        if (attempt == 4) { dk_matrix_release(ctx, m); return dk_fail(ctx, DK_ERR_CUDA, "join: output overflow twice"); }
     }
     g_chunk_hint = h_tot[2];
     m->R = h_tot[0]; m->U = h_tot[1]; m->n_chunks = h_tot[2];

@@ -93,6 +93,44 @@ def test_join_edge_cases(ctx):
     _join_both(ctx, [np.array([1, 2], np.uint64)] * 2, [np.array([2 ** 31 - 1, 5], np.int32), np.array([7, 2 ** 31 - 1], np.int32)], 2, 6)
 
 
+def _clustered_keys(rng, n, levels):
+    """k-mers in nested clusters: every level packs a share of the keys into a 2^-12 narrower window, down to
+    runs of consecutive integers (what low-complexity sequence does to a sorted dump)"""
+    parts, width, lo = [], 1 << 62, 0
+    for _ in range(levels):
+        parts.append(lo + rng.integers(0, width, n // levels, dtype=np.uint64))
+        lo = lo + int(rng.integers(0, max(1, width - (width >> 12))))
+        width = max(width >> 12, 64)
+    parts.append(np.uint64(lo) + np.arange(min(n, 3000), dtype=np.uint64))     # a run of consecutive k-mers
+    return np.unique(np.concatenate([p.astype(np.uint64) for p in parts]))
+
+
+@pytest.mark.parametrize("S,n,levels,pp,r,a", [(16, 120000, 5, 0.6, 3, 5), (3, 60000, 4, 0.9, 1, 1), (48, 40000, 3, 0.3, 4, 3),
+                                              (64, 20000, 5, 0.5, 1, 1), (5, 200000, 2, 0.8, 2, 2), (1, 50000, 5, 1.0, 1, 1)])
+def test_join_bucket_kernel_on_clustered_kmers(ctx, S, n, levels, pp, r, a):
+    """merge v4 (monotone buckets + owner election): clusters force its round-shrinking paths (more distinct k-mers
+    in a bucket than owner levels, more rows in a round than the recurrence matrix holds)"""
+    rng = np.random.default_rng(S * 7 + levels)
+    allk = _clustered_keys(rng, n, levels)
+    keys, cnts = [], []
+    for _ in range(S):
+        m = rng.random(len(allk)) < pp
+        keys.append(allk[m])
+        cnts.append(rng.integers(1, 12, size=int(m.sum())).astype(np.int32))
+    _join_both(ctx, keys, cnts, r, a)
+
+
+@pytest.mark.parametrize("which", ["3", "1"])
+def test_join_older_merge_kernels_stay_exact(ctx, which, monkeypatch):
+    """v3 is the path for S > 64 and for dumps holding copies of a k-mer, v1 the one behind it: keep both pinned"""
+    monkeypatch.setenv("DK_MERGE", which)
+    rng = np.random.default_rng(31)
+    keys, cnts = random_dumps(rng, 16, 150000, 62, 0.075, 12, p_core=0.2)
+    _join_both(ctx, keys, cnts, 3, 5)
+    keys, cnts = random_dumps(rng, 5, 80000, 62, 0.6, 12, p_core=0.3)
+    _join_both(ctx, keys, cnts, 1, 1)
+
+
 def test_join_large_checksum_properties(ctx):
     """size-independent properties at a size the oracle would take minutes for"""
     rng = np.random.default_rng(99)
