@@ -557,7 +557,7 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
             if (e == cudaSuccess) {
                 int per_sm = (int)((budget + 1024) / ((size_t)G4.smem_bytes + 1024));
                 if (per_sm < 1) per_sm = 1;
-                if (per_sm > 2) per_sm = 2;
+                if (per_sm > M4_CTAS) per_sm = M4_CTAS;
                 k4<<<ctx->sm_count * per_sm, M4_NT, G4.smem_bytes, ctx->stream>>>(P, G4, overflow_d);
                 e = cudaGetLastError();
             }
@@ -604,6 +604,18 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
             for (int i = 1; i < 11; i++) tot += pr[i];
             fprintf(stderr, "[m3 prof] kernel %.3f ms; phase shares: stage+wait %.3f pivot %.3f pack %.3f merge %.3f heads %.3f verdict %.3f | zero %.3f scatter %.3f copyout %.3f advance %.3f\n",
                     ms, pr[1] / tot, pr[2] / tot, pr[3] / tot, pr[4] / tot, pr[5] / tot, pr[6] / tot, pr[8] / tot, pr[9] / tot, pr[10] / tot, pr[7] / tot);
+        }
+#endif
+#ifdef DK_M4_PROF
+        if (which == 4) {
+            uint32_t pr[12];
+            cudaMemcpy(pr, scal + 4, sizeof pr, cudaMemcpyDeviceToHost);
+            double tot = 0;
+            for (int i = 1; i < 12; i++) tot += pr[i];
+            fprintf(stderr, "[m4 prof] kernel %.3f ms; phase shares: stage+wait %.3f pivot %.3f clear+prefix %.3f buckets+election %.3f "
+                    "bucket scan+ranks %.3f recurrence bytes %.3f verdicts %.3f | zero %.3f scatter %.3f copyout %.3f advance %.3f\n",
+                    ms, pr[1] / tot, pr[2] / tot, pr[3] / tot, pr[4] / tot, pr[5] / tot, pr[6] / tot, pr[7] / tot, pr[8] / tot,
+                    pr[9] / tot, pr[10] / tot, pr[11] / tot);
         }
 #endif
         if (h_tot[4] && which >= 3) {

@@ -23,10 +23,12 @@
 // reruns the join with v3 (which keeps such copies as separate rows exactly like the reference).
 #pragma once
 
-#define M4_NT 512
+#define M4_NTL 8
+#define M4_NT (1 << M4_NTL)         // 256 threads; 4 CTAs per SM
+#define M4_CTAS 4
 #define M4_VT 9
-#define M4_W (M4_NT * M4_VT)       // 4608 record slots per round
-#define M4_M 4096                  // buckets per round
+#define M4_W (M4_NT * M4_VT)       // 2304 record slots per round
+#define M4_M (8 * M4_NT)            // 2048 buckets per round (8 per thread in the bucket scan)
 #define M4_J 4                     // owner levels (distinct k-mers a bucket can hold)
 #define M4_EMPTY 0xFFFFu
 #define M4_ALIAS_BYTES ((M4_J - 1) * M4_M * 2)   // own[1..J-1] is reused for the byte matrix and the row images
@@ -62,11 +64,12 @@ __device__ __forceinline__ uint32_t m4_block_excl_scan(uint32_t v, M4Small &sm, 
     __syncthreads();                       // protects sm.scan from the previous use
     if (lane == 31) sm.scan[w] = x;
     __syncthreads();
-    uint32_t off = 0, tot = 0;
+    uint32_t t = lane < M4_NT / 32 ? sm.scan[lane] : 0u;
 #pragma unroll
-    for (int i = 0; i < M4_NT / 32; i++) { uint32_t s = sm.scan[i]; if (i < w) off += s; tot += s; }
-    total = tot;
-    return off + x - v;
+    for (int o = 1; o < M4_NT / 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, t, o); if (lane >= o) t += y; }
+    total = __shfl_sync(0xffffffffu, t, M4_NT / 32 - 1);
+    const uint32_t off = __shfl_sync(0xffffffffu, t, w > 0 ? w - 1 : 0);
+    return (w > 0 ? off : 0u) + x - v;
 }
 __device__ __forceinline__ unsigned long long m4_warp_min(unsigned long long v)
 {
@@ -86,8 +89,15 @@ __device__ __forceinline__ uint32_t m4_half(const uint4 &v, int q)
     return (q & 1) ? (w >> 16) : (w & 0xffffu);
 }
 
+// -DDK_M4_PROF: thread 0 of every CTA accumulates the cycles between phase marks into prof[1..11] (units of 16 cycles)
+#ifdef DK_M4_PROF
+#define M4_MARK(i) do { if (tid == 0) { long long t__ = clock64(); atomicAdd(&prof[i], (uint32_t)((t__ - tprev) >> 4)); tprev = t__; } } while (0)
+#else
+#define M4_MARK(i) do { } while (0)
+#endif
+
 template <int LV>
-__global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uint32_t *overflow)
+__global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg G, uint32_t *overflow)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     unsigned long long *bufK = reinterpret_cast<unsigned long long *>(smem_raw);
@@ -99,7 +109,7 @@ __global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uin
     unsigned long long *keybuf = reinterpret_cast<unsigned long long *>(reinterpret_cast<unsigned char *>(own + M4_M) + G.keybuf_off);
     M4Small &sm = *reinterpret_cast<M4Small *>(smem_raw + G.off_small);
 
-    constexpr int SP = 1 << LV, caps = M4_W >> LV, ks = (caps + 4 + 3) & ~3, TPSL = 9 - LV, TPS = 1 << TPSL;
+    constexpr int SP = 1 << LV, caps = M4_W >> LV, ks = (caps + 4 + 3) & ~3, TPSL = M4_NTL - LV, TPS = 1 << TPSL;
     M4Samp<SP> &ss = *reinterpret_cast<M4Samp<SP> *>(smem_raw + G.off_small + sizeof(M4Small));
     const int S = G.S, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t npart = *P.npart;
@@ -116,6 +126,10 @@ __global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uin
     const int min_ab = P.min_abund, min_rec = P.min_rec;
     const int ps = tid >> TPSL, psub = tid & (TPS - 1);
     const uint32_t ABW = (uint32_t)G.abw, RS = (uint32_t)G.RS;
+#ifdef DK_M4_PROF
+    uint32_t *prof = overflow + 1;     // scal[4..15]
+    long long tprev = 0;
+#endif
 
     for (;;) {
         if (tid == 0) sm.part = atomicAdd(P.work_counter, 1u);
@@ -131,6 +145,9 @@ __global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uin
 
         for (;;) {   // ---- rounds
             // R0: stage the key windows (TMA), read the (count >= a) bits while the copies fly
+#ifdef DK_M4_PROF
+            if (tid == 0) tprev = clock64();
+#endif
             uint32_t lo = 0, L = 0;
             if (owner) {
                 // per-dump state lives in shared / constant-cached memory, not in registers (64-register budget)
@@ -172,6 +189,7 @@ __global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uin
             mbar_wait(bar, phase);
             phase ^= 1u;
             __syncthreads();
+            M4_MARK(1);
             // R1: pivot (smallest look-ahead key), base (smallest first key), largest staged key
             unsigned long long candk = DK_SENTINEL, firstk = DK_SENTINEL, lastk = 0;
             uint32_t ncm = 0;
@@ -181,15 +199,18 @@ __global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uin
                 if (L == (uint32_t)(caps + 1)) { candk = kw[caps]; ncm = (uint32_t)caps; } else ncm = L;
                 lastk = kw[ncm - 1];
             }
-            candk = m4_warp_min(candk);
-            firstk = m4_warp_min(firstk);
-            lastk = m4_warp_max(lastk);
-            if (lane == 0) { sm.red[0][warp] = candk; sm.red[1][warp] = firstk; sm.red[2][warp] = lastk; }
+            constexpr int OW = (SP + 31) / 32;                     // warps that hold dump owners (tid < S <= SP)
+            if (warp < OW) {
+                candk = m4_warp_min(candk);
+                firstk = m4_warp_min(firstk);
+                lastk = m4_warp_max(lastk);
+                if (lane == 0) { sm.red[0][warp] = candk; sm.red[1][warp] = firstk; sm.red[2][warp] = lastk; }
+            }
             if (tid < SP) ss.L[tid] = (uint16_t)L;
             __syncthreads();
             unsigned long long pivot = DK_SENTINEL, base = DK_SENTINEL, maxk = 0;
 #pragma unroll
-            for (int i = 0; i < M4_NT / 32; i++) {
+            for (int i = 0; i < OW; i++) {
                 unsigned long long a = sm.red[0][i], b = sm.red[1][i], c = sm.red[2][i];
                 pivot = a < pivot ? a : pivot;
                 base = b < base ? b : base;
@@ -197,6 +218,7 @@ __global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uin
             }
             if (base == DK_SENTINEL) break;                        // every window empty: partition done
             if (maxk != DK_SENTINEL && maxk + 1ull < pivot) pivot = maxk + 1ull;   // span of the keys actually staged
+            M4_MARK(2);
 
             const uint32_t slo = (uint32_t)pcur & 3u;
             const unsigned long long *kw = bufK + (size_t)ps * ks + slo;
@@ -225,6 +247,7 @@ __global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uin
                 }
                 if (tid < SP) ss.n[tid] = (uint16_t)n;
                 __syncthreads();                                   // (B)
+                M4_MARK(3);
                 T = sm.total_real;
                 if (T == 0) {                                      // a window full of one k-mer: not this kernel's case
                     if (tid == 0) atomicExch(overflow, 1u);
@@ -290,6 +313,7 @@ __global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uin
                         continue;
                     }
                 }
+                M4_MARK(4);
                 // B3: k-mers per bucket, ranks inside multi-k-mer buckets, row ids
                 uint32_t nkm = 0, mine = 0;                        // nkm: 3 bits per bucket
                 {
@@ -346,6 +370,7 @@ __global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uin
                 break;
             }
             if (stop) break;
+            M4_MARK(5);
             // B4: recurrence. Zero the byte matrix (it aliases own[1..])
             {
                 const uint32_t nw4 = (nrows * ABW + 3u) >> 2;
@@ -356,15 +381,22 @@ __global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uin
             {
                 unsigned char *abb = reinterpret_cast<unsigned char *>(abw);
                 const uint32_t m = consm & abm;
+                uint32_t rwp[(M4_VT + 1) / 2];                     // from here on bkp holds the ROW of record k
+#pragma unroll
+                for (int k = 0; k < (M4_VT + 1) / 2; k++) rwp[k] = 0;
 #pragma unroll
                 for (int k = 0; k < M4_VT; k++) {
-                    if (!((m >> k) & 1u)) continue;
+                    if (!((consm >> k) & 1u)) continue;
                     const uint32_t inf = info[M4_BK(k)];
                     const uint32_t row = (inf & 0x1fffu) + ((inf >> (16 + 2 * ((lvl >> (2 * k)) & 3u))) & 3u);
-                    abb[row * (ABW * 4u) + (uint32_t)ps] = 1;
+                    rwp[k >> 1] |= row << (16 * (k & 1));
+                    if ((m >> k) & 1u) abb[row * (ABW * 4u) + (uint32_t)ps] = 1;
                 }
+#pragma unroll
+                for (int k = 0; k < (M4_VT + 1) / 2; k++) bkp[k] = rwp[k];
             }
             __syncthreads();
+            M4_MARK(6);
             const uint32_t RPT = (nrows + M4_NT - 1) / M4_NT, rb0 = (uint32_t)tid * RPT;
             uint32_t passmask = 0;
             for (uint32_t i = 0; i < RPT && rb0 + i < nrows; i++) {
@@ -391,27 +423,34 @@ __global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uin
                 }
                 sm.have_cur = have; sm.newbase = nb; sm.nnew = nnew;
             }
+            {   // the first batch of row images is zeroed while thread 0's chunk allocation is in flight
+                // (the byte matrix under it is dead: every verdict was computed before the scan's barriers)
+                const uint32_t nbr0 = nout < (uint32_t)G.BR ? nout : (uint32_t)G.BR;
+                const uint32_t n4 = (nbr0 * RS + 3u) >> 2;
+                int4 *z = reinterpret_cast<int4 *>(rowbuf);
+                for (uint32_t i = tid; i < n4; i += M4_NT) z[i] = make_int4(0, 0, 0, 0);
+            }
             __syncthreads();
+            M4_MARK(7);
             // B5: row images of the surviving rows, coalesced copy-out
             {
                 const uint32_t have = sm.have_cur, nb = sm.newbase, ccur = sm.chunk_cur;
                 const uint32_t rp = have ? sm.rowpos : 0u;
                 for (uint32_t b0 = 0; b0 < nout; b0 += (uint32_t)G.BR) {
                     const uint32_t nbr = (nout - b0) < (uint32_t)G.BR ? (nout - b0) : (uint32_t)G.BR;
-                    {
+                    if (b0) {
                         const uint32_t n4 = (nbr * RS + 3u) >> 2;
                         int4 *z = reinterpret_cast<int4 *>(rowbuf);
                         for (uint32_t i = tid; i < n4; i += M4_NT) z[i] = make_int4(0, 0, 0, 0);
+                        __syncthreads();
                     }
-                    __syncthreads();
+                    M4_MARK(8);
                     {
 #pragma unroll
                         for (int k = 0; k < M4_VT; k++) {
                             if (!((consm >> k) & 1u)) continue;
                             const uint32_t i = (uint32_t)(psub + k * TPS);
-                            const uint32_t inf = info[M4_BK(k)];
-                            const uint32_t row = (inf & 0x1fffu) + ((inf >> (16 + 2 * ((lvl >> (2 * k)) & 3u))) & 3u);
-                            const uint32_t o = (uint32_t)orow[row] - b0;
+                            const uint32_t o = (uint32_t)orow[M4_BK(k)] - b0;
                             if (o < nbr) {
                                 rowbuf[o * RS + (uint32_t)ps] = __ldg(cp + i);
                                 if ((headm >> k) & 1u) keybuf[o] = kw[i];
@@ -419,6 +458,7 @@ __global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uin
                         }
                     }
                     __syncthreads();
+                    M4_MARK(9);
                     if (G.S4) {
                         const uint32_t S4 = (uint32_t)G.S4, n4 = nbr * S4;
                         for (uint32_t i = tid; i < n4; i += M4_NT) {
@@ -443,6 +483,7 @@ __global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uin
                         if (chunk < P.max_chunks) P.out_keys[(size_t)chunk * DK_CH + off] = keybuf[rr];
                     }
                     __syncthreads();
+                    M4_MARK(10);
                 }
             }
             // R7: advance the partition state
@@ -458,6 +499,7 @@ __global__ void __launch_bounds__(M4_NT, 2) k_merge4(MergeParams P, M4Cfg G, uin
                 sm.prow += nout; sm.puni += nrows;
             }
             __syncthreads();
+            M4_MARK(11);
         }
         __syncthreads();
         if (tid == 0) {
