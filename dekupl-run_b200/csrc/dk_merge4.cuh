@@ -263,6 +263,7 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
                 consm = 0;
 #pragma unroll
                 for (int k = 0; k < (M4_VT + 1) / 2; k++) bkp[k] = 0;
+                bool dupf = false;
 #pragma unroll
                 for (int k = 0; k < M4_VT; k++) {
                     const uint32_t i = (uint32_t)(psub + k * TPS);
@@ -271,9 +272,10 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
                         consm |= 1u << k;
                         const uint32_t f = (uint32_t)((key - base) >> wsh);
                         bkp[k >> 1] |= ((f * scale) >> 16) << (16 * (k & 1));
-                        if (i + 1u < sL && kw[i + 1] == key) atomicExch(overflow, 1u);     // copies inside a dump: v3's case
+                        dupf |= i + 1u < sL && kw[i + 1] == key;
                     }
                 }
+                if (dupf) atomicExch(overflow, 1u);                 // copies of a k-mer inside a dump: v3's case
                 // B2: owner election, level by level
                 uint32_t unres = consm;
                 lvl = 0; headm = 0;
@@ -385,15 +387,17 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
 #pragma unroll
                 for (int k = 0; k < (M4_VT + 1) / 2; k++) rwp[k] = 0;
 #pragma unroll
-                for (int k = 0; k < M4_VT; k++) {
+                for (int k = 0; k < M4_VT; k++) {                  // all loads first (a store in between would order them)
                     if (!((consm >> k) & 1u)) continue;
                     const uint32_t inf = info[M4_BK(k)];
                     const uint32_t row = (inf & 0x1fffu) + ((inf >> (16 + 2 * ((lvl >> (2 * k)) & 3u))) & 3u);
                     rwp[k >> 1] |= row << (16 * (k & 1));
-                    if ((m >> k) & 1u) abb[row * (ABW * 4u) + (uint32_t)ps] = 1;
                 }
 #pragma unroll
                 for (int k = 0; k < (M4_VT + 1) / 2; k++) bkp[k] = rwp[k];
+#pragma unroll
+                for (int k = 0; k < M4_VT; k++)
+                    if ((m >> k) & 1u) abb[M4_BK(k) * (ABW * 4u) + (uint32_t)ps] = 1;
             }
             __syncthreads();
             M4_MARK(6);
@@ -446,15 +450,28 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
                     }
                     M4_MARK(8);
                     {
+                        // three passes so that the loads of all 9 records are in flight together
+                        uint32_t op[(M4_VT + 1) / 2], live = 0;
+                        int32_t cv[M4_VT];
+#pragma unroll
+                        for (int k = 0; k < (M4_VT + 1) / 2; k++) op[k] = 0;
 #pragma unroll
                         for (int k = 0; k < M4_VT; k++) {
                             if (!((consm >> k) & 1u)) continue;
-                            const uint32_t i = (uint32_t)(psub + k * TPS);
                             const uint32_t o = (uint32_t)orow[M4_BK(k)] - b0;
-                            if (o < nbr) {
-                                rowbuf[o * RS + (uint32_t)ps] = __ldg(cp + i);
-                                if ((headm >> k) & 1u) keybuf[o] = kw[i];
-                            }
+                            if (o < nbr) { live |= 1u << k; op[k >> 1] |= o << (16 * (k & 1)); }
+                        }
+#pragma unroll
+                        for (int k = 0; k < M4_VT; k++) {
+                            cv[k] = 0;
+                            if ((live >> k) & 1u) cv[k] = __ldg(cp + (uint32_t)(psub + k * TPS));
+                        }
+#pragma unroll
+                        for (int k = 0; k < M4_VT; k++) {
+                            if (!((live >> k) & 1u)) continue;
+                            const uint32_t o = (op[k >> 1] >> (16 * (k & 1))) & 0xffffu;
+                            rowbuf[o * RS + (uint32_t)ps] = cv[k];
+                            if ((headm >> k) & 1u) keybuf[o] = kw[(uint32_t)(psub + k * TPS)];
                         }
                     }
                     __syncthreads();
