@@ -276,29 +276,48 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
                     }
                 }
                 if (dupf) atomicExch(overflow, 1u);                 // copies of a k-mer inside a dump: v3's case
-                // B2: owner election, level by level
+                // B2: owner election. Level 0 takes every record (unrolled, buckets in registers); the few records
+                // still unresolved after it walk levels 1.. in data-dependent loops (bucket recomputed from the key)
                 uint32_t unres = consm;
                 lvl = 0; headm = 0;
                 bool all_done = false;
 #pragma unroll
-                for (int l = 0; l < M4_J; l++) {
-                    uint16_t *ow = own + l * M4_M;
+                for (int k = 0; k < M4_VT; k++)
+                    if ((unres >> k) & 1u) own[M4_BK(k)] = (uint16_t)(slot0 + (uint32_t)(psub + k * TPS));
+                __syncthreads();
 #pragma unroll
-                    for (int k = 0; k < M4_VT; k++)
-                        if ((unres >> k) & 1u) ow[M4_BK(k)] = (uint16_t)(slot0 + (uint32_t)(psub + k * TPS));
-                    if (!__syncthreads_or(unres != 0u)) { all_done = true; break; }
-#pragma unroll
-                    for (int k = 0; k < M4_VT; k++)
-                        if ((unres >> k) & 1u) {
-                            const uint32_t i = (uint32_t)(psub + k * TPS);
-                            const uint32_t h = ow[M4_BK(k)];
-                            const bool ishead = h == slot0 + i;
-                            if (ishead || bufK[h] == kw[i]) {
-                                unres &= ~(1u << k);
-                                lvl |= (uint32_t)l << (2 * k);
-                                if (ishead) headm |= 1u << k;
-                            }
+                for (int k = 0; k < M4_VT; k++)
+                    if ((unres >> k) & 1u) {
+                        const uint32_t i = (uint32_t)(psub + k * TPS);
+                        const uint32_t h = own[M4_BK(k)];
+                        const bool ishead = h == slot0 + i;
+                        if (ishead || bufK[h] == kw[i]) {
+                            unres &= ~(1u << k);
+                            if (ishead) headm |= 1u << k;
                         }
+                    }
+#pragma unroll 1
+                for (int l = 1; l < M4_J; l++) {
+                    uint16_t *ow = own + l * M4_M;
+                    for (uint32_t m = unres; m; m &= m - 1) {
+                        const uint32_t i = (uint32_t)psub + (uint32_t)(__ffs(m) - 1) * TPS;
+                        const uint32_t f = (uint32_t)((kw[i] - base) >> wsh);
+                        ow[(f * scale) >> 16] = (uint16_t)(slot0 + i);
+                    }
+                    if (!__syncthreads_or(unres != 0u)) { all_done = true; break; }
+                    for (uint32_t m = unres; m; m &= m - 1) {
+                        const uint32_t k = (uint32_t)(__ffs(m) - 1);
+                        const uint32_t i = (uint32_t)psub + k * TPS;
+                        const unsigned long long key = kw[i];
+                        const uint32_t f = (uint32_t)((key - base) >> wsh);
+                        const uint32_t h = ow[(f * scale) >> 16];
+                        const bool ishead = h == slot0 + i;
+                        if (ishead || bufK[h] == key) {
+                            unres &= ~(1u << k);
+                            lvl |= (uint32_t)l << (2u * k);
+                            if (ishead) headm |= 1u << k;
+                        }
+                    }
                 }
                 if (!all_done) {
                     if (unres) {
@@ -372,6 +391,22 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
                 break;
             }
             if (stop) break;
+#ifdef DK_M4_PREFETCH   // A/B at cfg 2: 48.8 ms without, 51.5 ms with (the owner threads stall on the issue) — off
+            if (owner) {   // next round's windows (keys and counts) on their way into L2 while this round is finished
+                const unsigned long long nc = ss.cur[tid] + n, e = ss.endg[tid];
+                if (nc < e) {
+                    const unsigned long long a0 = nc & ~3ull;
+                    unsigned long long a1 = nc + (unsigned long long)(caps + 1);
+                    a1 = a1 < e ? a1 : e;
+                    a1 &= ~3ull;                                   // whole 4-record groups only: never past the arrays
+                    if (a1 > a0) {
+                        const uint32_t nrec = (uint32_t)(a1 - a0);
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(P.T.keys[tid] + a0), "r"(nrec * 8u) : "memory");
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ss.cptr[tid] + a0), "r"(nrec * 4u) : "memory");
+                    }
+                }
+            }
+#endif
             M4_MARK(5);
             // B4: recurrence. Zero the byte matrix (it aliases own[1..])
             {
