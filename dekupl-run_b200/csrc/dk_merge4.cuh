@@ -391,6 +391,7 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
                 break;
             }
             if (stop) break;
+            if (owner) ss.cur[tid] += n;                           // read again only at the top of the next round
 #ifdef DK_M4_PREFETCH   // A/B at cfg 2: 48.8 ms without, 51.5 ms with (the owner threads stall on the issue) — off
             if (owner) {   // next round's windows (keys and counts) on their way into L2 while this round is finished
                 const unsigned long long nc = ss.cur[tid] + n, e = ss.endg[tid];
@@ -539,7 +540,6 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
                 }
             }
             // R7: advance the partition state
-            if (owner) ss.cur[tid] += n;
             if (tid == 0) {
                 const uint32_t v = (sm.have_cur ? sm.rowpos : 0u) + nout;
                 if (sm.nnew) {
@@ -550,7 +550,7 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
                 if (sm.chunk_cur != CHUNK_NONE && sm.rowpos == DK_CH) { sm.chunk_cur = CHUNK_NONE; sm.rowpos = 0; }
                 sm.prow += nout; sm.puni += nrows;
             }
-            __syncthreads();
+            // no barrier here: the next round touches shared state only in ways the barriers above already order
             M4_MARK(11);
         }
         __syncthreads();
