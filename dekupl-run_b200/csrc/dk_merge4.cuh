@@ -26,8 +26,10 @@
 #define M4_NTL 8
 #define M4_NT (1 << M4_NTL)         // 256 threads; 4 CTAs per SM
 #define M4_CTAS 4
-#define M4_VT 9
-#define M4_W (M4_NT * M4_VT)       // 2304 record slots per round
+#ifndef M4_VT
+#define M4_VT 11
+#endif
+#define M4_W (M4_NT * M4_VT)       // 2816 record slots per round (A/B at cfg 2: VT 8/9/10/11/12 = 51.7/48.0/46.4/45.6/45.7 ms)
 #define M4_M (8 * M4_NT)            // 2048 buckets per round (8 per thread in the bucket scan)
 #define M4_J 4                     // owner levels (distinct k-mers a bucket can hold)
 #define M4_EMPTY 0xFFFFu

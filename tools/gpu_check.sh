@@ -1,7 +1,7 @@
 #!/bin/bash
 # One GPU-box session: parity tests, smoke, bench (no profiler), then ncu launch list + one full capture.
 # usage: tools/gpu_check.sh <tag> [kernel-regex for the full capture]
-TAG=${1:-run}; KREGEX=${2:-k_merge}
+TAG=${1:-run}; KREGEX=${2:-k_merge4}
 O=gpurun_out; mkdir -p $O
 python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?" | tee -a $O/${TAG}_pytest.log
 tail -3 $O/${TAG}_pytest.log
