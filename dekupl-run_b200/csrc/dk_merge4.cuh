@@ -268,14 +268,15 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
                 bool dupf = false;
 #pragma unroll
                 for (int k = 0; k < M4_VT; k++) {
+                    // straight-line code (no branch per record): slots past the consumable prefix hold stale keys that
+                    // are inside the window buffer; their bucket is masked into range and never used
                     const uint32_t i = (uint32_t)(psub + k * TPS);
-                    if (i < sn) {
-                        const unsigned long long key = kw[i];
-                        consm |= 1u << k;
-                        const uint32_t f = (uint32_t)((key - base) >> wsh);
-                        bkp[k >> 1] |= ((f * scale) >> 16) << (16 * (k & 1));
-                        dupf |= i + 1u < sL && kw[i + 1] == key;
-                    }
+                    const unsigned long long key = kw[i], nxt = kw[i + 1];
+                    const bool c = i < sn;
+                    consm |= (c ? 1u : 0u) << k;
+                    const uint32_t f = (uint32_t)((key - base) >> wsh);
+                    bkp[k >> 1] |= (((f * scale) >> 16) & (uint32_t)(M4_M - 1)) << (16 * (k & 1));
+                    dupf |= c && i + 1u < sL && nxt == key;
                 }
                 if (dupf) atomicExch(overflow, 1u);                 // copies of a k-mer inside a dump: v3's case
                 // B2: owner election. Level 0 takes every record (unrolled, buckets in registers); the few records
@@ -426,8 +427,7 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
                 for (int k = 0; k < (M4_VT + 1) / 2; k++) rwp[k] = 0;
 #pragma unroll
                 for (int k = 0; k < M4_VT; k++) {                  // all loads first (a store in between would order them)
-                    if (!((consm >> k) & 1u)) continue;
-                    const uint32_t inf = info[M4_BK(k)];
+                    const uint32_t inf = info[M4_BK(k)];           // unconditional: in range for every slot, used under consm only
                     const uint32_t row = (inf & 0x1fffu) + ((inf >> (16 + 2 * ((lvl >> (2 * k)) & 3u))) & 3u);
                     rwp[k >> 1] |= row << (16 * (k & 1));
                 }
