@@ -23,15 +23,19 @@
 // reruns the join with v3 (which keeps such copies as separate rows exactly like the reference).
 #pragma once
 
+#ifndef M4_NTL
 #define M4_NTL 8
-#define M4_NT (1 << M4_NTL)         // 256 threads; 4 CTAs per SM
 #define M4_CTAS 4
+#endif
+#define M4_NT (1 << M4_NTL)         // 256 threads; 4 CTAs per SM
 #ifndef M4_VT
 #define M4_VT 11
 #endif
 #define M4_W (M4_NT * M4_VT)       // 2816 record slots per round (A/B at cfg 2: VT 8/9/10/11/12 = 51.7/48.0/46.4/45.6/45.7 ms)
 #define M4_M (8 * M4_NT)            // 2048 buckets per round (8 per thread in the bucket scan)
+#ifndef M4_J
 #define M4_J 4                     // owner levels (distinct k-mers a bucket can hold)
+#endif
 #define M4_EMPTY 0xFFFFu
 #define M4_ALIAS_BYTES ((M4_J - 1) * M4_M * 2)   // own[1..J-1] is reused for the byte matrix and the row images
 
@@ -451,19 +455,14 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
             const uint32_t obase = m4_block_excl_scan(__popc(passmask), sm, nout);
             for (uint32_t i = 0; i < RPT && rb0 + i < nrows; i++)
                 orow[rb0 + i] = ((passmask >> i) & 1u) ? (uint16_t)(obase + __popc(passmask & ((1u << i) - 1u))) : (uint16_t)0xFFFFu;
-            if (tid == 0) {   // chunk allocation for nout rows appended to the partition's chunk sequence
-                const uint32_t have = (sm.chunk_cur != CHUNK_NONE) ? 1u : 0u;
-                const uint32_t slots = have ? (DK_CH - sm.rowpos) : 0u;
-                const uint32_t nnew = nout > slots ? (nout - slots + DK_CH - 1) / DK_CH : 0u;
-                uint32_t nb = 0;
-                if (nnew) {
-                    nb = atomicAdd(P.chunk_counter, nnew);
-                    for (uint32_t k = 0; k < nnew; k++) {
-                        const uint32_t id = nb + k;
-                        if (id < P.max_chunks) { P.chunk_part[id] = part; P.chunk_seq[id] = sm.seq + k; P.chunk_rows[id] = DK_CH; }
-                    }
-                }
-                sm.have_cur = have; sm.newbase = nb; sm.nnew = nnew;
+            // chunk allocation for nout rows appended to the partition's chunk sequence: thread 0 ISSUES the global atomic
+            // here and consumes its result only after the row images are built (the round trip hides behind that pass)
+            uint32_t a_have = 0, a_nnew = 0, a_nb = 0;
+            if (tid == 0) {
+                a_have = (sm.chunk_cur != CHUNK_NONE) ? 1u : 0u;
+                const uint32_t slots = a_have ? (DK_CH - sm.rowpos) : 0u;
+                a_nnew = nout > slots ? (nout - slots + DK_CH - 1) / DK_CH : 0u;
+                if (a_nnew) a_nb = atomicAdd(P.chunk_counter, a_nnew);
             }
             {   // the first batch of row images is zeroed while thread 0's chunk allocation is in flight
                 // (the byte matrix under it is dead: every verdict was computed before the scan's barriers)
@@ -476,8 +475,6 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
             M4_MARK(7);
             // B5: row images of the surviving rows, coalesced copy-out
             {
-                const uint32_t have = sm.have_cur, nb = sm.newbase, ccur = sm.chunk_cur;
-                const uint32_t rp = have ? sm.rowpos : 0u;
                 for (uint32_t b0 = 0; b0 < nout; b0 += (uint32_t)G.BR) {
                     const uint32_t nbr = (nout - b0) < (uint32_t)G.BR ? (nout - b0) : (uint32_t)G.BR;
                     if (b0) {
@@ -512,8 +509,17 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
                             if ((headm >> k) & 1u) keybuf[o] = kw[(uint32_t)(psub + k * TPS)];
                         }
                     }
+                    if (tid == 0 && b0 == 0) {                      // the allocation is needed from here on
+                        for (uint32_t k = 0; k < a_nnew; k++) {
+                            const uint32_t id = a_nb + k;
+                            if (id < P.max_chunks) { P.chunk_part[id] = part; P.chunk_seq[id] = sm.seq + k; P.chunk_rows[id] = DK_CH; }
+                        }
+                        sm.have_cur = a_have; sm.newbase = a_nb;
+                    }
                     __syncthreads();
                     M4_MARK(9);
+                    const uint32_t have = sm.have_cur, nb = sm.newbase, ccur = sm.chunk_cur;
+                    const uint32_t rp = have ? sm.rowpos : 0u;
                     if (G.S4) {
                         const uint32_t S4 = (uint32_t)G.S4, n4 = nbr * S4;
                         for (uint32_t i = tid; i < n4; i += M4_NT) {
@@ -543,11 +549,11 @@ __global__ void __launch_bounds__(M4_NT, M4_CTAS) k_merge4(MergeParams P, M4Cfg 
             }
             // R7: advance the partition state
             if (tid == 0) {
-                const uint32_t v = (sm.have_cur ? sm.rowpos : 0u) + nout;
-                if (sm.nnew) {
-                    sm.chunk_cur = sm.newbase + sm.nnew - 1;
-                    sm.seq += sm.nnew;
-                    sm.rowpos = v - (sm.have_cur + sm.nnew - 1) * DK_CH;
+                const uint32_t v = (a_have ? sm.rowpos : 0u) + nout;
+                if (a_nnew) {
+                    sm.chunk_cur = a_nb + a_nnew - 1;
+                    sm.seq += a_nnew;
+                    sm.rowpos = v - (a_have + a_nnew - 1) * DK_CH;
                 } else sm.rowpos = v;
                 if (sm.chunk_cur != CHUNK_NONE && sm.rowpos == DK_CH) { sm.chunk_cur = CHUNK_NONE; sm.rowpos = 0; }
                 sm.prow += nout; sm.puni += nrows;
@@ -592,7 +598,7 @@ static bool m4_make_cfg(int S, size_t smem_budget, M4Cfg &G)
     size_t off = dk_round_up((size_t)sp * G.ks * 8, 128);
     G.off_own = (uint32_t)off; off += (size_t)M4_J * M4_M * 2;
     G.off_info = (uint32_t)off; off += (size_t)M4_M * 4;
-    G.off_orow = (uint32_t)off; off += dk_round_up((size_t)M4_W * 2, 128);
+    G.off_orow = (uint32_t)off; off += dk_round_up((size_t)(G.RMAX < M4_W ? G.RMAX : M4_W) * 2 + 16, 128);   // one slot per row
     G.off_small = (uint32_t)off; off += dk_round_up(sizeof(M4Small) + (size_t)sp * 28 + 16, 128);
     G.smem_bytes = (uint32_t)off;
     return off <= smem_budget;
