@@ -395,6 +395,24 @@ __global__ void k_stale_tail(uint64_t *keys, int32_t *cnts, uint32_t *chunk_rows
     }
 }
 
+// records and distinct k-mers of partitions [0, n): the probe that picks the merge kernel (see dk_join_impl)
+__global__ void k_probe_stats(const uint32_t *part_union, const uint64_t *starts, int S, uint32_t n, uint64_t *out)
+{
+    __shared__ uint64_t su[32];
+    uint64_t u = 0;
+    for (uint32_t p = threadIdx.x; p < n; p += blockDim.x) u += part_union[p];
+    for (int o = 16; o; o >>= 1) u += __shfl_down_sync(0xffffffffu, u, o);
+    if ((threadIdx.x & 31) == 0) su[threadIdx.x >> 5] = u;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        u = 0;
+        for (int w = 0; w < (blockDim.x + 31) / 32; w++) u += su[w];
+        uint64_t rec = 0;
+        for (int s = 0; s < S; s++) rec += starts[(size_t)n * S + s] - starts[s];
+        out[0] = u; out[1] = rec;
+    }
+}
+
 // ------------------------------------------------------------- host driver ---
 struct MergeCfg { int gw, spl, chk, nslot; };
 static MergeCfg pick_cfg(int S)
@@ -460,7 +478,8 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     // holds copies of a k-mer; DK_MERGE=1|2|3 forces the older kernels (profiling)
     size_t budget = ctx->smem_optin ? ctx->smem_optin : 227 * 1024;
     int which = 4;
-    if (const char *e = getenv("DK_MERGE")) which = atoi(e);
+    bool auto_pick = true;           // v4 or v3 by a probe of the data (below) unless DK_MERGE forces one
+    if (const char *e = getenv("DK_MERGE")) { which = atoi(e); auto_pick = false; }
     M3Cfg G3;
     M4Cfg G4;
     memset(&G3, 0, sizeof G3);
@@ -506,6 +525,13 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     DK_TRY(dk_scan_excl_u32(ctx, flag, rank, NB));
     k_part_starts<<<NB + 1, 32, 0, st>>>(T, S, NB, range, flag, rank, starts, npart_d); DK_LAUNCHED(ctx);
 
+    uint32_t NP_host = 0;
+    bool picked = false;
+    if (which == 4 && auto_pick) {
+        DK_CUDA(ctx, cudaMemcpyAsync(&NP_host, npart_d, 4, cudaMemcpyDeviceToHost, st));
+        DK_CUDA(ctx, cudaStreamSynchronize(st));
+    }
+
     // ---- K2 launch geometry
     MergeCfg cfg = pick_cfg(S);
     size_t stream_bytes = dk_round_up((size_t)S * (cfg.chk * cfg.nslot * 12 + cfg.nslot * 8), 16);
@@ -548,46 +574,77 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
         P.part_nchunks = part_nchunks; P.part_rows = part_rows; P.part_union = part_union;
 
         DK_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
-        cudaError_t e;
-        if (which == 4) {
-            typedef void (*m4_fn)(MergeParams, M4Cfg, uint32_t *);
-            static const m4_fn m4_tab[7] = {k_merge4<0>, k_merge4<1>, k_merge4<2>, k_merge4<3>, k_merge4<4>, k_merge4<5>, k_merge4<6>};
-            const m4_fn k4 = m4_tab[G4.levels];
-            e = cudaFuncSetAttribute(k4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G4.smem_bytes);
+        cudaError_t e = cudaSuccess;
+        auto launch_k = [&](int wk, int max_ctas) -> cudaError_t {
+            cudaError_t e;
+            auto clampg = [&](int g) { return (max_ctas > 0 && g > max_ctas) ? max_ctas : g; };
+            if (wk == 4) {
+                typedef void (*m4_fn)(MergeParams, M4Cfg, uint32_t *);
+                static const m4_fn m4_tab[7] = {k_merge4<0>, k_merge4<1>, k_merge4<2>, k_merge4<3>, k_merge4<4>, k_merge4<5>, k_merge4<6>};
+                const m4_fn k4 = m4_tab[G4.levels];
+                e = cudaFuncSetAttribute(k4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G4.smem_bytes);
+                if (e == cudaSuccess) {
+                    int per_sm = (int)((budget + 1024) / ((size_t)G4.smem_bytes + 1024));
+                    if (per_sm < 1) per_sm = 1;
+                    if (per_sm > M4_CTAS) per_sm = M4_CTAS;
+                    k4<<<clampg(ctx->sm_count * per_sm), M4_NT, G4.smem_bytes, ctx->stream>>>(P, G4, overflow_d);
+                    e = cudaGetLastError();
+                }
+            } else if (wk == 3) {
+                typedef void (*m3_fn)(MergeParams, M3Cfg, uint32_t *);
+                static const m3_fn m3_tab[9] = {k_merge3<0>, k_merge3<1>, k_merge3<2>, k_merge3<3>, k_merge3<4>,
+                                                k_merge3<5>, k_merge3<6>, k_merge3<7>, k_merge3<8>};
+                const m3_fn k3 = m3_tab[G3.levels];
+                e = cudaFuncSetAttribute(k3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G3.smem_bytes);
+                if (e == cudaSuccess) {
+                    int per_sm = (int)((budget + 1024) / ((size_t)G3.smem_bytes + 1024));
+                    if (per_sm < 1) per_sm = 1;
+                    if (per_sm > 3) per_sm = 3;
+                    k3<<<clampg(ctx->sm_count * per_sm), M3_NT, G3.smem_bytes, ctx->stream>>>(P, G3, overflow_d);
+                    e = cudaGetLastError();
+                }
+            } else if (wk == 2) {
+                e = cudaFuncSetAttribute(k_merge2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M2Smem));
+                if (e == cudaSuccess) {
+                    int per_sm = (int)(budget / (sizeof(M2Smem) + 1024));
+                    if (per_sm < 1) per_sm = 1;
+                    k_merge2<<<ctx->sm_count * per_sm, M2_NT, sizeof(M2Smem), ctx->stream>>>(P);
+                    e = cudaGetLastError();
+                }
+            } else if (cfg.gw == 16) e = launch_merge<16, 1, 8, 4>(ctx, P, warps, grid, smem);
+            else if (cfg.spl == 1) e = launch_merge<32, 1, 8, 4>(ctx, P, warps, grid, smem);
+            else if (cfg.spl == 2) e = launch_merge<32, 2, 8, 4>(ctx, P, warps, grid, smem);
+            else if (cfg.spl == 4) e = launch_merge<32, 4, 8, 2>(ctx, P, warps, grid, smem);
+            else e = launch_merge<32, 8, 8, 2>(ctx, P, warps, grid, smem);
+            ctx->launches++;
+            return e;
+        };
+        // Probe: v4's cost is per ROW of the union (bucket tables, byte matrix), v3's per record. On data where a k-mer
+        // occurs in few dumps (config 5: 2.1 records per k-mer) v3 is the faster kernel (34 vs 74 ms), on cohort-like data
+        // v4 is (cfg 2: 44 vs 71 ms, cfg 3: 20 vs 35 ms). So v4 first merges a few partitions (~1-3% of the input), the
+        // records-per-k-mer ratio of those decides, and the chosen kernel takes the remaining partitions: both kernels
+        // append to the same chunked matrix through the same partition tables.
+        if (which == 4 && auto_pick && !picked && have3 && NP_host >= 64) {
+            uint32_t probe_n = NP_host / 32;
+            const uint32_t cap_n = (uint32_t)ctx->sm_count * M4_CTAS;
+            if (probe_n > cap_n) probe_n = cap_n;
+            uint32_t *probe_d = (uint32_t *)(totals + 6);
+            uint64_t *pstat_d = totals + 4, h_ps[2] = {0, 0};   // totals[4..5] are rewritten by k_join_totals afterwards
+            DK_CUDA(ctx, cudaMemcpyAsync(probe_d, &probe_n, 4, cudaMemcpyHostToDevice, st));
+            P.npart = probe_d;
+            e = launch_k(4, (int)probe_n);
             if (e == cudaSuccess) {
-                int per_sm = (int)((budget + 1024) / ((size_t)G4.smem_bytes + 1024));
-                if (per_sm < 1) per_sm = 1;
-                if (per_sm > M4_CTAS) per_sm = M4_CTAS;
-                k4<<<ctx->sm_count * per_sm, M4_NT, G4.smem_bytes, ctx->stream>>>(P, G4, overflow_d);
-                e = cudaGetLastError();
+                k_probe_stats<<<1, 256, 0, st>>>(part_union, starts, S, probe_n, pstat_d); DK_LAUNCHED(ctx);
+                DK_CUDA(ctx, cudaMemcpyAsync(h_ps, pstat_d, 16, cudaMemcpyDeviceToHost, st));
+                DK_CUDA(ctx, cudaStreamSynchronize(st));
+                if (h_ps[0] && (double)h_ps[1] < 4.0 * (double)h_ps[0]) which = 3;      // < 4 records per k-mer
+                picked = true;
+                DK_CUDA(ctx, cudaMemcpyAsync(work_d, &probe_n, 4, cudaMemcpyHostToDevice, st));
+                DK_CUDA(ctx, cudaStreamSynchronize(st));                                // probe_n is a stack variable
+                P.npart = npart_d;
             }
-        } else if (which == 3) {
-            typedef void (*m3_fn)(MergeParams, M3Cfg, uint32_t *);
-            static const m3_fn m3_tab[9] = {k_merge3<0>, k_merge3<1>, k_merge3<2>, k_merge3<3>, k_merge3<4>,
-                                            k_merge3<5>, k_merge3<6>, k_merge3<7>, k_merge3<8>};
-            const m3_fn k3 = m3_tab[G3.levels];
-            e = cudaFuncSetAttribute(k3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G3.smem_bytes);
-            if (e == cudaSuccess) {
-                int per_sm = (int)((budget + 1024) / ((size_t)G3.smem_bytes + 1024));
-                if (per_sm < 1) per_sm = 1;
-                if (per_sm > 3) per_sm = 3;
-                k3<<<ctx->sm_count * per_sm, M3_NT, G3.smem_bytes, ctx->stream>>>(P, G3, overflow_d);
-                e = cudaGetLastError();
-            }
-        } else if (which == 2) {
-            e = cudaFuncSetAttribute(k_merge2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M2Smem));
-            if (e == cudaSuccess) {
-                int per_sm = (int)(budget / (sizeof(M2Smem) + 1024));
-                if (per_sm < 1) per_sm = 1;
-                k_merge2<<<ctx->sm_count * per_sm, M2_NT, sizeof(M2Smem), ctx->stream>>>(P);
-                e = cudaGetLastError();
-            }
-        } else if (cfg.gw == 16) e = launch_merge<16, 1, 8, 4>(ctx, P, warps, grid, smem);
-        else if (cfg.spl == 1) e = launch_merge<32, 1, 8, 4>(ctx, P, warps, grid, smem);
-        else if (cfg.spl == 2) e = launch_merge<32, 2, 8, 4>(ctx, P, warps, grid, smem);
-        else if (cfg.spl == 4) e = launch_merge<32, 4, 8, 2>(ctx, P, warps, grid, smem);
-        else e = launch_merge<32, 8, 8, 2>(ctx, P, warps, grid, smem);
-        ctx->launches++;
+        }
+        if (e == cudaSuccess) e = launch_k(which, 0);
         if (e != cudaSuccess) { dk_matrix_release(ctx, m); return dk_fail(ctx, DK_ERR_CUDA, "merge launch: %s", cudaGetErrorString(e)); }
         DK_CUDA(ctx, cudaEventRecord(ctx->ev[3], st));
         k_join_totals<<<1, 256, 0, st>>>(part_rows, part_union, npart_d, chunkctr_d, overflow_d, totals); DK_LAUNCHED(ctx);

@@ -120,6 +120,15 @@ def test_join_bucket_kernel_on_clustered_kmers(ctx, S, n, levels, pp, r, a):
     _join_both(ctx, keys, cnts, r, a)
 
 
+def test_join_probe_hands_sparse_data_to_the_merge_tree(ctx):
+    """enough partitions for the kernel-choice probe (dk_join_impl): ~2 records per k-mer, so the first partitions are
+    merged by v4 and the rest by v3 into the same matrix; the result must not show the seam"""
+    rng = np.random.default_rng(77)
+    keys, cnts = random_dumps(rng, 16, 6_000_000, 62, 0.12, 12)
+    _join_both(ctx, keys, cnts, 2, 3)
+    _join_both(ctx, keys, cnts, 1, 1)
+
+
 @pytest.mark.parametrize("which", ["3", "1"])
 def test_join_older_merge_kernels_stay_exact(ctx, which, monkeypatch):
     """v3 is the path for S > 64 and for dumps holding copies of a k-mer, v1 the one behind it: keep both pinned"""
