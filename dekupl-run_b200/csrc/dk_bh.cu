@@ -145,6 +145,8 @@ extern "C" int dk_ttest_candidates(dk_ctx *ctx, dk_ttest *t, double p_cut, uint6
         DK_CUDA(ctx, cudaStreamSynchronize(st));
     }
     dk_dev_release(ctx, t->cand_p); dk_dev_release(ctx, t->cand_row);
+    // adjusted values belong to the candidate list they were written through (dk_ttest_filter walks that list): a new list voids them
+    dk_dev_release(ctx, t->p_adj); t->p_adj = nullptr;
     t->cand_p = (double *)dk_dev_alloc(ctx, sizeof(double) * (nc + 1));
     t->cand_row = (uint32_t *)dk_dev_alloc(ctx, sizeof(uint32_t) * (nc + 1));
     if (!t->cand_p || !t->cand_row) return DK_ERR_NOMEM;

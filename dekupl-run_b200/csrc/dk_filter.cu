@@ -39,6 +39,35 @@ __global__ void k_filter(const double *p_adj, const double *l2fc, uint64_t R, do
         if (k < cap) surv[k] = i;
     }
 }
+// the same test over the BH candidates only: p_adj is NaN (never <= pmax, never a tie) on every other row, because
+// dk_ttest_apply_adjusted writes adjusted values at the candidate rows alone — 20x fewer rows to look at than R at P = 0.05
+__global__ void k_filter_cand(const uint32_t *crow, uint64_t nc, const double *p_adj, const double *l2fc, double pmax, double fmin_,
+                              unsigned long long *counter, uint64_t *surv /*may be null: count only*/, uint64_t cap,
+                              unsigned long long *ties)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool keep = false;
+    uint64_t row = 0;
+    if (i < nc) {
+        row = crow[i];
+        double p = p_adj[row], f = fabs(l2fc[row]);
+        keep = (p <= pmax) && (f >= fmin_);                              // TtestFilter.c:486
+        if (!surv) {   // tie census on the counting pass only
+            if (fabs(p - pmax) <= 1e-9 * fabs(pmax) && (f >= fmin_)) atomicAdd(&ties[0], 1ull);
+            if (fmin_ != 0 && fabs(f - fmin_) <= 1e-9 * fabs(fmin_) && (p <= pmax)) atomicAdd(&ties[1], 1ull);
+        }
+    }
+    unsigned b = __ballot_sync(0xffffffffu, keep);
+    if (!b) return;
+    int lane = threadIdx.x & 31, leader = __ffs(b) - 1;
+    unsigned long long base = 0;
+    if (lane == leader) base = atomicAdd(counter, (unsigned long long)__popc(b));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (keep && surv) {
+        uint64_t k = base + __popc(b & ((1u << lane) - 1u));
+        if (k < cap) surv[k] = row;
+    }
+}
 __global__ void k_u64_to_u32(const uint64_t *in, uint32_t *out, uint64_t n)
 {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -54,9 +83,13 @@ extern "C" int dk_ttest_filter(dk_ctx *ctx, dk_ttest *t, double pmax, double fmi
     DK_CUDA(ctx, cudaMemsetAsync(ctr, 0, 64, st));
     DK_CUDA(ctx, cudaMemsetAsync(t->tie_counts, 0, 16, st));          // keep [2] (sd ties from the row pass)
     unsigned grid = (unsigned)((t->R + 255) / 256);
+    const bool by_cand = t->cand_row != nullptr;                      // the list the adjusted values were written through
+    const unsigned cgrid = (unsigned)((t->n_cand + 255) / 256);
     uint64_t D = 0;
-    if (t->R) {
-        k_filter<<<grid, 256, 0, st>>>(t->p_adj, t->log2fc, t->R, pmax, fmin_, ctr, nullptr, 0, (unsigned long long *)t->tie_counts);
+    if (t->R && !(by_cand && t->n_cand == 0)) {
+        if (by_cand) k_filter_cand<<<cgrid, 256, 0, st>>>(t->cand_row, t->n_cand, t->p_adj, t->log2fc, pmax, fmin_, ctr, nullptr, 0,
+                                                         (unsigned long long *)t->tie_counts);
+        else k_filter<<<grid, 256, 0, st>>>(t->p_adj, t->log2fc, t->R, pmax, fmin_, ctr, nullptr, 0, (unsigned long long *)t->tie_counts);
         DK_LAUNCHED(ctx);
         DK_CUDA(ctx, cudaMemcpyAsync(&D, ctr, 8, cudaMemcpyDeviceToHost, st));
         DK_CUDA(ctx, cudaStreamSynchronize(st));
@@ -70,7 +103,9 @@ extern "C" int dk_ttest_filter(dk_ctx *ctx, dk_ttest *t, double pmax, double fmi
         if (!k0 || !k1 || !v0 || !v1) return DK_ERR_NOMEM;
         DK_CUDA(ctx, cudaMemsetAsync(ctr, 0, 8, st));
         DK_CUDA(ctx, cudaMemsetAsync(v0, 0, 4 * D, st));
-        k_filter<<<grid, 256, 0, st>>>(t->p_adj, t->log2fc, t->R, pmax, fmin_, ctr, k0, D, nullptr); DK_LAUNCHED(ctx);
+        if (by_cand) k_filter_cand<<<cgrid, 256, 0, st>>>(t->cand_row, t->n_cand, t->p_adj, t->log2fc, pmax, fmin_, ctr, k0, D, nullptr);
+        else k_filter<<<grid, 256, 0, st>>>(t->p_adj, t->log2fc, t->R, pmax, fmin_, ctr, k0, D, nullptr);
+        DK_LAUNCHED(ctx);
         uint64_t *sk; uint32_t *sv;
         DK_TRY(dk_sort_pairs_u64(ctx, k0, v0, k1, v1, D, &sk, &sv));  // ascending row index == reference order
         k_u64_to_u32<<<(unsigned)((D + 255) / 256), 256, 0, st>>>(sk, t->surv_row, D); DK_LAUNCHED(ctx);
