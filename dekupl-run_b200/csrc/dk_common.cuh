@@ -26,6 +26,7 @@ struct dk_ctx {
     std::multimap<size_t, void *> free_blocks;
     std::map<void *, size_t> live;
     size_t cached_bytes = 0;
+    uint64_t chunk_hint = 0;      // matrix chunks the previous join of THIS context needed (sizes the next one)
 };
 
 int dk_fail(dk_ctx *ctx, int code, const char *fmt, ...);

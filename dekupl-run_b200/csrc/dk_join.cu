@@ -352,6 +352,7 @@ __global__ void __launch_bounds__(128) k_merge(MergeParams P)
 #include "dk_merge2.cuh"
 #include "dk_merge3.cuh"
 #include "dk_merge4.cuh"
+#include "dk_merge5.cuh"
 
 // -------------------------------------------------------- chunk bookkeeping ---
 // totals[0]=R, totals[1]=U, totals[2]=chunks requested, totals[3]=npart
@@ -441,8 +442,6 @@ void dk_matrix_release(dk_ctx *ctx, dk_matrix *m)
     delete m;
 }
 
-static uint64_t g_chunk_hint = 0;   // chunks needed by the previous join (sizes the next one)
-
 int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int32_t *const *cnts_dev,
                  const uint64_t *n, int min_rec, int min_abund, int emit_stale_tail, dk_matrix **out)
 {
@@ -477,13 +476,17 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     // kernel choice: v4 (bucket join, S <= 64) by default, v3 (merge-path tree, any S) otherwise and whenever a dump
     // holds copies of a k-mer; DK_MERGE=1|2|3 forces the older kernels (profiling)
     size_t budget = ctx->smem_optin ? ctx->smem_optin : 227 * 1024;
-    int which = 4;
-    bool auto_pick = true;           // v4 or v3 by a probe of the data (below) unless DK_MERGE forces one
+    int which = 5;
+    bool auto_pick = true;           // v4 hands sparse unions to v3 after a probe of the data (below) unless DK_MERGE forces a kernel
     if (const char *e = getenv("DK_MERGE")) { which = atoi(e); auto_pick = false; }
     M3Cfg G3;
     M4Cfg G4;
+    M5Cfg G5;
+    int lv5 = 4;
     memset(&G3, 0, sizeof G3);
     memset(&G4, 0, sizeof G4);
+    memset(&G5, 0, sizeof G5);
+    if (which == 5 && !m5_make_cfg(S, budget, G5, lv5)) which = 4;      // v5: S <= 32
     if (which == 4 && !m4_make_cfg(S, budget, G4)) which = 3;
     const bool have3 = m3_make_cfg(S, budget, G3);
     if (which == 3 && !have3) which = 1;
@@ -492,6 +495,7 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     // ---- K1: partitions of ~PART_TARGET records (v3 consumes ~4K records per round: longer partitions
     //      amortise the partial last round)
     uint64_t PART_TARGET = which >= 3 ? 65536 : 16384;
+    if (which == 5) auto_pick = false;
     if (which >= 3) {       // big joins: fewer, longer partitions (less partition bookkeeping, fewer partly filled chunks) while
                             // every CTA still gets >= 32 of them (A/B at cfg 2: 65536 -> 262144 = 104.3 -> 102.7 ms per step)
         const uint64_t per_cta = total / ((uint64_t)ctx->sm_count * 3 * 32);
@@ -514,7 +518,11 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     // scalars: [0]=npart [1]=work_counter [2]=chunk_counter ; then part tables
     uint32_t *scal = (uint32_t *)dk_dev_alloc(ctx, sizeof(uint32_t) * (16 + 4 * (size_t)NPmax));
     uint64_t *totals = (uint64_t *)dk_dev_alloc(ctx, 64);
-    if (!range || !below || !flag || !rank || !starts || !scal || !totals) return DK_ERR_NOMEM;
+    auto drop_tables = [&]() {
+        dk_dev_release(ctx, tab); dk_dev_release(ctx, range); dk_dev_release(ctx, below); dk_dev_release(ctx, flag);
+        dk_dev_release(ctx, rank); dk_dev_release(ctx, starts); dk_dev_release(ctx, scal); dk_dev_release(ctx, totals);
+    };
+    if (!range || !below || !flag || !rank || !starts || !scal || !totals) { drop_tables(); return DK_ERR_NOMEM; }
     uint32_t *npart_d = scal, *work_d = scal + 1, *chunkctr_d = scal + 2, *overflow_d = scal + 3;
     uint32_t *part_nchunks = scal + 16, *part_rows = part_nchunks + NPmax, *part_union = part_rows + NPmax,
              *part_choff = part_union + NPmax;   // NPmax entries (+1 lives in rank reuse below)
@@ -547,22 +555,27 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     int grid = ctx->sm_count * ctas_per_sm;
 
     // ---- output capacity: previous need, else a guess; retried with the exact need on overflow
-    uint64_t guess = g_chunk_hint ? g_chunk_hint + g_chunk_hint / 16 + 64
+    uint64_t guess = ctx->chunk_hint ? ctx->chunk_hint + ctx->chunk_hint / 16 + 64
                                   : (total / (uint64_t)(min_rec > 1 ? min_rec : 1) / 4) / DK_CH + NPmax / 4 + 64;
     dk_matrix *m = new dk_matrix();
     m->S = S;
     uint32_t *chunk_part = nullptr, *chunk_seq = nullptr;
     uint64_t h_tot[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int attempt = 0; attempt < 5; attempt++) {
+    auto drop_chunks = [&]() {
+        dk_dev_release(ctx, chunk_part); dk_dev_release(ctx, chunk_seq);
+        chunk_part = chunk_seq = nullptr;
+    };
+    // capacity retries and kernel fallbacks are counted apart: a fallback (v5/v4 -> v3 -> v1) is not a failed attempt
+    for (int attempt = 0, fallbacks = 0; attempt < 3 && fallbacks < 3;) {
         uint64_t cap = guess + 1;   // +1: room for the stale-tail row
-        if (cap >= 0xFFFFFFF0ull) { dk_matrix_release(ctx, m); return dk_fail(ctx, DK_ERR_NOMEM, "join: too many chunks"); }
+        if (cap >= 0xFFFFFFF0ull) { dk_matrix_release(ctx, m); drop_tables(); return dk_fail(ctx, DK_ERR_NOMEM, "join: too many chunks"); }
         m->cap_chunks = cap;
         m->keys = (uint64_t *)dk_dev_alloc(ctx, sizeof(uint64_t) * cap * DK_CH);
         m->cnts = (int32_t *)dk_dev_alloc(ctx, sizeof(int32_t) * cap * DK_CH * S);
         m->chunk_rows = (uint32_t *)dk_dev_alloc(ctx, sizeof(uint32_t) * cap);
         chunk_part = (uint32_t *)dk_dev_alloc(ctx, sizeof(uint32_t) * cap);
         chunk_seq = (uint32_t *)dk_dev_alloc(ctx, sizeof(uint32_t) * cap);
-        if (!m->keys || !m->cnts || !m->chunk_rows || !chunk_part || !chunk_seq) { dk_matrix_release(ctx, m); return DK_ERR_NOMEM; }
+        if (!m->keys || !m->cnts || !m->chunk_rows || !chunk_part || !chunk_seq) { dk_matrix_release(ctx, m); drop_chunks(); drop_tables(); return DK_ERR_NOMEM; }
         DK_CUDA(ctx, cudaMemsetAsync(scal + 1, 0, sizeof(uint32_t) * (15 + 4 * (size_t)NPmax), st));
 
         MergeParams P;
@@ -578,7 +591,19 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
         auto launch_k = [&](int wk, int max_ctas) -> cudaError_t {
             cudaError_t e;
             auto clampg = [&](int g) { return (max_ctas > 0 && g > max_ctas) ? max_ctas : g; };
-            if (wk == 4) {
+            if (wk == 5) {
+                typedef void (*m5_fn)(MergeParams, M5Cfg, uint32_t *);
+                const m5_fn k5 = lv5 == 4 ? (m5_fn)k_merge5<4> : (m5_fn)k_merge5<5>;
+                e = cudaFuncSetAttribute(k5, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G5.smem_bytes);
+                if (e == cudaSuccess) {
+                    int per_sm = (int)((budget + 1024) / ((size_t)G5.smem_bytes + 1024));
+                    if (per_sm < 1) per_sm = 1;
+                    if (per_sm > M5_CTAS) per_sm = M5_CTAS;
+                    if (const char *pe = getenv("DK_M5_CTAS")) { int v = atoi(pe); if (v >= 1 && v < per_sm) per_sm = v; }   // tuning runs
+                    k5<<<clampg(ctx->sm_count * per_sm), M5_NT, G5.smem_bytes, ctx->stream>>>(P, G5, overflow_d);
+                    e = cudaGetLastError();
+                }
+            } else if (wk == 4) {
                 typedef void (*m4_fn)(MergeParams, M4Cfg, uint32_t *);
                 static const m4_fn m4_tab[7] = {k_merge4<0>, k_merge4<1>, k_merge4<2>, k_merge4<3>, k_merge4<4>, k_merge4<5>, k_merge4<6>};
                 const m4_fn k4 = m4_tab[G4.levels];
@@ -645,7 +670,7 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
             }
         }
         if (e == cudaSuccess) e = launch_k(which, 0);
-        if (e != cudaSuccess) { dk_matrix_release(ctx, m); return dk_fail(ctx, DK_ERR_CUDA, "merge launch: %s", cudaGetErrorString(e)); }
+        if (e != cudaSuccess) { dk_matrix_release(ctx, m); drop_chunks(); drop_tables(); return dk_fail(ctx, DK_ERR_CUDA, "merge launch: %s", cudaGetErrorString(e)); }
         DK_CUDA(ctx, cudaEventRecord(ctx->ev[3], st));
         k_join_totals<<<1, 256, 0, st>>>(part_rows, part_union, npart_d, chunkctr_d, overflow_d, totals); DK_LAUNCHED(ctx);
         DK_CUDA(ctx, cudaMemcpyAsync(h_tot, totals, sizeof h_tot, cudaMemcpyDeviceToHost, st));
@@ -663,6 +688,17 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
                     ms, pr[1] / tot, pr[2] / tot, pr[3] / tot, pr[4] / tot, pr[5] / tot, pr[6] / tot, pr[8] / tot, pr[9] / tot, pr[10] / tot, pr[7] / tot);
         }
 #endif
+#ifdef DK_M5_PROF
+        if (which == 5) {
+            uint32_t pr[12];
+            cudaMemcpy(pr, scal + 4, sizeof pr, cudaMemcpyDeviceToHost);
+            double tot = 0;
+            for (int i = 1; i < 9; i++) tot += pr[i];
+            fprintf(stderr, "[m5 prof] kernel %.3f ms; phase shares: tma wait %.3f pivot+prefix %.3f table %.3f classify+light %.3f "
+                    "simple rows %.3f complex rows %.3f scan+alloc %.3f copy-out %.3f\n",
+                    ms, pr[1] / tot, pr[2] / tot, pr[3] / tot, pr[4] / tot, pr[5] / tot, pr[6] / tot, pr[7] / tot, pr[8] / tot);
+        }
+#endif
 #ifdef DK_M4_PROF
         if (which == 4) {
             uint32_t pr[12];
@@ -676,23 +712,28 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
         }
 #endif
         if (h_tot[4] && which >= 3) {
-            // v4: a dump holds copies of a k-mer -> redo with v3 (copies become separate rows, as in the reference);
-            // v3: a dump holds one k-mer more than 4 times (its copy-index field overflowed) -> redo with the v1 kernel
-            which = (which == 4 && have3) ? 3 : 1;
+            // v5: one k-mer fills a whole window of a dump; v4: a dump holds copies of a k-mer -> redo with v3 (copies become
+            // separate rows, as in the reference); v3: a dump holds one k-mer more than 4 times (its copy-index field
+            // overflowed) -> redo with the v1 kernel. The chunk need seen so far still sizes the next try.
+            which = (which >= 4 && have3) ? 3 : 1;
             dk_dev_release(ctx, m->keys); dk_dev_release(ctx, m->cnts); dk_dev_release(ctx, m->chunk_rows);
-            dk_dev_release(ctx, chunk_part); dk_dev_release(ctx, chunk_seq);
+            drop_chunks();
             m->keys = nullptr; m->cnts = nullptr; m->chunk_rows = nullptr;
+            if (h_tot[2] > guess) guess = h_tot[2];
+            fallbacks++;
             continue;
         }
         if (h_tot[2] <= guess) break;
         // overflow: the counter kept counting, so h_tot[2] is the exact need
         dk_dev_release(ctx, m->keys); dk_dev_release(ctx, m->cnts); dk_dev_release(ctx, m->chunk_rows);
-        dk_dev_release(ctx, chunk_part); dk_dev_release(ctx, chunk_seq);
+        drop_chunks();
         m->keys = nullptr; m->cnts = nullptr; m->chunk_rows = nullptr;
         guess = h_tot[2];
-        if (attempt == 4) { dk_matrix_release(ctx, m); return dk_fail(ctx, DK_ERR_CUDA, "join: output overflow twice"); }
+        attempt++;
+        if (attempt == 3) { dk_matrix_release(ctx, m); drop_tables(); return dk_fail(ctx, DK_ERR_CUDA, "join: output overflow twice"); }
     }
-    g_chunk_hint = h_tot[2];
+    if (!m->keys) { dk_matrix_release(ctx, m); drop_tables(); return dk_fail(ctx, DK_ERR_CUDA, "join: no merge kernel accepted the input"); }
+    ctx->chunk_hint = h_tot[2];
     m->R = h_tot[0]; m->U = h_tot[1]; m->n_chunks = h_tot[2];
     uint32_t NP = (uint32_t)h_tot[3];
     uint32_t nch = (uint32_t)m->n_chunks;
@@ -701,7 +742,7 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     m->order = (uint32_t *)dk_dev_alloc(ctx, sizeof(uint32_t) * (nch + 2));
     m->lbase = (uint64_t *)dk_dev_alloc(ctx, sizeof(uint64_t) * (nch + 3));
     uint32_t *choff = (uint32_t *)dk_dev_alloc(ctx, sizeof(uint32_t) * ((size_t)NP + 2));
-    if (!m->order || !m->lbase || !choff) { dk_matrix_release(ctx, m); return DK_ERR_NOMEM; }
+    if (!m->order || !m->lbase || !choff) { dk_matrix_release(ctx, m); dk_dev_release(ctx, choff); drop_chunks(); drop_tables(); return DK_ERR_NOMEM; }
     (void)part_choff;
     DK_TRY(dk_scan_excl_u32(ctx, part_nchunks, choff, NP));
     if (nch) {
@@ -718,9 +759,8 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     float ms = 0;
     cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
     ctx->stage_ms[0] = ms;
-    dk_dev_release(ctx, tab); dk_dev_release(ctx, range); dk_dev_release(ctx, below); dk_dev_release(ctx, flag);
-    dk_dev_release(ctx, rank); dk_dev_release(ctx, starts); dk_dev_release(ctx, scal); dk_dev_release(ctx, totals);
-    dk_dev_release(ctx, chunk_part); dk_dev_release(ctx, chunk_seq); dk_dev_release(ctx, choff);
+    drop_tables();
+    drop_chunks(); dk_dev_release(ctx, choff);
     *out = m;
     return DK_OK;
 }
