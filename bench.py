@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--nf", default="reference", choices=["reference", "full"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the full-size invariants and the seeded-sample oracle check")
     ap.add_argument("--no-mask", action="store_true", help="skip the reference-transcript mask measurement")
     ap.add_argument("--no-ingest", action="store_true", help="skip the k-mer counting measurement")
     ap.add_argument("--cpu-rows", type=int, default=6_000_000, help="union rows of the CPU-baseline sample")
@@ -99,7 +100,7 @@ def algorithmic_bytes(n_records, R, S):
 
 
 # ------------------------------------------------------------------ CPU reference arm ---
-def cpu_path(keys, cnts, cfg, idxA, idxB, threads):
+def cpu_path(keys, cnts, cfg, idxA, idxB, threads, nf_mode="reference"):
     """the reference algorithm (oracle port of joinCounts -> computeNF -> TtestFilter) on `threads` host threads.
     The merge and the per-row test are prefix-separable, so threads>1 splits the key range; NF and BH stay serial."""
     import numpy as np
@@ -120,7 +121,8 @@ def cpu_path(keys, cnts, cfg, idxA, idxB, threads):
         th = [threading.Thread(target=work, args=(p,)) for p in range(threads)]
         [t.start() for t in th]; [t.join() for t in th]
     mk = np.concatenate([p[0] for p in parts]); mc = np.concatenate([p[1] for p in parts]); U = sum(p[2] for p in parts)
-    nf, _, _ = orc.nf_reference(mc)
+    nf = orc.nf_reference(mc)[0] if nf_mode == "reference" else orc.nf_full(mc)
+    cpu_path.nf_raw = nf
     nf = np.array([float("%f" % v) for v in nf])                 # the pipeline's "%f" round trip
     R = len(mk)
     if threads == 1 or R < threads * 4:
@@ -135,17 +137,26 @@ def cpu_path(keys, cnts, cfg, idxA, idxB, threads):
         [t.start() for t in th]; [t.join() for t in th]
         p, fc = np.concatenate([r[0] for r in res]), np.concatenate([r[3] for r in res])
     adj = orc.bh(p)
-    D = int(((adj <= PMAX) & (np.abs(fc) >= FMIN)).sum())
+    keep = (adj <= PMAX) & (np.abs(fc) >= FMIN)
+    D = int(keep.sum())
     dt = time.perf_counter() - t0
     cpu_path.checksum = (int(np.bitwise_xor.reduce(mk)) if R else 0, int(mc.astype(np.uint32).astype(np.uint64).sum()) if R else 0)
+    cpu_path.nf = nf
+    cpu_path.surv_xor = int(np.bitwise_xor.reduce(mk[keep])) if D else 0
+    cpu_path.surv_adj_sum = float(adj[keep].sum()) if D else 0.0
     return U, R, D, dt
 
 
-def make_cpu_sample(cfg, rows):
+# the parity sample plants a strong group effect (64x on 3% of the rows) so that survivors exist: D = 0 == 0 proves nothing
+PARITY_EFF = dict(eff=64.0, eff_frac=0.03)
+
+
+def make_cpu_sample(cfg, rows, row0=0, **eff):
     import torch
     from dekupl_run_b200 import synth
     dev = "cuda" if torch.cuda.is_available() else "cpu"
-    k, c = synth.gen_shard(cfg["S"], cfg["U"], 0, rows, device=dev, model=cfg["model"], q=cfg["q"], alpha=cfg["alpha"], chunk=1 << 22)
+    k, c = synth.gen_shard(cfg["S"], cfg["U"], row0, row0 + rows, device=dev, model=cfg["model"], q=cfg["q"], alpha=cfg["alpha"],
+                           chunk=1 << 22, **eff)
     import numpy as np
     return [x.cpu().numpy().view(np.uint64) for x in k], [x.cpu().numpy() for x in c]
 
@@ -301,33 +312,124 @@ def run_ours(args):
     # ---- §8(f)#4, k-mer counting of one sample from its reads (jellyfish count | dump | sort): measured beside the headline
     if world == 1 and not args.no_ingest:
         out["ingest"] = run_ingest(args, ctx)
-    # ---- e2e: host buffers through the C ABI, H2D of all dumps + D2H of the survivors inside the timed region
+    # ---- parity of what was timed. (1) full size, every rank: U, R, xor of the surviving k-mers and sum of the
+    # surviving counts of one more (untimed) run against the generator's own presence/count model; (2) a small seeded sample
+    # with a planted group effect (so that survivors exist) through the same code path as the timed run — run_path at N=1,
+    # run_sharded over all ranks at N>1 — against the CPU oracle on rank 0: U, R, D, NFs, matrix checksums, survivor set.
+    if not args.no_parity:
+        out["parity_check"] = parity_checks(args, cfg, ctx, dev, rank, world, dist, keys, cnts, kp, cp, n, rows_total, rows_rank,
+                                            idxA, idxB, nf_mode)
+    if rank == 0 and not args.no_cpu:
+        ck, cc = make_cpu_sample(cfg, args.cpu_rows)
+        cU, cR, cD, dt = cpu_path(ck, cc, cfg, idxA, idxB, 1)
+        out["cpu_baseline"] = {"value": cU / dt, "unit": "k-mers/s", "cores": 1, "kind": "port", "seconds": dt,
+                               "sample": f"first {args.cpu_rows} of {cfg['U']} rows of the same generator ({cU} union k-mers), "
+                                         "oracle C port of the three single-threaded reference tools"}
+    # ---- e2e last: it releases the device-resident dumps to make room for nothing, but pins host copies of them
     if not args.no_e2e and world == 1:
         out["e2e"] = run_e2e(args, cfg, ctx, keys, cnts, n, idxA, idxB, nf_mode)
     elif world > 1:
         out["e2e"] = {"value": None, "unit": "k-mers/s", "note": "measured at N=1 only (host staging is per-GPU identical)"}
-    if rank == 0 and not args.no_cpu:
-        ck, cc = make_cpu_sample(cfg, args.cpu_rows)
-        cU, cR, cD, dt = cpu_path(ck, cc, cfg, idxA, idxB, 1)
-        # the same sample through the CUDA path: U, R, D and the order-independent matrix checksums must agree
-        st_s, m_s, t_s = ctx.run_path([k.ctypes.data for k in ck], [c.ctypes.data for c in cc], [len(k) for k in ck], False,
-                                      cfg["r"], cfg["a"], nf_mode, idxA, idxB, PMAX, FMIN, nf_text_roundtrip=True, keep=True)
-        gsum = m_s.checksum()
-        out["parity_check"] = {"sample_rows": args.cpu_rows, "cpu": {"U": cU, "R": cR, "D": cD, "key_xor": cpu_path.checksum[0],
-                                                                   "count_sum": cpu_path.checksum[1]},
-                               "gpu": {"U": st_s["U"], "R": st_s["R"], "D": st_s["D"], "key_xor": int(gsum[0]), "count_sum": int(gsum[1])},
-                               "equal": bool(cU == st_s["U"] and cR == st_s["R"] and cD == st_s["D"]
-                                             and cpu_path.checksum == (int(gsum[0]), int(gsum[1])))}
-        if t_s is not None:
-            t_s.free()
-        m_s.free()
-        out["cpu_baseline"] = {"value": cU / dt, "unit": "k-mers/s", "cores": 1, "kind": "port", "seconds": dt,
-                               "sample": f"first {args.cpu_rows} of {cfg['U']} rows of the same generator ({cU} union k-mers), "
-                                         "oracle C port of the three single-threaded reference tools"}
     if rank == 0:
         print(json.dumps(out))
     if dist:
         dist.destroy_process_group()
+
+
+def _xor_fold(vals):
+    x = 0
+    for v in vals:
+        x ^= int(v)
+    return x
+
+
+def parity_checks(args, cfg, ctx, dev, rank, world, dist, keys, cnts, kp, cp, n, rows_total, rows_rank, idxA, idxB, nf_mode):
+    import numpy as np
+    import torch
+    import dekupl_run_b200 as dk
+    from dekupl_run_b200 import synth
+    S = cfg["S"]
+    M64 = (1 << 64) - 1
+    res = {}
+    # (1) full size: one more run of exactly the timed call, matrix kept
+    if world == 1:
+        st, m, t = ctx.run_path(kp, cp, n, True, cfg["r"], cfg["a"], nf_mode, idxA, idxB, PMAX, FMIN, nf_text_roundtrip=True, keep=True)
+        gx, gs = m.checksum()
+        gU, gR = st["U"], st["R"]
+        if t is not None:
+            t.free()
+        m.free()
+    else:
+        from dekupl_run_b200.distributed import GpuBackend, run_sharded
+        be = GpuBackend(ctx, dev)
+        st = run_sharded(be, kp, cp, n, cfg["r"], cfg["a"], idxA, idxB, PMAX, FMIN, nf_mode=args.nf, device=dev)
+        gx, gs = be.m.checksum()
+        gU, gR = st["U_local"], st["R_local"]
+        be.free()
+    exp = synth.expected_invariants(S, rows_total, rank * rows_rank, (rank + 1) * rows_rank, cfg["r"], cfg["a"], device=dev,
+                                    model=cfg["model"], q=cfg["q"], alpha=cfg["alpha"])
+    ok = (gU == exp["U"] and gR == exp["R"] and (gx & M64) == exp["key_xor"] and (gs & M64) == exp["count_sum"]
+          and exp["records"] == sum(n))
+    tot = [gU, gR, exp["U"], exp["R"], 1 if ok else 0]
+    if dist:
+        tt = torch.tensor(tot, dtype=torch.int64, device=dev)
+        dist.all_reduce(tt)
+        tot = [int(x) for x in tt.tolist()]
+    res["full_size"] = {"gpu": {"U": tot[0], "R": tot[1]}, "generator_model": {"U": tot[2], "R": tot[3]},
+                        "rank0_key_xor": [int(gx & M64), exp["key_xor"]], "rank0_count_sum": [int(gs & M64), exp["count_sum"]],
+                        "ranks_equal": tot[4], "equal": bool(tot[4] == world),
+                        "what": "U, R, xor of surviving k-mers, sum of surviving counts per rank vs the generator's presence/count model"}
+    # (2) seeded sample with a planted effect, same code path as the timed run, against the oracle
+    rows = args.cpu_rows
+    r0, r1 = rank * rows // world, (rank + 1) * rows // world
+    sk, sc = synth.gen_shard(S, cfg["U"], r0, r1, device=dev, model=cfg["model"], q=cfg["q"], alpha=cfg["alpha"], chunk=1 << 22,
+                             **PARITY_EFF)
+    sn = [int(k.numel()) for k in sk]
+    skp, scp = [k.data_ptr() for k in sk], [c.data_ptr() for c in sc]
+    if world == 1:
+        st, m, t = ctx.run_path(skp, scp, sn, True, cfg["r"], cfg["a"], nf_mode, idxA, idxB, PMAX, FMIN, nf_text_roundtrip=True, keep=True)
+        gx, gs = m.checksum()
+        surv = t.export_survivors() if t is not None else {"key": np.zeros(0, np.uint64), "p_adj": np.zeros(0)}
+        g = dict(U=st["U"], R=st["R"], D=st["D"], key_xor=int(gx), count_sum=int(gs), nf=[float(x) for x in st["nf"]],
+                 surv_xor=_xor_fold(surv["key"]), surv_adj_sum=float(np.sum(surv["p_adj"])))
+        if t is not None:
+            t.free()
+        m.free()
+        sample_nf_mode = args.nf
+    else:
+        # reference-mode NF needs its million-row steps inside rank 0's shard: the small sample uses the shard-symmetric full mode
+        sample_nf_mode = "full"
+        be = GpuBackend(ctx, dev)
+        st = run_sharded(be, skp, scp, sn, cfg["r"], cfg["a"], idxA, idxB, PMAX, FMIN, nf_mode=sample_nf_mode, device=dev)
+        gx, gs = be.m.checksum()
+        surv = be.t.export_survivors()
+        loc = torch.tensor([gx & 0x7FFFFFFFFFFFFFFF, gx >> 63, gs & 0x7FFFFFFFFFFFFFFF, gs >> 63,
+                            _xor_fold(surv["key"]) & 0x7FFFFFFFFFFFFFFF, _xor_fold(surv["key"]) >> 63], dtype=torch.int64, device=dev)
+        allv = [torch.zeros_like(loc) for _ in range(world)]
+        dist.all_gather(allv, loc)
+        adj = torch.tensor([float(np.sum(surv["p_adj"]))], dtype=torch.float64, device=dev)
+        dist.all_reduce(adj)
+        allv = [[int(x) for x in v.tolist()] for v in allv]
+        g = dict(U=st["U"], R=st["R"], D=st["D"], key_xor=_xor_fold(v[0] | (v[1] << 63) for v in allv),
+                 count_sum=sum(v[2] | (v[3] << 63) for v in allv) & M64, nf=[float(x) for x in st["nf"]],
+                 surv_xor=_xor_fold(v[4] | (v[5] << 63) for v in allv), surv_adj_sum=float(adj.item()))
+        be.free()
+    del sk, sc
+    if rank == 0:
+        ck, cc = make_cpu_sample(cfg, rows, **PARITY_EFF)
+        cU, cR, cD, _ = cpu_path(ck, cc, cfg, idxA, idxB, 1, nf_mode=sample_nf_mode)
+        c = dict(U=cU, R=cR, D=cD, key_xor=cpu_path.checksum[0], count_sum=cpu_path.checksum[1], surv_xor=cpu_path.surv_xor,
+                 surv_adj_sum=cpu_path.surv_adj_sum)
+        nf_err = float(np.max(np.abs(np.array(g["nf"]) - cpu_path.nf_raw) / cpu_path.nf_raw)) if cR else 0.0
+        adj_err = abs(g["surv_adj_sum"] - c["surv_adj_sum"]) / max(c["surv_adj_sum"], 1e-300) if cD else 0.0
+        ints_equal = all(g[k] == c[k] for k in ("U", "R", "D", "key_xor", "count_sum", "surv_xor"))
+        gg = {k: v for k, v in g.items() if k != "nf"}
+        res.update({"sample_rows": rows, "planted_effect": PARITY_EFF, "nf_mode": sample_nf_mode, "cpu": c, "gpu": gg,
+                    "nf_max_rel_err": nf_err, "surv_adj_sum_rel_err": adj_err,
+                    "sample_equal": bool(ints_equal and nf_err <= 1e-9 and adj_err <= 1e-9)})
+        res["equal"] = bool(res["sample_equal"] and res["full_size"]["equal"])
+    return res
+
 
 
 def run_ingest(args, ctx):

@@ -77,6 +77,9 @@ __global__ void k_u64_to_u32(const uint64_t *in, uint32_t *out, uint64_t n)
 extern "C" int dk_ttest_filter(dk_ctx *ctx, dk_ttest *t, double pmax, double fmin_, uint64_t *n_keep, uint64_t *ties)
 {
     if (!ctx || !t || !t->p_adj) return dk_fail(ctx, DK_ERR_ARG, "ttest_filter: call dk_ttest_adjust first");
+    // adjusted values exist at the candidate rows (p_raw <= p_cut) only and are exact only up to p_cut
+    if (t->p_cut < 1.0 && pmax > t->p_cut)
+        return dk_fail(ctx, DK_ERR_ARG, "ttest_filter: pmax %g exceeds the cut %g the adjusted p-values were computed for", pmax, t->p_cut);
     cudaStream_t st = ctx->stream;
     unsigned long long *ctr = (unsigned long long *)dk_dev_alloc(ctx, 64);
     if (!ctr) return DK_ERR_NOMEM;

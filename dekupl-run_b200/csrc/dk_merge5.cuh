@@ -321,13 +321,14 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                                     if (tw[w]) { const uint32_t by = (uint32_t)(__ffs(tw[w]) - 1) >> 3; s = 4u * w + by; i = (xw[w] >> (8u * by)) & 0xffu; }
                                 const unsigned char *f = fb + s * FBS + i;
                                 uint32_t rows = 1;
-                                while (!f[rows]) rows++;
+                                while (!f[rows]) { if (++rows > (uint32_t)FBS) __trap(); }   // (a run ends at the look-ahead slot at the latest)
                                 urows += rows;
                             } else {
                                 uint32_t pm = 0;
 #pragma unroll
                                 for (int w = 0; w < TW; w++) pm |= (((tw[w] >> 7) * 0x10204080u) >> 28) << (4 * w);
-                                while (pm) {
+                                for (uint32_t guard = 0; pm; guard++) {
+                                    if (guard > (uint32_t)(SP * FBS)) __trap();
                                     unsigned long long kmin = DK_SENTINEL;
                                     for (uint32_t m = pm; m; m &= m - 1) {
                                         const uint32_t s = __ffs(m) - 1;
@@ -420,7 +421,8 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                         uint32_t rows = 0, npass = 0;
                         bool present = i != M5_EMPTY;
                         uint32_t pw = __ballot_sync(0xffffffffu, present);
-                        while (pw) {
+                        for (uint32_t guard = 0; pw; guard++) {
+                            if (guard > (uint32_t)(SP * FBS)) __trap();                              // (a bucket holds < SP * FBS records)
                             unsigned long long key = DK_SENTINEL;
                             if (present) key = kg[i];
                             const uint32_t hi = (uint32_t)(key >> 32), lo32 = (uint32_t)key;

@@ -30,6 +30,10 @@ class GpuBackend:
     def __init__(self, ctx, device):
         self.ctx, self.device = ctx, device
         self.m = self.t = self.nfs = None
+        # The library's kernels and torch's ops / NCCL collectives hand device buffers to each other (histograms,
+        # candidate lists, adjusted values): both must run on ONE stream, or nothing orders them (a context's own
+        # stream is non-blocking). See dk_set_stream in include/dekupl_b200.h.
+        ctx.set_stream(torch.cuda.current_stream(device).cuda_stream)
 
     def join(self, key_ptrs, cnt_ptrs, n, r, a):
         self.m = self.ctx.join_counts_dev(key_ptrs, cnt_ptrs, n, r, a)

@@ -40,38 +40,49 @@ def sample_depths(S, seed=SEED):
     return (0.5 + 1.5 * torch.rand(S, generator=g, dtype=torch.float64)).tolist()
 
 
-def gen_shard(S, U_total, row0, row1, *, device, model="two_class", q=0.075, alpha=2.0, group_b=None, chunk=1 << 24,
-              seed=SEED, pinned_out=False):
-    """returns (keys[s] int64 tensors holding uint64 bit patterns, cnts[s] int32 tensors) for rows [row0,row1)"""
+def _rows(S, U_total, a, b, *, device, model, q, alpha, group_b, seed, eff=4.0, eff_frac=0.01):
+    """rows [a,b) of the implicit union: (key, [(present, count) per sample]) — the one place the generator is defined"""
     stride = (1 << 62) // U_total
     depths = sample_depths(S, seed)
+    i = torch.arange(a, b, device=device, dtype=torch.int64)
+    h = mix64(i + seed)
+    key = i * stride + (_lsr(h, 2) % stride)
+    cls = _lsr(mix64(h ^ 0x5851F42D), 40).to(torch.float64) / float(1 << 24)     # row class uniform [0,1)
+    effr = _lsr(mix64(h ^ 0x2545F491), 40).to(torch.float64) / float(1 << 24) < eff_frac
+    if model == "genome":
+        single = cls < 0.9
+        owner = _lsr(mix64(h ^ 0x1234567), 8) % S
+
+    def sample(s):
+        hs = mix64(h + _wrap((s + 1) * 0x632BE59BD9B4E019))
+        u = _lsr(hs, 40).to(torch.float64) / float(1 << 24)                       # presence
+        if model == "two_class":
+            present = u < torch.where(cls < 0.2, 0.95, q)
+        else:
+            present = torch.where(single, owner == s, u < 0.75)
+        v = ((_lsr(hs, 8) & 0xFFFFFFFF).to(torch.float64) + 1.0) / 4294967296.0   # (0,1]
+        z = torch.floor(v ** (-1.0 / (alpha - 1.0)))
+        e = torch.where(effr, float(eff), 1.0) if s in group_b else 1.0
+        c = torch.clamp(1.0 + torch.floor(z * depths[s] * e), 2.0, 2147483647.0).to(torch.int32)
+        return present, c
+    return key, sample
+
+
+def gen_shard(S, U_total, row0, row1, *, device, model="two_class", q=0.075, alpha=2.0, group_b=None, chunk=1 << 24,
+              seed=SEED, pinned_out=False, eff=4.0, eff_frac=0.01):
+    """returns (keys[s] int64 tensors holding uint64 bit patterns, cnts[s] int32 tensors) for rows [row0,row1)"""
     group_b = set(range(S // 2, S)) if group_b is None else set(group_b)
     keys_parts = [[] for _ in range(S)]
     cnts_parts = [[] for _ in range(S)]
     for a in range(row0, row1, chunk):
         b = min(row1, a + chunk)
-        i = torch.arange(a, b, device=device, dtype=torch.int64)
-        h = mix64(i + seed)
-        key = i * stride + (_lsr(h, 2) % stride)
-        cls = _lsr(mix64(h ^ 0x5851F42D), 40).to(torch.float64) / float(1 << 24)     # row class uniform [0,1)
-        eff = _lsr(mix64(h ^ 0x2545F491), 40).to(torch.float64) / float(1 << 24) < 0.01
-        if model == "genome":
-            single = cls < 0.9
-            owner = _lsr(mix64(h ^ 0x1234567), 8) % S
+        key, sample = _rows(S, U_total, a, b, device=device, model=model, q=q, alpha=alpha, group_b=group_b, seed=seed,
+                            eff=eff, eff_frac=eff_frac)
         for s in range(S):
-            hs = mix64(h + _wrap((s + 1) * 0x632BE59BD9B4E019))
-            u = _lsr(hs, 40).to(torch.float64) / float(1 << 24)                       # presence
-            if model == "two_class":
-                present = u < torch.where(cls < 0.2, 0.95, q)
-            else:
-                present = torch.where(single, owner == s, u < 0.75)
-            v = ((_lsr(hs, 8) & 0xFFFFFFFF).to(torch.float64) + 1.0) / 4294967296.0   # (0,1]
-            z = torch.floor(v ** (-1.0 / (alpha - 1.0)))
-            e = torch.where(eff, 4.0, 1.0) if s in group_b else 1.0
-            c = torch.clamp(1.0 + torch.floor(z * depths[s] * e), 2.0, 2147483647.0).to(torch.int32)
+            present, c = sample(s)
             keys_parts[s].append(key[present])
             cnts_parts[s].append(c[present])
-        del i, h, key, cls, eff
+        del key, sample
     keys, cnts = [], []
     for s in range(S):
         k = torch.cat(keys_parts[s]) if keys_parts[s] else torch.empty(0, dtype=torch.int64, device=device)
@@ -80,3 +91,44 @@ def gen_shard(S, U_total, row0, row1, *, device, model="two_class", q=0.075, alp
         keys.append(k)
         cnts.append(c)
     return keys, cnts
+
+
+def expected_invariants(S, U_total, row0, row1, r, a, *, device, model="two_class", q=0.075, alpha=2.0, group_b=None,
+                        chunk=1 << 24, seed=SEED, eff=4.0, eff_frac=0.01):
+    """What joinCounts must produce from gen_shard's dumps of rows [row0,row1), computed from the generator's own
+    presence/count model without merging anything (joinCounts.c:81-83,104): U = rows present in any sample,
+    R = rows with #{present and count >= a} >= r, xor of the surviving keys, sum of all surviving counts (mod 2^64)."""
+    group_b = set(range(S // 2, S)) if group_b is None else set(group_b)
+    U = R = 0
+    kx = torch.zeros((), dtype=torch.int64, device=device)
+    csum = 0
+    n_rec = 0
+    for a0 in range(row0, row1, chunk):
+        b0 = min(row1, a0 + chunk)
+        key, sample = _rows(S, U_total, a0, b0, device=device, model=model, q=q, alpha=alpha, group_b=group_b, seed=seed,
+                            eff=eff, eff_frac=eff_frac)
+        anyp = torch.zeros(b0 - a0, dtype=torch.bool, device=device)
+        rec = torch.zeros(b0 - a0, dtype=torch.int32, device=device)
+        tot = torch.zeros(b0 - a0, dtype=torch.int64, device=device)
+        for s in range(S):
+            present, c = sample(s)
+            anyp |= present
+            rec += (present & (c >= a)).to(torch.int32)
+            tot += torch.where(present, c.to(torch.int64), 0)
+            n_rec += int(present.sum().item())
+        keep = rec >= r
+        if r <= 0:
+            keep = keep & anyp
+        U += int(anyp.sum().item())
+        R += int(keep.sum().item())
+        kk = key[keep]
+        if kk.numel():
+            # xor-reduce: torch has no bitwise_xor reduction; fold halves
+            v = kk
+            while v.numel() > 1:
+                if v.numel() % 2:
+                    v = torch.cat([v, torch.zeros(1, dtype=v.dtype, device=device)])
+                v = v[: v.numel() // 2] ^ v[v.numel() // 2:]
+            kx ^= v[0]
+        csum = (csum + int(tot[keep].sum().item())) & ((1 << 64) - 1)
+    return dict(U=U, R=R, key_xor=int(kx.item()) & ((1 << 64) - 1), count_sum=csum, records=n_rec)

@@ -48,7 +48,10 @@ int  dk_init(dk_ctx **out, int device);           /* device = CUDA ordinal */
 void dk_free(dk_ctx *ctx);
 const char *dk_last_error(const dk_ctx *ctx);     /* never freed by the caller; ctx may be NULL */
 const char *dk_version(void);
-/* work is enqueued on this CUDA stream (a cudaStream_t passed as void*); default: a stream the ctx owns */
+/* work is enqueued on this CUDA stream (a cudaStream_t passed as void*); default: a NON-BLOCKING stream the ctx owns.
+ * A caller that passes _dev buffers written or read by its own kernels / collectives (the multi-GPU building blocks
+ * below) MUST either put the context on the stream those run on with dk_set_stream, or order the two streams itself
+ * (event record + cudaStreamWaitEvent around every such call): nothing else orders a non-blocking stream against them. */
 int  dk_set_stream(dk_ctx *ctx, void *cuda_stream);
 int  dk_sync(dk_ctx *ctx);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
@@ -170,6 +173,8 @@ int dk_bh_rank_slice(dk_ctx *ctx, const double *p_dev, uint64_t n, uint64_t n_be
                      double *sorted_p_dev /* out [n] ascending */, double *F_dev /* out [n] running minimum inside the slice */);
 int dk_ttest_apply_adjusted(dk_ctx *ctx, dk_ttest *t, const double *sorted_p_dev, const double *F_dev, uint64_t n_all);
 /* TtestFilter.c:486: survivors = adj_p <= pmax && fabs(log2FC) >= fmin; returns D in *n_keep.
+ * pmax must not exceed the p_cut the adjusted values were computed for (dk_ttest_adjust / _candidates): they are exact
+ * only up to it and absent beyond it, so a larger pmax is refused with DK_ERR_ARG.
  * ties (may be NULL): ties[0] = rows with adj_p within 1e-9 rel of pmax, ties[1] = rows with
  * fabs(log2FC) within 1e-9 rel of fmin, ties[2] = rows whose sd was within 1e-13 of the sd==0 test */
 int dk_ttest_filter(dk_ctx *ctx, dk_ttest *t, double pmax, double fmin, uint64_t *n_keep, uint64_t *ties);

@@ -46,3 +46,16 @@ def random_dumps(rng, S, n_union, kbits, p_present, max_count, p_core=0.0):
         out_k.append(keys[m])
         out_c.append(rng.integers(1, max_count, size=int(m.sum())).astype(np.int32))
     return out_k, out_c
+
+
+def plant_effect(rng, keys, cnts, group_b, frac=0.05, factor=40):
+    """multiply the counts of the group-B samples on a random `frac` of the union k-mers: rows the t-test must find"""
+    allk = np.unique(np.concatenate([k for k in keys if len(k)]))
+    hit = allk[rng.random(len(allk)) < frac]
+    out = []
+    for s, (k, c) in enumerate(zip(keys, cnts)):
+        c = c.copy()
+        if s in group_b:
+            c[np.isin(k, hit)] *= factor
+        out.append(c)
+    return out

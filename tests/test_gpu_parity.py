@@ -489,3 +489,101 @@ def test_format_rows_on_chunked_join_output(ctx):
         ctx._chk(ctx.L.dk_matrix_format_rows(ctx.h, m.h, 0, m.rows, 31, buf.ctypes.data, 8, C.byref(ln)))
     assert ln.value == len(format_join(gk, gc, 31))                     # too-small buffer: size needed is reported
     m.free()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("G,flow", [(3, "routed"), (2, "gathered")])
+def test_sharded_c_abi_path_on_one_device(ctx, G, flow):
+    """The multi-GPU path, shard by shard on ONE device: a seeded input with a planted effect is cut into G key ranges,
+    every shard goes through the C-ABI building blocks the ranks call (dk_join_counts_dev, dk_nf_begin/_set_rank/
+    _hist_dev/_advance_dev/_result, dk_ttest_rows, dk_ttest_candidates, then either the routed BH — dk_bh_rank_slice per
+    p-value range + dk_ttest_apply_adjusted — or dk_ttest_adjust_global on the gathered list, dk_ttest_filter), the
+    'collectives' are done by hand on the host, and U, R, NFs, adjusted p and the survivor set must equal the oracle on
+    the UNSHARDED input (TtestFilter.c:459-497, computeNF.c:38-47)."""
+    import torch
+    from common import plant_effect
+    from dekupl_run_b200.distributed import GpuBackend
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(100 + G)
+    S, nA, r, a, pmax = 8, 4, 2, 5, 0.05
+    idxA, idxB = list(range(nA)), list(range(nA, S))
+    keys, cnts = random_dumps(rng, S, 150_000, 62, 0.15, 60, p_core=0.3)
+    cnts = plant_effect(rng, keys, cnts, set(idxB))
+    ok, oc, oU = orc.join(keys, cnts, r, a)
+    onf = orc.nf_full(oc)
+    op, omA, omB, ofc = orc.ttest_rows(oc, onf, idxA, idxB)
+    oadj = orc.bh(op)
+    okeep = np.nonzero(oadj <= pmax)[0]
+    assert len(okeep) > 50
+    # key-range shards
+    edges = [0] + [int(ok[len(ok) * g // G]) for g in range(1, G)] + [1 << 63]
+    bes, bufs, rows0 = [], [], []
+    R_glob = U_glob = 0
+    for g in range(G):
+        tk, tc = [], []
+        for k, c in zip(keys, cnts):
+            lo, hi = np.searchsorted(k, np.uint64(edges[g])), np.searchsorted(k, np.uint64(edges[g + 1]))
+            tk.append(torch.from_numpy(k[lo:hi].view(np.int64).copy()).to(dev))
+            tc.append(torch.from_numpy(c[lo:hi].copy()).to(dev))
+        bufs.append((tk, tc))
+        be = GpuBackend(ctx, dev)
+        Rl, Ul = be.join([t.data_ptr() for t in tk], [t.data_ptr() for t in tc], [t.numel() for t in tk], r, a)
+        rows0.append(R_glob)
+        R_glob += Rl; U_glob += Ul
+        bes.append(be)
+    assert (U_glob, R_glob) == (oU, len(ok))
+    # NF, full mode: histograms summed over the shards by hand (the all-reduce)
+    n_pos = sum(be.nf_begin() for be in bes)
+    for be in bes:
+        be.nf_set_rank(n_pos // 2)
+    for _ in range(8):
+        hs = [be.nf_hist().clone() for be in bes]
+        tot = torch.stack(hs).sum(0)
+        for be in bes:
+            be.nf_advance(tot.clone())
+    nfs = [be.nf_result() for be in bes]
+    for v in nfs:
+        np.testing.assert_allclose(v, onf, rtol=RTOL)
+    for be in bes:
+        be.ttest_rows(onf, idxA, idxB)
+    cands = [be.candidates(pmax).clone() for be in bes]
+    if flow == "gathered":
+        allp = torch.cat(cands)
+        for be in bes:
+            be.adjust_global(allp, R_glob)
+    else:
+        pe = [pmax * g / G for g in range(1, G)]
+        sends = [torch.sort(c)[0] for c in cands]
+        cuts = [[0] + [int(torch.searchsorted(s, torch.tensor([e], dtype=torch.float64, device=dev), right=True).item()) for e in pe]
+                + [s.numel()] for s in sends]
+        mines = [torch.cat([sends[src][cuts[src][g]:cuts[src][g + 1]] for src in range(G)]) for g in range(G)]
+        n_below = [sum(cuts[src][g] for src in range(G)) for g in range(G)]
+        ranked = [bes[g].bh_rank_slice(mines[g].contiguous(), n_below[g], R_glob) for g in range(G)]
+        ctx.sync()
+        firsts = [float(F[0].item()) if F.numel() else float("inf") for _, F in ranked]
+        for g in range(G):
+            above = min(firsts[g + 1:], default=None)
+            sp, F = ranked[g]
+            ranked[g] = (sp, torch.clamp(F, max=above) if (above is not None and F.numel()) else F)
+        for src in range(G):
+            parts = []
+            for g in range(G):
+                seg = sends[src][cuts[src][g]:cuts[src][g + 1]]
+                sp, F = ranked[g]
+                parts.append(F[torch.searchsorted(sp, seg)] if seg.numel() else seg)
+            bes[src].apply_adjusted(sends[src], torch.cat(parts).contiguous())
+    got_rows, got_adj = [], []
+    for g, be in enumerate(bes):
+        D, ties = be.filter(pmax, 0.0)
+        sv = be.t.export_survivors()
+        got_rows.append(sv["row"].astype(np.int64) + rows0[g])
+        got_adj.append(sv["p_adj"])
+        p, fc, adj = be.t.export_rows()
+        sl = slice(rows0[g], rows0[g] + len(p))
+        np.testing.assert_allclose(p, op[sl], rtol=RTOL, atol=1e-300)
+    got_rows, got_adj = np.concatenate(got_rows), np.concatenate(got_adj)
+    near = np.abs(oadj - pmax) <= 1e-9 * pmax
+    assert set(np.nonzero((oadj <= pmax) & ~near)[0].tolist()) <= set(got_rows.tolist()) <= set(np.nonzero((oadj <= pmax) | near)[0].tolist())
+    np.testing.assert_allclose(got_adj, oadj[got_rows], rtol=RTOL, atol=1e-300)
+    for be in bes:
+        be.free()
