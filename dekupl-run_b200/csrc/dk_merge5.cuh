@@ -51,14 +51,18 @@ struct M5Small {
     unsigned long long bar;
     unsigned long long pivot, base;
     uint32_t scan[M5_NT / 32];
-    uint32_t part, total_real, nstage, uround, ncomplex;
-    uint32_t chunk_cur, rowpos, seq, newbase, have_cur, prow, puni;
+    uint32_t part, nstage, uround, ncomplex;
+    uint32_t chunk_cur, rowpos, seq, prow, puni;
+    uint32_t cp_nout, cp_have, cp_nb, cp_rp, cp_ccur;      // the previous round's rows: copied out behind this round's first barrier
 };
 template <int SP>
 struct M5Samp {
     unsigned long long cur[SP], endg[SP];
+    const uint64_t *ksrc[SP];      // the dump tables, read from global memory once per CTA
+    const int32_t *csrc[SP];
+    unsigned long long nsrc[SP];
     uint32_t koff[SP];
-    uint32_t n[SP];
+    uint32_t n[SP], ncm[SP];
 };
 
 __device__ __forceinline__ uint32_t m5_block_excl_scan(uint32_t v, M5Small &sm, uint32_t &total)
@@ -86,6 +90,20 @@ __device__ __forceinline__ void m5_mbar_wait(uint32_t bar, uint32_t parity)
             : "=r"(done) : "r"(bar), "r"(parity) : "memory");
         if (it > (1u << 24)) __trap();
     }
+}
+__device__ __forceinline__ unsigned long long m5_warp_min64(unsigned long long v)
+{
+    const uint32_t hi = (uint32_t)(v >> 32), lo = (uint32_t)v;
+    const uint32_t mh = __reduce_min_sync(0xffffffffu, hi);
+    const uint32_t ml = __reduce_min_sync(0xffffffffu, hi == mh ? lo : 0xffffffffu);
+    return ((unsigned long long)mh << 32) | ml;
+}
+__device__ __forceinline__ unsigned long long m5_warp_max64(unsigned long long v)
+{
+    const uint32_t hi = (uint32_t)(v >> 32), lo = (uint32_t)v;
+    const uint32_t mh = __reduce_max_sync(0xffffffffu, hi);
+    const uint32_t ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
+    return ((unsigned long long)mh << 32) | ml;
 }
 // most significant bit of every byte of x that is not 0xFF
 __device__ __forceinline__ uint32_t m5_present_msb(uint32_t x)
@@ -163,6 +181,7 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         sm.nstage = 0; sm.uround = 0; sm.ncomplex = 0;
     }
+    if (owner) { ss.ksrc[tid] = P.T.keys[tid]; ss.csrc[tid] = P.T.cnts[tid]; ss.nsrc[tid] = P.T.n[tid]; }
     {   // table empty, no survivors, look-ahead slots start a run
         uint4 *t4 = reinterpret_cast<uint4 *>(Tb);
         for (int i = tid; i < M5_M * SP / 16; i += M5_NT) t4[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
@@ -175,9 +194,9 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
 
     // owner threads: stage the next window of their dump (keys and counts, one transaction count)
     auto issue = [&]() {
-        const unsigned long long cur = ss.cur[tid], endg = ss.endg[tid], nsrc = P.T.n[tid];
-        const uint64_t *ksrc = P.T.keys[tid];
-        const int32_t *csrc = P.T.cnts[tid];
+        const unsigned long long cur = ss.cur[tid], endg = ss.endg[tid], nsrc = ss.nsrc[tid];
+        const uint64_t *ksrc = ss.ksrc[tid];
+        const int32_t *csrc = ss.csrc[tid];
         const unsigned long long a0 = cur & ~3ull;
         o_lo = (uint32_t)(cur - a0);
         o_cap = (uint32_t)caps >> shrink;
@@ -218,6 +237,10 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
         if (tid == 0) { sm.chunk_cur = CHUNK_NONE; sm.rowpos = 0; sm.seq = 0; sm.prow = 0; sm.puni = 0; }
         if (owner) issue();
         bool stop = false;
+        // thread 0: the chunk allocation of a round's rows is ISSUED when the round ends and CONSUMED at the top of the next
+        // round (its latency hides behind the scan, the copies' wait and the pivot); the rows are copied out there too
+        bool pend = false;
+        uint32_t a_have = 0, a_nnew = 0, a_nb = 0, p_nout = 0;
 
         for (;;) {   // ---- rounds
 #ifdef DK_M5_PROF
@@ -226,69 +249,117 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
             m5_mbar_wait(bar, phase);
             phase ^= 1u;
             M5_MARK(1);
-            // R1 (warp 0 alone): pivot = smallest look-ahead key, base = smallest first key, consumable prefix per dump
-            uint32_t o_n = 0, o_ncm = 0;
-            auto publish = [&](unsigned long long pv, unsigned long long bs) {      // warp 0: prefix of every window below pv
-                uint32_t n = 0;
-                if (owner && o_ncm) {
-                    const unsigned long long *kwo = bufK + (size_t)tid * ks + o_lo;
-                    uint32_t a = 0, b = o_ncm;
-                    while (a < b) { const uint32_t mid = (a + b) >> 1; if (kwo[mid] < pv) a = mid + 1; else b = mid; }
-                    n = a;
-                }
-                o_n = n;
-                const uint32_t tot = __reduce_add_sync(0xffffffffu, n);
-                if (lane < SP) ss.n[lane] = n;
-                if (lane == 0) { sm.pivot = pv; sm.base = bs; sm.total_real = tot; }
-            };
+            // R1 (warp 0 alone): pivot = smallest look-ahead key, base = smallest first key
             if (warp == 0) {
                 unsigned long long candk = DK_SENTINEL, firstk = DK_SENTINEL, lastk = 0;
+                uint32_t ncm = 0;
                 if (owner && o_L) {
                     const unsigned long long *kw = bufK + (size_t)tid * ks + o_lo;
                     firstk = kw[0];
-                    if (o_L == o_cap + 1u) { candk = kw[o_cap]; o_ncm = o_cap; } else o_ncm = o_L;
-                    lastk = kw[o_ncm - 1];
+                    if (o_L == o_cap + 1u) { candk = kw[o_cap]; ncm = o_cap; } else ncm = o_L;
+                    lastk = kw[ncm - 1];
                 }
-                candk = m4_warp_min(candk);
-                firstk = m4_warp_min(firstk);
-                lastk = m4_warp_max(lastk);
-                if (firstk != DK_SENTINEL && lastk != DK_SENTINEL && lastk + 1ull < candk) candk = lastk + 1ull;   // span of the keys staged
-                publish(candk, firstk);
+                candk = m5_warp_min64(candk);
+                firstk = m5_warp_min64(firstk);
+                lastk = m5_warp_max64(lastk);
+                if (firstk != DK_SENTINEL && lastk + 1ull < candk) candk = lastk + 1ull;   // span of the keys staged
+                if (lane < SP) ss.ncm[lane] = ncm;
+                if (lane == 0) {
+                    sm.pivot = candk; sm.base = firstk;
+                    uint32_t cpn = 0;
+                    if (pend) {
+                        for (uint32_t k = 0; k < a_nnew; k++) {
+                            const uint32_t id = a_nb + k;
+                            if (id < P.max_chunks) { P.chunk_part[id] = part; P.chunk_seq[id] = sm.seq + k; P.chunk_rows[id] = DK_CH; }
+                        }
+                        sm.cp_have = a_have; sm.cp_nb = a_nb; sm.cp_rp = a_have ? sm.rowpos : 0u; sm.cp_ccur = sm.chunk_cur;
+                        cpn = p_nout;
+                        const uint32_t v = (a_have ? sm.rowpos : 0u) + p_nout;
+                        if (a_nnew) {
+                            sm.chunk_cur = a_nb + a_nnew - 1;
+                            sm.seq += a_nnew;
+                            sm.rowpos = v - (a_have + a_nnew - 1) * DK_CH;
+                        } else sm.rowpos = v;
+                        if (sm.chunk_cur != CHUNK_NONE && sm.rowpos == DK_CH) { sm.chunk_cur = CHUNK_NONE; sm.rowpos = 0; }
+                        pend = false;
+                    }
+                    sm.cp_nout = cpn;
+                }
             }
             __syncthreads();                                            // B1
+            M5_MARK(2);
+            // the previous round's rows go out now: staging, bpos and the copy descriptor are rewritten behind B3 / B4 only
+            {
+                const uint32_t nprev = sm.cp_nout;
+                if (nprev) {
+                    const uint32_t have = sm.cp_have, nb = sm.cp_nb, rp = sm.cp_rp, ccur = sm.cp_ccur;
+                    if (G.S4) {
+                        const uint32_t S4 = G.S4, n4 = nprev * S4;
+                        for (uint32_t i = tid; i < n4; i += M5_NT) {
+                            const uint32_t rr = S4 == 1 ? i : __umulhi(i, G.divS4), c4 = i - rr * S4;
+                            const uint32_t meta = smeta[rr];
+                            const uint32_t v = rp + (uint32_t)bpos[meta & 0xffffu] + (meta >> 16), k = v / DK_CH, off = v % DK_CH;
+                            const uint32_t chunk = (have && k == 0) ? ccur : nb + (k - have);
+                            const int32_t *src = stage + rr * RS + 4u * c4;
+                            if (chunk < P.max_chunks)
+                                reinterpret_cast<int4 *>(P.out_cnts + ((size_t)chunk * DK_CH + off) * S)[c4] = make_int4(src[0], src[1], src[2], src[3]);
+                        }
+                    } else {
+                        for (uint32_t rr = tid / 32u; rr < nprev; rr += M5_NT / 32u) {
+                            const uint32_t meta = smeta[rr];
+                            const uint32_t v = rp + (uint32_t)bpos[meta & 0xffffu] + (meta >> 16), k = v / DK_CH, off = v % DK_CH;
+                            const uint32_t chunk = (have && k == 0) ? ccur : nb + (k - have);
+                            if (chunk < P.max_chunks)
+                                for (uint32_t c = lane; c < (uint32_t)S; c += 32u) P.out_cnts[((size_t)chunk * DK_CH + off) * S + c] = stage[rr * RS + c];
+                        }
+                    }
+                    for (uint32_t rr = tid; rr < nprev; rr += M5_NT) {
+                        const uint32_t meta = smeta[rr];
+                        const uint32_t v = rp + (uint32_t)bpos[meta & 0xffffu] + (meta >> 16), k = v / DK_CH, off = v % DK_CH;
+                        const uint32_t chunk = (have && k == 0) ? ccur : nb + (k - have);
+                        if (chunk < P.max_chunks) P.out_keys[(size_t)chunk * DK_CH + off] = skey[rr];
+                    }
+                }
+            }
+            M5_MARK(3);
             unsigned long long pivot = sm.pivot;
             const unsigned long long base = sm.base;
             if (base == DK_SENTINEL) break;                             // every window empty: partition done
-            M5_MARK(2);
             uint32_t nout = 0;
             for (;;) {   // ---- one attempt at the round; redone with a smaller pivot when the staging area overflows
-                if (sm.total_real == 0) {                               // a window full of one k-mer: not this kernel's case
-                    if (tid == 0) atomicExch(overflow, 1u);
-                    stop = true;
-                    break;
-                }
-                // T: bucket of every record; the first record of a run stores its window index
-                const unsigned long long span = pivot - base;          // >= 1
+                // T: bucket of every record below the pivot; the first record of a run stores its buffer slot
+                const unsigned long long span = pivot - base;          // >= 1 whenever a record lies below the pivot
                 const int wsh = (64 - __clzll((long long)span)) > 16 ? (64 - __clzll((long long)span)) - 16 : 0;
                 const uint32_t fmax = (uint32_t)((span - 1ull) >> wsh);
                 const uint32_t scale = (fmax + 1u <= (uint32_t)M5_M) ? 65536u : (uint32_t)(((uint32_t)M5_M << 16) / (fmax + 1u));
+                uint32_t cntv = 0;
                 {
-                    const uint32_t sn = ss.n[ps];
+                    const uint32_t ncm = ss.ncm[ps];
                     const uint32_t lo_ps = ss.koff[ps] - (uint32_t)ps * ks;
                     const unsigned long long *kw = bufK + ss.koff[ps];
                     const uint32_t i0 = (uint32_t)psub * M5_VT;
-                    uint32_t bk[M5_VT];
+                    uint32_t bk[M5_VT], vm = 0;
 #pragma unroll
                     for (int j = 0; j < M5_VT; j++) {
-                        const uint32_t f = (uint32_t)((kw[i0 + j] - base) >> wsh);     // slots past the prefix: stale, never used
+                        const unsigned long long key = kw[i0 + j];                       // slots past the window: stale, never used
+                        vm |= ((i0 + j < ncm && key < pivot) ? 1u : 0u) << j;            // keys are sorted: the valid records are a prefix
+                        const uint32_t f = (uint32_t)((key - base) >> wsh);
                         bk[j] = (f * scale) >> 16;
+                    }
+                    cntv = __popc(vm);
+                    {   // consumable prefix of the dump: exactly one thread of the dump sees its end
+                        const bool v0 = vm & 1u, vl = (vm >> (M5_VT - 1)) & 1u;
+                        const bool pvl = __shfl_up_sync(0xffffffffu, vl ? 1u : 0u, 1) != 0u;
+                        if (v0 && !vl) ss.n[ps] = i0 + cntv;
+                        else if (vl && psub == TPS - 1) ss.n[ps] = i0 + M5_VT;
+                        else if (!v0 && (psub == 0 || pvl)) ss.n[ps] = i0;
                     }
                     const uint32_t prev = __shfl_up_sync(0xffffffffu, bk[M5_VT - 1], 1);
                     const uint32_t sl0 = lo_ps + i0;                    // buffer slot of my first record
                     unsigned char *fbp = fb + ps * FBS + sl0;
 #pragma unroll
                     for (int j = 0; j < M5_VT; j++) {
-                        const bool valid = i0 + j < sn;
+                        const bool valid = (vm >> j) & 1u;
                         const bool first = j ? (bk[j] != bk[j - 1]) : (psub == 0 || bk[0] != prev);
                         if (valid && first) Tb[bk[j] * SP + (uint32_t)ps] = (unsigned char)(sl0 + j);
                         if (valid && !first) mflag[bk[j]] = 1;          // this bucket holds a run: gathered by a lane group
@@ -296,8 +367,12 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                     }
                     if (psub == TPS - 1) fbp[M5_VT] = 1;                // the look-ahead slot always starts a run
                 }
-                __syncthreads();                                        // B3
-                M5_MARK(3);
+                if (!__syncthreads_or(cntv != 0u)) {                    // B3. No record below the pivot: a window full of ONE
+                    if (tid == 0) atomicExch(overflow, 1u);            // k-mer (its copies fill a dump's window): v3's case
+                    stop = true;
+                    break;
+                }
+                M5_MARK(4);
                 // ---- C1: buckets of this warp: rows counted (L) or listed (G)
                 uint32_t urows = 0;
                 {
@@ -314,7 +389,15 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                         for (int w = 0; w < TW; w++) { tw[w] = m5_present_msb(xw[w]); np += __popc(tw[w]); }
                         const bool heavy = np >= hth;
                         if (np && !heavy) {                             // L: rec <= np < r, no row can pass (joinCounts.c:104): count the rows
-                            if (np == 1) {
+                            const bool runs = mflag[bq] != 0;
+                            if (np == 1 && !runs) urows += 1;           // one record: one row
+                            else if (np == 2 && !runs) {                // two records of two dumps: one row if they hold one k-mer
+                                uint32_t pm = 0;
+#pragma unroll
+                                for (int w = 0; w < TW; w++) pm |= (((tw[w] >> 7) * 0x10204080u) >> 28) << (4 * w);
+                                const uint32_t s1 = __ffs(pm) - 1, s2 = 31 - __clz(pm);
+                                urows += bufK[s1 * ks + trow[s1]] == bufK[s2 * ks + trow[s2]] ? 1u : 2u;
+                            } else if (np == 1) {
                                 uint32_t s = 0, i = 0;
 #pragma unroll
                                 for (int w = 0; w < TW; w++)
@@ -345,14 +428,14 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                                 }
                             }
                             m5_clear_row<TW>(trow);
-                            mflag[bq] = 0;
+                            if (runs) mflag[bq] = 0;
                         }
                         const uint32_t hb = __ballot_sync(0xffffffffu, heavy);
                         if (heavy) lst[hcnt + __popc(hb & ((1u << lane) - 1u))] = (unsigned char)(q * 32 + lane);
                         hcnt += __popc(hb);
                     }
                     __syncwarp();
-                    M5_MARK(4);
+                    M5_MARK(5);
                     // ---- C2: one thread per listed bucket: the usual bucket holds ONE k-mer and no run. Every dump's record
                     // is compared with the first present one, the counts are gathered, the row is judged and staged — straight
                     // line code over the dumps. Anything else goes to the CTA's list for the lane groups.
@@ -405,7 +488,7 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                     }
                 }
                 __syncthreads();                                        // B3b: the CTA's list of complex buckets is complete
-                M5_MARK(5);
+                M5_MARK(6);
                 {
                     // ---- C3: lane groups, lane gl = dump gl, walk the rows of a complex bucket in k-mer order
                     const unsigned long long *kg = bufK + gl * ks;
@@ -427,8 +510,20 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                             if (present) key = kg[i];
                             const uint32_t hi = (uint32_t)(key >> 32), lo32 = (uint32_t)key;
                             const uint32_t gp = (pw >> gsh) & gbits;                                 // lanes of my group holding a record
-                            const uint32_t mh = __reduce_min_sync(gmask, hi);                        // smallest k-mer of the group (:97-100)
-                            const uint32_t ml = __reduce_min_sync(gmask, hi == mh ? lo32 : 0xffffffffu);
+                            // smallest k-mer of the group (:97-100). One full-mask redux per group: a redux over half a warp
+                            // compiles to a divergent slow path
+                            uint32_t mh, ml;
+                            if (GPW == 1) {
+                                mh = __reduce_min_sync(0xffffffffu, hi);
+                                ml = __reduce_min_sync(0xffffffffu, hi == mh ? lo32 : 0xffffffffu);
+                            } else {
+                                const uint32_t h0 = __reduce_min_sync(0xffffffffu, gidx == 0 ? hi : 0xffffffffu);
+                                const uint32_t h1 = __reduce_min_sync(0xffffffffu, gidx == 1 ? hi : 0xffffffffu);
+                                mh = gidx ? h1 : h0;
+                                const uint32_t l0 = __reduce_min_sync(0xffffffffu, (gidx == 0 && hi == mh) ? lo32 : 0xffffffffu);
+                                const uint32_t l1 = __reduce_min_sync(0xffffffffu, (gidx == 1 && hi == mh) ? lo32 : 0xffffffffu);
+                                ml = gidx ? l1 : l0;
+                            }
                             const bool member = present && hi == mh && lo32 == ml;                   // joinCounts.c:78
                             int32_t c = 0;
                             if (member) c = cg[i];
@@ -457,7 +552,7 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                     if (lane == 0 && ut) atomicAdd(&sm.uround, ut);
                 }
                 __syncthreads();                                        // B4
-                M5_MARK(6);
+                M5_MARK(7);
                 const uint32_t nst = sm.nstage;
                 if (nst > (uint32_t)M5_CAP) {                           // more survivors than staging slots: smaller round
                     for (int i = tid; i < M5_M; i += M5_NT) binfo[i] = 0;
@@ -471,26 +566,25 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                     if (ns >= span) ns = span - 1ull;
                     pivot = base + ns;
                     if (shrink < 4u) shrink++;
-                    __syncthreads();
+                    __syncthreads();                                    // every thread has read the counters
                     if (tid == 0) { sm.nstage = 0; sm.uround = 0; sm.ncomplex = 0; }
-                    if (warp == 0) publish(pivot, base);
-                    __syncthreads();
-                    continue;
+                    continue;                                           // (they are next touched behind the redone pass's barrier)
                 }
                 nout = nst;
                 break;
             }
             if (stop) break;
             if (shrink && nout < (uint32_t)M5_CAP / 4u) shrink--;
-            const uint32_t ccur = sm.chunk_cur, rpos = sm.rowpos;       // thread 0 moves them on right after its copy-out
             // the next round's windows start flying now; the chunk allocation of this round's rows too
-            if (owner) { ss.cur[tid] += o_n; issue(); }
-            uint32_t a_have = 0, a_nnew = 0, a_nb = 0;
+            if (owner) { ss.cur[tid] += ss.n[tid]; issue(); }
             if (tid == 0) {
                 a_have = (sm.chunk_cur != CHUNK_NONE) ? 1u : 0u;
                 const uint32_t slots = a_have ? (DK_CH - sm.rowpos) : 0u;
                 a_nnew = nout > slots ? (nout - slots + DK_CH - 1) / DK_CH : 0u;
-                if (a_nnew) a_nb = atomicAdd(P.chunk_counter, a_nnew);
+                a_nb = 0;
+                if (a_nnew) a_nb = atomicAdd(P.chunk_counter, a_nnew);  // consumed at the top of the next round
+                p_nout = nout;
+                pend = nout != 0u;
             }
             // O: output slot of every bucket's first surviving row
             {
@@ -500,7 +594,7 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
 #pragma unroll
                 for (int q = 0; q < M5_MB / 2; q++) { v[q] = bi[q]; mine += (v[q] & 0xffffu) + (v[q] >> 16); bi[q] = 0u; }
                 uint32_t tot;
-                uint32_t run = m5_block_excl_scan(mine, sm, tot);
+                uint32_t run = m5_block_excl_scan(mine, sm, tot);       // (one block barrier inside)
 #pragma unroll
                 for (int q = 0; q < M5_MB / 2; q++) {
                     const uint32_t p0 = run, p1 = run + (v[q] & 0xffffu);
@@ -508,60 +602,14 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                     run = p1 + (v[q] >> 16);
                 }
             }
-            if (tid == 0) {
-                for (uint32_t k = 0; k < a_nnew; k++) {
-                    const uint32_t id = a_nb + k;
-                    if (id < P.max_chunks) { P.chunk_part[id] = part; P.chunk_seq[id] = sm.seq + k; P.chunk_rows[id] = DK_CH; }
-                }
-                sm.have_cur = a_have; sm.newbase = a_nb;
-            }
-            __syncthreads();                                            // B7
-            M5_MARK(7);
-            {
-                const uint32_t have = sm.have_cur, nb = sm.newbase;
-                const uint32_t rp = have ? rpos : 0u;
-                if (G.S4) {
-                    const uint32_t S4 = G.S4, n4 = nout * S4;
-                    for (uint32_t i = tid; i < n4; i += M5_NT) {
-                        const uint32_t rr = S4 == 1 ? i : __umulhi(i, G.divS4), c4 = i - rr * S4;
-                        const uint32_t meta = smeta[rr];
-                        const uint32_t v = rp + (uint32_t)bpos[meta & 0xffffu] + (meta >> 16), k = v / DK_CH, off = v % DK_CH;
-                        const uint32_t chunk = (have && k == 0) ? ccur : nb + (k - have);
-                        const int32_t *src = stage + rr * RS + 4u * c4;
-                        if (chunk < P.max_chunks)
-                            reinterpret_cast<int4 *>(P.out_cnts + ((size_t)chunk * DK_CH + off) * S)[c4] = make_int4(src[0], src[1], src[2], src[3]);
-                    }
-                } else {
-                    for (uint32_t rr = tid / 32u; rr < nout; rr += M5_NT / 32u) {
-                        const uint32_t meta = smeta[rr];
-                        const uint32_t v = rp + (uint32_t)bpos[meta & 0xffffu] + (meta >> 16), k = v / DK_CH, off = v % DK_CH;
-                        const uint32_t chunk = (have && k == 0) ? ccur : nb + (k - have);
-                        if (chunk < P.max_chunks)
-                            for (uint32_t c = lane; c < (uint32_t)S; c += 32u) P.out_cnts[((size_t)chunk * DK_CH + off) * S + c] = stage[rr * RS + c];
-                    }
-                }
-                for (uint32_t rr = tid; rr < nout; rr += M5_NT) {
-                    const uint32_t meta = smeta[rr];
-                    const uint32_t v = rp + (uint32_t)bpos[meta & 0xffffu] + (meta >> 16), k = v / DK_CH, off = v % DK_CH;
-                    const uint32_t chunk = (have && k == 0) ? ccur : nb + (k - have);
-                    if (chunk < P.max_chunks) P.out_keys[(size_t)chunk * DK_CH + off] = skey[rr];
-                }
-            }
             M5_MARK(8);
-            // no barrier: staging, bpos and the partition state are next written behind the coming round's barriers
-            if (tid == 0) {
-                const uint32_t v = (a_have ? sm.rowpos : 0u) + nout;
-                if (a_nnew) {
-                    sm.chunk_cur = a_nb + a_nnew - 1;
-                    sm.seq += a_nnew;
-                    sm.rowpos = v - (a_have + a_nnew - 1) * DK_CH;
-                } else sm.rowpos = v;
-                if (sm.chunk_cur != CHUNK_NONE && sm.rowpos == DK_CH) { sm.chunk_cur = CHUNK_NONE; sm.rowpos = 0; }
+            if (tid == 0) {     // behind the scan's barrier every thread has read this round's counters
                 sm.prow += nout; sm.puni += sm.uround;
                 sm.nstage = 0; sm.uround = 0; sm.ncomplex = 0;
             }
         }
-        __syncthreads();                                                // (no copy is in flight here: a failing attempt issues none)
+        __syncthreads();                                                // (no copy is in flight here: a failing attempt issues none;
+                                                                        //  the last round's rows went out behind B1 above)
         if (tid == 0) {
             if (sm.chunk_cur != CHUNK_NONE && sm.chunk_cur < P.max_chunks) P.chunk_rows[sm.chunk_cur] = sm.rowpos;
             P.part_nchunks[part] = sm.seq;
@@ -595,7 +643,7 @@ static bool m5_make_cfg(int S, size_t smem_budget, M5Cfg &G, int &lv)
     G.off_list = (uint32_t)off; off += (size_t)(M5_NT / 32) * M5_LB;
     G.off_mflag = (uint32_t)off; off += (size_t)M5_M;
     G.off_clist = (uint32_t)off; off += (size_t)M5_M * 2;
-    G.off_small = (uint32_t)off; off += dk_round_up(sizeof(M5Small) + (size_t)sp * 32 + 16, 128);
+    G.off_small = (uint32_t)off; off += dk_round_up(sizeof(M5Small) + (size_t)sp * 56 + 16, 128);
     G.smem_bytes = (uint32_t)off;
     return off <= smem_budget;
 }
