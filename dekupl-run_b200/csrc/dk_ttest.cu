@@ -178,6 +178,157 @@ k_ttest_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, 
     if (ties) atomicAdd(tie_sd, ties);
 }
 
+// ---- fast row kernel (groups in column order, <= TT8_N samples per group, S % 4 == 0, S <= 2 * TT8_N) ----------
+// r2e ncu of k_ttest_rows at cfg 2 (profiles/r02_ttest_before.txt): 2937 warp instructions per 32 rows at 19.5 active
+// lanes. 26 % of them are a SECOND copy of the continued-fraction loop (the x < (v+1)/(v+2.5) branch of the incomplete
+// beta, taken by 12 % of the rows, running with 3.8 lanes), 5 % the direct log path of counts beyond the shared-memory
+// table (1 lane), and 60 % straight-line fp64 code: 25 divisions per row (18 of them by the group sizes, which are
+// constants), 4 square roots, 2 logs, an exp. This kernel computes the same values with
+//   * ONE continued-fraction loop: the branch only selects its parameters (a, b, x), so all lanes iterate together;
+//   * a second-level table in global memory (count < TT8_TN2) behind the shared-memory one: a miss is one 16-byte load;
+//   * reciprocals of the group-size constants, sd^2 taken straight from the sum of squares (no sqrt followed by a
+//     square), t^2 instead of t, x and y from one reciprocal, the Gamma ratio's denominator and the fraction's B folded
+//     into the final division: 7 divisions, 1 square root per row;
+//   * the logs of a group kept in registers (no shared-memory scratch), so two 512-thread CTAs share an SM.
+// Arithmetic that decides exact comparisons is untouched: the logs and their sequential sums, mean = sum / n by a true
+// division, the sum of squared deviations (sd == 0 <=> that sum == 0; TtestFilter.c:128). Everything else moves by
+// a few ulp at most, far inside the 1e-9 contract (tests/test_gpu_parity.py).
+#define TT8_N 8
+#ifndef TT8_THREADS
+#define TT8_THREADS 384
+#endif
+#define TT8_TN 256
+#define TT8_TN2 4096
+
+// continued fraction of I_x(a,b) (Wallis form, see dk_beta_cf): returns A and B unreduced
+__device__ __forceinline__ void dk_beta_cf2(double a, double b, double x, double &Ao, double &Bo)
+{
+    double Ap = 0.0, A = 1.0, Bp = 1.0, B = 1.0, Dp = 1.0;
+    const double ab = a + b;
+    for (int m = 0; m < 2000; m++) {
+        const double fm = (double)m, a2 = a + 2.0 * fm;
+        double N = -(a + fm) * (ab + fm) * x, D = a2 * (a2 + 1.0);               // d_{2m+1}
+        double t = Dp * N;
+        double An = __fma_rn(D, A, t * Ap), Bn = __fma_rn(D, B, t * Bp);
+        Ap = A; A = An; Bp = B; B = Bn; Dp = D;
+        const double m1 = fm + 1.0, a3 = a2 + 1.0;
+        N = m1 * (b - m1) * x; D = a3 * (a3 + 1.0);                              // d_{2m+2}
+        t = Dp * N;
+        An = __fma_rn(D, A, t * Ap); Bn = __fma_rn(D, B, t * Bp);
+        const bool conv = fabs(__fma_rn(An, B, -(A * Bn))) <= 1e-15 * fabs(Bn * B);
+        Ap = A; A = An; Bp = B; B = Bn; Dp = D;
+        if (fabs(B) > 1e100) { Ap *= 1e-100; A *= 1e-100; Bp *= 1e-100; B *= 1e-100; }
+        if (conv) break;
+    }
+    Ao = A; Bo = B;
+}
+
+struct TT8Consts { double rnA, rnB, rnA1, rnB1; };   // 1/nA, 1/nB, 1/(nA-1), 1/(nB-1)
+
+__global__ void k_tt8_table(const double *nf_g, int S, double2 *tab2)
+{
+    const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (uint32_t)S * TT8_TN2) return;
+    const uint32_t k = e / TT8_TN2, cc = e - k * TT8_TN2;
+    const double nf = nf_g[k];
+    double a, l;
+    dk_norm_log<true>((int32_t)cc, nf, 1.0 / nf, a, l);
+    tab2[e] = make_double2(a, l);
+}
+
+__device__ __forceinline__ void tt8_lookup(int32_t cc, int k, const double2 *tab, const double2 *tab2, const double *nf,
+                                           const double *rnf, double &a, double &l)
+{
+    if ((uint32_t)cc < TT8_TN) { const double2 t = tab[(uint32_t)k * TT8_TN + (uint32_t)cc]; a = t.x; l = t.y; }
+    else if ((uint32_t)cc < TT8_TN2) { const double2 t = __ldg(tab2 + (size_t)k * TT8_TN2 + (uint32_t)cc); a = t.x; l = t.y; }
+    else dk_norm_log<true>(cc, nf[k], rnf[k], a, l);
+}
+
+__global__ void __launch_bounds__(TT8_THREADS, 2)
+k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, uint32_t n_chunks, int S, const double *nf_g,
+              const double2 *tab2, int nA, int nB, TT8Consts K, double *p_raw, double *log2fc, unsigned long long *tie_sd)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    double2 *tab = (double2 *)sm;                                // [S][TT8_TN] (a, l)
+    double *nf = (double *)(tab + (size_t)S * TT8_TN);           // [S]
+    double *rnf = nf + S;                                        // [S]
+    const uint32_t T = blockDim.x, cpb = T / DK_CH;
+    for (int i = threadIdx.x; i < S; i += T) { nf[i] = nf_g[i]; rnf[i] = 1.0 / nf_g[i]; }
+    for (uint32_t e = threadIdx.x; e < (uint32_t)S * TT8_TN; e += T) {
+        const uint32_t k = e / TT8_TN, cc = e - k * TT8_TN;
+        tab[e] = tab2[(size_t)k * TT8_TN2 + cc];
+    }
+    __syncthreads();
+    const uint32_t nblk = (n_chunks + cpb - 1) / cpb;
+    unsigned long long ties = 0;
+    for (uint32_t blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
+        const uint32_t oc = blk * cpb + threadIdx.x / DK_CH;
+        const uint32_t j = threadIdx.x % DK_CH;
+        if (oc >= n_chunks) continue;
+        const uint64_t b0 = lbase[oc], b1 = lbase[oc + 1];
+        if (j >= b1 - b0) continue;
+        const int32_t *c = cnts + ((size_t)order[oc] * DK_CH + j) * (size_t)S;
+        // ---- group moments (TtestFilter.c:379-411; sum/mean/sd :77-98), sums sequential in column order
+        double la[TT8_N], sa = 0, sl = 0;
+#pragma unroll
+        for (int i = 0; i < TT8_N; i++)
+            if (i < nA) { double a, l; tt8_lookup(__ldg(c + i), i, tab, tab2, nf, rnf, a, l); sa += a; sl += l; la[i] = l; }
+        const double m1 = sl / nA;                               // mean() of the logs: a true division (it decides sd == 0)
+        double s1 = 0;
+#pragma unroll
+        for (int i = 0; i < TT8_N; i++) if (i < nA) { const double d = la[i] - m1; s1 += d * d; }
+        double sb = 0;
+        sl = 0;
+#pragma unroll
+        for (int i = 0; i < TT8_N; i++)
+            if (i < nB) { double a, l; tt8_lookup(__ldg(c + nA + i), nA + i, tab, tab2, nf, rnf, a, l); sb += a; sl += l; la[i] = l; }
+        const double m2 = sl / nB;
+        double s2 = 0;
+#pragma unroll
+        for (int i = 0; i < TT8_N; i++) if (i < nB) { const double d = la[i] - m2; s2 += d * d; }
+        // ---- Welch (TtestFilter.c:120-150) on sd^2 = s/(n-1)
+        double p;
+        if (s1 == 0 && s2 == 0) p = 0.5;                         // sd1 == 0 && sd2 == 0 (:128)
+        else {
+            const double q1 = s1 * K.rnA1, q2 = s2 * K.rnB1;     // sd1^2, sd2^2
+            const double v1 = q1 * K.rnA, v2 = q2 * K.rnB, vv = v1 + v2;
+            const double den = v1 * v1 * K.rnA1 + v2 * v2 * K.rnB1;
+            const double df = vv * vv / den;                     // :132-138
+            const double dm = m1 - m2, dm2 = dm * dm;            // t^2 = dm2 / vv (:139-143)
+            if (isinf(df) || !(den > 0)) p = dk_student_t_2tail(fabs(dm / sqrt(vv)), df);      // degenerate variances: the old route
+            else {
+                // x = df/(df+t^2), y = t^2/(df+t^2) from one reciprocal
+                const double dv = df * vv, r2 = 1.0 / (dv + dm2);
+                const double x = dv * r2, y = dm2 * r2, v = 0.5 * df;
+                if (!(x > 0.0)) p = 0.0;
+                else if (!(y > 0.0)) p = 1.0;
+                else {
+                    const double INV_SQRT_PI = 0.56418958354775628695;
+                    const double lx = (y < 0.5) ? log1p(-y) : log(x);
+                    double num = 1.0, dg = 1.0, w = v;
+                    while (w < 20.0) { num *= w; dg *= (w + 0.5); w += 1.0; }
+                    const double r = 1.0 / w, rr = r * r;
+                    const double ser = r * (-1.0 / 8.0 + rr * (1.0 / 192.0 + rr * (-1.0 / 640.0 + rr * (17.0 / 14336.0 + rr * (-31.0 / 18432.0)))));
+                    const double front = sqrt(w * y) * INV_SQRT_PI * num * exp(ser + v * lx);   // (its 1/dg joins the last division)
+                    const bool lower = x * (v + 2.5) < (v + 1.0);                               // x < (v+1)/(v+2.5)
+                    const double aa = lower ? v : 0.5, bb = lower ? 0.5 : v, xx = lower ? x : y;
+                    double A, B;
+                    dk_beta_cf2(aa, bb, xx, A, B);
+                    const double res = front * A / (dg * B * aa);
+                    p = lower ? res : 1.0 - res;
+                }
+            }
+        }
+        const uint64_t row = b0 + j;
+        p_raw[row] = p;
+        log2fc[row] = log((sb * K.rnB) / (sa * K.rnA)) * 1.4426950408889634074;   // log(meanB/meanA)/log(2) (:72-75,433)
+        const double eps2 = 1e-24;
+        const double e1 = 1 + fabs(m1), e2 = 1 + fabs(m2);
+        if (s1 * K.rnA1 <= eps2 * e1 * e1 && s2 * K.rnB1 <= eps2 * e2 * e2 && (m1 != 0 || m2 != 0)) ties++;
+    }
+    if (ties) atomicAdd(tie_sd, ties);
+}
+
 void dk_ttest_release(dk_ctx *ctx, dk_ttest *t)
 {
     if (!t) return;
@@ -216,6 +367,43 @@ extern "C" int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf, 
     DK_CUDA(ctx, cudaMemcpyAsync(t->idx_dev, idx.data(), sizeof(int) * (nA + nB), cudaMemcpyHostToDevice, st));
     DK_CUDA(ctx, cudaMemsetAsync(t->tie_counts, 0, 64, st));
     DK_CUDA(ctx, cudaStreamSynchronize(st));          // idx is a local staging vector
+    // fast kernel: groups in column order (what a conditions file listing the samples in matrix order gives), small groups
+    bool ident = true;
+    for (int i = 0; i < nA; i++) if (idxA[i] != i) ident = false;
+    for (int i = 0; i < nB; i++) if (idxB[i] != nA + i) ident = false;
+    bool nf_ok = true;
+    for (int s = 0; s < S; s++) if (!(nf[s] >= 1e-30 && nf[s] <= 1e30)) nf_ok = false;
+    const char *force_old = getenv("DK_TTEST_OLD");
+    if (ident && nf_ok && nA <= TT8_N && nB <= TT8_N && nA + nB <= S && !(force_old && atoi(force_old)) &&
+        (size_t)S * TT8_TN * 16 + 16 * S + 256 <= 100 * 1024) {
+        double2 *tab2 = (double2 *)dk_dev_alloc(ctx, sizeof(double2) * (size_t)S * TT8_TN2);
+        if (!tab2) { dk_ttest_release(ctx, t); return DK_ERR_NOMEM; }
+        k_tt8_table<<<(unsigned)(((size_t)S * TT8_TN2 + 255) / 256), 256, 0, st>>>(t->nf_dev, S, tab2); DK_LAUNCHED(ctx);
+        const size_t smem8 = (size_t)S * TT8_TN * 16 + 16 * S;
+        DK_CUDA(ctx, cudaFuncSetAttribute(k_ttest_rows8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem8));
+        const uint32_t nch8 = (uint32_t)m->n_chunks;
+        if (nch8) {
+            const unsigned cpb = TT8_THREADS / DK_CH;
+            unsigned grid = (nch8 + cpb - 1) / cpb;
+            int per_sm = 1;
+            DK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ttest_rows8, TT8_THREADS, smem8));
+            if (per_sm < 1) per_sm = 1;
+            if (grid > (unsigned)(ctx->sm_count * per_sm)) grid = (unsigned)(ctx->sm_count * per_sm);
+            TT8Consts K;
+            K.rnA = 1.0 / nA; K.rnB = 1.0 / nB; K.rnA1 = 1.0 / (nA - 1); K.rnB1 = 1.0 / (nB - 1);
+            k_ttest_rows8<<<grid, TT8_THREADS, smem8, st>>>(m->cnts, m->order, m->lbase, nch8, S, t->nf_dev, tab2, nA, nB, K,
+                                                            t->p_raw, t->log2fc, (unsigned long long *)(t->tie_counts + 2));
+            DK_LAUNCHED(ctx);
+        }
+        DK_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));
+        DK_CUDA(ctx, cudaStreamSynchronize(st));
+        dk_dev_release(ctx, tab2);
+        float ms8 = 0;
+        cudaEventElapsedTime(&ms8, ctx->ev[0], ctx->ev[1]);
+        ctx->stage_ms[2] = ms8;
+        *out = t;
+        return DK_OK;
+    }
     int nmax = nA > nB ? nA : nB;
     // Block size and (a, l) table size. The kernel is latency-bound (dependent fp64 chains, scattered count loads:
     // r01j ncu), so resident warps matter most: take the largest block whose per-thread scratch (nmax doubles) still

@@ -80,6 +80,10 @@ void orc_bh(const double *p_raw, size_t R, double *p_adj);
 size_t orc_filter(const double *p_adj, const double *log2fc, size_t R,
                   double pmax, double fmin, uint8_t *keep);
 
+/* text I/O used by bench.py's CPU baseline only: dumps as joinCounts reads them, rows as it prints them */
+long orc_write_dump_text(const char *path, const uint64_t *keys, const int32_t *cnts, size_t n, int k);
+long orc_parse_matrix_text(const char *path, int S, int32_t *cnts, size_t cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -198,3 +198,50 @@ long long orc_count_kmers(const char *bases, const uint64_t *offsets, size_t n_r
     free(v);
     return (long long)o;
 }
+
+/* ---- text I/O for the CPU baseline of bench.py (test infrastructure) ---------------------------------------
+ * orc_write_dump_text: one sample's dump as `jellyfish dump -c | sort` leaves it ("KMER COUNT\n", the format
+ * joinCounts.c:55-68 reads), from the packed arrays. orc_parse_matrix_text: the rows joinCounts prints
+ * ("KMER(\tCOUNT)xS\n", joinCounts.c:105-109) back into an int matrix, tokens as kseq's ks_getuntil / atoi see them. */
+#include <stdio.h>
+long orc_write_dump_text(const char *path, const uint64_t *keys, const int32_t *cnts, size_t n, int k)
+{
+    FILE *f = fopen(path, "w");
+    if (!f) return -1;
+    static const char B[4] = {'A', 'C', 'G', 'T'};
+    char line[96];
+    long bytes = 0;
+    for (size_t i = 0; i < n; i++) {
+        for (int j = 0; j < k; j++) line[j] = B[(keys[i] >> (2 * (k - 1 - j))) & 3];
+        int len = k + snprintf(line + k, sizeof line - k, "\t%d\n", cnts[i]);
+        fwrite(line, 1, (size_t)len, f);
+        bytes += len;
+    }
+    fclose(f);
+    return bytes;
+}
+/* returns the number of rows parsed (<= cap); a first line that starts with a non-ACGT token is skipped as a header */
+long orc_parse_matrix_text(const char *path, int S, int32_t *cnts, size_t cap)
+{
+    FILE *f = fopen(path, "r");
+    if (!f) return -1;
+    size_t bufn = 1 << 20;
+    char *line = (char *)malloc(bufn);
+    long R = 0;
+    while ((size_t)R < cap && fgets(line, (int)bufn, f)) {
+        char *p = line;
+        while (*p && *p != '\t' && *p != ' ' && *p != '\n') p++;          /* the k-mer token */
+        if (R == 0 && !(line[0] == 'A' || line[0] == 'C' || line[0] == 'G' || line[0] == 'T')) continue;
+        int s = 0;
+        while (s < S && *p && *p != '\n') {
+            while (*p == '\t' || *p == ' ') p++;
+            cnts[(size_t)R * S + s++] = atoi(p);                          /* joinCounts.c:68, TtestFilter.c:380 */
+            while (*p && *p != '\t' && *p != ' ' && *p != '\n') p++;
+        }
+        for (; s < S; s++) cnts[(size_t)R * S + s] = 0;
+        R++;
+    }
+    free(line);
+    fclose(f);
+    return R;
+}

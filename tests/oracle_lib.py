@@ -36,6 +36,10 @@ def load():
     L.orc_antijoin.argtypes = [vp, sz, vp, sz, vp]
     L.orc_count_kmers.restype = C.c_longlong
     L.orc_count_kmers.argtypes = [vp, vp, sz, vp, i32, i32, C.c_uint32, vp, vp, sz]
+    L.orc_write_dump_text.restype = C.c_long
+    L.orc_write_dump_text.argtypes = [C.c_char_p, vp, vp, sz, i32]
+    L.orc_parse_matrix_text.restype = C.c_long
+    L.orc_parse_matrix_text.argtypes = [C.c_char_p, i32, vp, sz]
     L.orc_bh.restype = None
     L.orc_bh.argtypes = [vp, sz, vp]
     L.orc_filter.restype = sz
@@ -143,3 +147,20 @@ def bh(p):
 
 def student_t_2tail(t, df):
     return load().orc_student_t_2tail(float(t), float(df))
+
+
+def write_dump_text(path, keys, cnts, k=31):
+    """one sample's dump as text ("KMER<tab>COUNT" lines, what joinCounts reads); returns the bytes written"""
+    keys = np.ascontiguousarray(keys, dtype=np.uint64)
+    cnts = np.ascontiguousarray(cnts, dtype=np.int32)
+    n = load().orc_write_dump_text(path.encode(), keys.ctypes.data, cnts.ctypes.data, len(keys), k)
+    assert n >= 0, path
+    return int(n)
+
+
+def parse_matrix_text(path, S, cap):
+    """the rows joinCounts printed (optionally behind a header line) as an int32 matrix"""
+    out = np.empty((cap, S), np.int32)
+    R = load().orc_parse_matrix_text(path.encode(), S, out.ctypes.data, cap)
+    assert R >= 0, path
+    return out[:R]
