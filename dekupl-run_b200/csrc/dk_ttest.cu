@@ -197,7 +197,9 @@ k_ttest_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, 
 #ifndef TT8_THREADS
 #define TT8_THREADS 384
 #endif
+#ifndef TT8_TN
 #define TT8_TN 256
+#endif
 #define TT8_TN2 4096
 
 // continued fraction of I_x(a,b) (Wallis form, see dk_beta_cf): returns A and B unreduced
@@ -244,7 +246,21 @@ __device__ __forceinline__ void tt8_lookup(int32_t cc, int k, const double2 *tab
     else dk_norm_log<true>(cc, nf[k], rnf[k], a, l);
 }
 
-__global__ void __launch_bounds__(TT8_THREADS, 2)
+#ifndef TT8_MINB
+#define TT8_MINB 2
+#endif
+#define TT8_BINS 64
+// The continued fraction needs 1 to ~20 steps depending on where x sits between 0 and the switch point, so rows that
+// share a warp by row order keep 12 of 32 lanes busy in its loop (r2g ncu: 44 % of the kernel's instructions). Each
+// tile of rows is therefore processed in two phases: (1) one thread per row does everything up to the fraction's
+// arguments and queues (x, v, front, denominator, row); the queue is ordered by a 64-bin counting sort on x (steps
+// needed grow with x, per branch); (2) thread i evaluates the fraction of queue entry i, so a warp holds rows of
+// similar x. The values computed per row do not depend on the order.
+// VEC (S % 4 == 0, nA % 4 == 0): the tile's rows are fetched by cp.async one tile ahead into a per-thread 64-byte
+// slot (r2i ncu: after the re-binning the kernel waited on its 16 dependent 4-byte count loads, long scoreboard
+// 3.2 per issue), and read back with 16-byte shared loads (slot segments swizzled: conflict-free)
+template <bool VEC>
+__global__ void __launch_bounds__(TT8_THREADS, TT8_MINB)
 k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, uint32_t n_chunks, int S, const double *nf_g,
               const double2 *tab2, int nA, int nB, TT8Consts K, double *p_raw, double *log2fc, unsigned long long *tie_sd)
 {
@@ -253,6 +269,23 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
     double *nf = (double *)(tab + (size_t)S * TT8_TN);           // [S]
     double *rnf = nf + S;                                        // [S]
     const uint32_t T = blockDim.x, cpb = T / DK_CH;
+    double *q_x = rnf + S, *q_v = q_x + T, *q_f = q_v + T, *q_d = q_f + T;   // [T] each: queue of fraction arguments
+    unsigned long long *q_row = (unsigned long long *)(q_d + T);             // [T] row | lower << 63
+    uint32_t *hist = (uint32_t *)(q_row + T);                                // [BINS] + [BINS] bases + total
+    uint32_t *base = hist + TT8_BINS;
+    int32_t *slot = (int32_t *)(hist + 2 * TT8_BINS + 4) + (size_t)threadIdx.x * 16;   // VEC: my row of the tile in flight
+    const uint32_t swz = (threadIdx.x >> 1) & 3u;
+    // VEC: start the copy of my row of tile `b` (nothing for a thread without a row there)
+    auto fetch = [&](uint32_t b) {
+        const uint32_t oc = b * cpb + threadIdx.x / DK_CH, j = threadIdx.x % DK_CH;
+        if (b < (n_chunks + cpb - 1) / cpb && oc < n_chunks && j < lbase[oc + 1] - lbase[oc]) {
+            const int32_t *src = cnts + ((size_t)order[oc] * DK_CH + j) * (size_t)S;
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(slot);
+            for (int q = 0; q < S / 4; q++)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst + ((q ^ swz) << 4)), "l"(src + 4 * q) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
     for (int i = threadIdx.x; i < S; i += T) { nf[i] = nf_g[i]; rnf[i] = 1.0 / nf_g[i]; }
     for (uint32_t e = threadIdx.x; e < (uint32_t)S * TT8_TN; e += T) {
         const uint32_t k = e / TT8_TN, cc = e - k * TT8_TN;
@@ -261,70 +294,122 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
     __syncthreads();
     const uint32_t nblk = (n_chunks + cpb - 1) / cpb;
     unsigned long long ties = 0;
+    if (VEC) fetch(blockIdx.x);
     for (uint32_t blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
+        if (threadIdx.x < TT8_BINS) hist[threadIdx.x] = 0;
         const uint32_t oc = blk * cpb + threadIdx.x / DK_CH;
         const uint32_t j = threadIdx.x % DK_CH;
-        if (oc >= n_chunks) continue;
-        const uint64_t b0 = lbase[oc], b1 = lbase[oc + 1];
-        if (j >= b1 - b0) continue;
-        const int32_t *c = cnts + ((size_t)order[oc] * DK_CH + j) * (size_t)S;
-        // ---- group moments (TtestFilter.c:379-411; sum/mean/sd :77-98), sums sequential in column order
-        double la[TT8_N], sa = 0, sl = 0;
+        bool act = oc < n_chunks;
+        uint64_t b0 = 0;
+        if (act) { b0 = lbase[oc]; act = j < lbase[oc + 1] - b0; }
+        bool needcf = false;
+        uint32_t bin = 0;
+        double c_x = 0, c_v = 0, c_f = 0, c_d = 1;
+        bool lower = false;
+        if (act) {
+            const int32_t *c = cnts + ((size_t)order[oc] * DK_CH + j) * (size_t)S;
+            int32_t cA[TT8_N], cB[TT8_N];
+            if (VEC) {
+                asm volatile("cp.async.wait_group 0;" ::: "memory");           // my own copy: no barrier needed
+                const int4 *s4 = reinterpret_cast<const int4 *>(slot);
+                const uint32_t qb = (uint32_t)nA >> 2;
+                const int4 a0 = s4[0 ^ swz], a1 = s4[1 ^ swz], b0v = s4[(qb & 3u) ^ swz], b1v = s4[((qb + 1u) & 3u) ^ swz];
+                cA[0] = a0.x; cA[1] = a0.y; cA[2] = a0.z; cA[3] = a0.w; cA[4] = a1.x; cA[5] = a1.y; cA[6] = a1.z; cA[7] = a1.w;
+                cB[0] = b0v.x; cB[1] = b0v.y; cB[2] = b0v.z; cB[3] = b0v.w; cB[4] = b1v.x; cB[5] = b1v.y; cB[6] = b1v.z; cB[7] = b1v.w;
+            } else {
 #pragma unroll
-        for (int i = 0; i < TT8_N; i++)
-            if (i < nA) { double a, l; tt8_lookup(__ldg(c + i), i, tab, tab2, nf, rnf, a, l); sa += a; sl += l; la[i] = l; }
-        const double m1 = sl / nA;                               // mean() of the logs: a true division (it decides sd == 0)
-        double s1 = 0;
+                for (int i = 0; i < TT8_N; i++) { cA[i] = i < nA ? __ldg(c + i) : 0; cB[i] = i < nB ? __ldg(c + nA + i) : 0; }
+            }
+            // ---- group moments (TtestFilter.c:379-411; sum/mean/sd :77-98), sums sequential in column order
+            double la[TT8_N], sa = 0, sl = 0;
 #pragma unroll
-        for (int i = 0; i < TT8_N; i++) if (i < nA) { const double d = la[i] - m1; s1 += d * d; }
-        double sb = 0;
-        sl = 0;
+            for (int i = 0; i < TT8_N; i++)
+                if (i < nA) { double a, l; tt8_lookup(cA[i], i, tab, tab2, nf, rnf, a, l); sa += a; sl += l; la[i] = l; }
+            const double m1 = sl / nA;                           // mean() of the logs: a true division (it decides sd == 0)
+            double s1 = 0;
 #pragma unroll
-        for (int i = 0; i < TT8_N; i++)
-            if (i < nB) { double a, l; tt8_lookup(__ldg(c + nA + i), nA + i, tab, tab2, nf, rnf, a, l); sb += a; sl += l; la[i] = l; }
-        const double m2 = sl / nB;
-        double s2 = 0;
+            for (int i = 0; i < TT8_N; i++) if (i < nA) { const double d = la[i] - m1; s1 += d * d; }
+            double sb = 0;
+            sl = 0;
 #pragma unroll
-        for (int i = 0; i < TT8_N; i++) if (i < nB) { const double d = la[i] - m2; s2 += d * d; }
-        // ---- Welch (TtestFilter.c:120-150) on sd^2 = s/(n-1)
-        double p;
-        if (s1 == 0 && s2 == 0) p = 0.5;                         // sd1 == 0 && sd2 == 0 (:128)
-        else {
-            const double q1 = s1 * K.rnA1, q2 = s2 * K.rnB1;     // sd1^2, sd2^2
-            const double v1 = q1 * K.rnA, v2 = q2 * K.rnB, vv = v1 + v2;
-            const double den = v1 * v1 * K.rnA1 + v2 * v2 * K.rnB1;
-            const double df = vv * vv / den;                     // :132-138
-            const double dm = m1 - m2, dm2 = dm * dm;            // t^2 = dm2 / vv (:139-143)
-            if (isinf(df) || !(den > 0)) p = dk_student_t_2tail(fabs(dm / sqrt(vv)), df);      // degenerate variances: the old route
-            else {
-                // x = df/(df+t^2), y = t^2/(df+t^2) from one reciprocal
-                const double dv = df * vv, r2 = 1.0 / (dv + dm2);
-                const double x = dv * r2, y = dm2 * r2, v = 0.5 * df;
-                if (!(x > 0.0)) p = 0.0;
-                else if (!(y > 0.0)) p = 1.0;
+            for (int i = 0; i < TT8_N; i++)
+                if (i < nB) { double a, l; tt8_lookup(cB[i], nA + i, tab, tab2, nf, rnf, a, l); sb += a; sl += l; la[i] = l; }
+            const double m2 = sl / nB;
+            double s2 = 0;
+#pragma unroll
+            for (int i = 0; i < TT8_N; i++) if (i < nB) { const double d = la[i] - m2; s2 += d * d; }
+            // ---- Welch (TtestFilter.c:120-150) on sd^2 = s/(n-1)
+            double p = 0.5;                                      // sd1 == 0 && sd2 == 0 (:128)
+            if (!(s1 == 0 && s2 == 0)) {
+                const double q1 = s1 * K.rnA1, q2 = s2 * K.rnB1; // sd1^2, sd2^2
+                const double v1 = q1 * K.rnA, v2 = q2 * K.rnB, vv = v1 + v2;
+                const double den = v1 * v1 * K.rnA1 + v2 * v2 * K.rnB1;
+                const double df = vv * vv / den;                 // :132-138
+                const double dm = m1 - m2, dm2 = dm * dm;        // t^2 = dm2 / vv (:139-143)
+                if (isinf(df) || !(den > 0)) p = dk_student_t_2tail(fabs(dm / sqrt(vv)), df);  // degenerate variances: the old route
                 else {
-                    const double INV_SQRT_PI = 0.56418958354775628695;
-                    const double lx = (y < 0.5) ? log1p(-y) : log(x);
-                    double num = 1.0, dg = 1.0, w = v;
-                    while (w < 20.0) { num *= w; dg *= (w + 0.5); w += 1.0; }
-                    const double r = 1.0 / w, rr = r * r;
-                    const double ser = r * (-1.0 / 8.0 + rr * (1.0 / 192.0 + rr * (-1.0 / 640.0 + rr * (17.0 / 14336.0 + rr * (-31.0 / 18432.0)))));
-                    const double front = sqrt(w * y) * INV_SQRT_PI * num * exp(ser + v * lx);   // (its 1/dg joins the last division)
-                    const bool lower = x * (v + 2.5) < (v + 1.0);                               // x < (v+1)/(v+2.5)
-                    const double aa = lower ? v : 0.5, bb = lower ? 0.5 : v, xx = lower ? x : y;
-                    double A, B;
-                    dk_beta_cf2(aa, bb, xx, A, B);
-                    const double res = front * A / (dg * B * aa);
-                    p = lower ? res : 1.0 - res;
+                    // x = df/(df+t^2), y = t^2/(df+t^2) from one reciprocal
+                    const double dv = df * vv, r2 = 1.0 / (dv + dm2);
+                    const double x = dv * r2, y = dm2 * r2, v = 0.5 * df;
+                    if (!(x > 0.0)) p = 0.0;
+                    else if (!(y > 0.0)) p = 1.0;
+                    else {
+                        const double INV_SQRT_PI = 0.56418958354775628695;
+                        const double lx = (y < 0.5) ? log1p(-y) : log(x);
+                        double num = 1.0, dg = 1.0, w = v;
+                        while (w < 20.0) { num *= w; dg *= (w + 0.5); w += 1.0; }
+                        const double r = 1.0 / w, rr = r * r;
+                        const double ser = r * (-1.0 / 8.0 + rr * (1.0 / 192.0 + rr * (-1.0 / 640.0 + rr * (17.0 / 14336.0 + rr * (-31.0 / 18432.0)))));
+                        lower = x * (v + 2.5) < (v + 1.0);       // x < (v+1)/(v+2.5)
+                        c_x = lower ? x : y;
+                        c_v = v;
+                        c_f = sqrt(w * y) * INV_SQRT_PI * num * exp(ser + v * lx);   // (its 1/dg joins the last division)
+                        c_d = dg * (lower ? v : 0.5);
+                        needcf = true;
+                        const int bq = lower ? (int)(c_x * 38.0) : (int)(c_x * 80.0);
+                        bin = (lower ? 32u : 0u) + (uint32_t)(bq > 31 ? 31 : bq);
+                    }
                 }
             }
+            const uint64_t row = b0 + j;
+            if (!needcf) p_raw[row] = p;
+            log2fc[row] = log((sb * K.rnB) / (sa * K.rnA)) * 1.4426950408889634074;   // log(meanB/meanA)/log(2) (:72-75,433)
+            const double eps2 = 1e-24;
+            const double e1 = 1 + fabs(m1), e2 = 1 + fabs(m2);
+            if (s1 * K.rnA1 <= eps2 * e1 * e1 && s2 * K.rnB1 <= eps2 * e2 * e2 && (m1 != 0 || m2 != 0)) ties++;
         }
-        const uint64_t row = b0 + j;
-        p_raw[row] = p;
-        log2fc[row] = log((sb * K.rnB) / (sa * K.rnA)) * 1.4426950408889634074;   // log(meanB/meanA)/log(2) (:72-75,433)
-        const double eps2 = 1e-24;
-        const double e1 = 1 + fabs(m1), e2 = 1 + fabs(m2);
-        if (s1 * K.rnA1 <= eps2 * e1 * e1 && s2 * K.rnB1 <= eps2 * e2 * e2 && (m1 != 0 || m2 != 0)) ties++;
+        if (VEC) fetch(blk + gridDim.x);                         // my slot is free: the next tile's row starts flying
+        __syncthreads();                                         // hist is zero
+        uint32_t inbin = 0;
+        if (needcf) inbin = atomicAdd(&hist[bin], 1u);
+        __syncthreads();
+        if (threadIdx.x < 32) {                                  // exclusive prefix of the 64 bins
+            const uint32_t h0 = hist[2 * threadIdx.x], h1 = hist[2 * threadIdx.x + 1];
+            uint32_t x = h0 + h1;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if ((int)threadIdx.x >= o) x += y; }
+            base[2 * threadIdx.x] = x - h0 - h1;
+            base[2 * threadIdx.x + 1] = x - h1;
+            if (threadIdx.x == 31) base[TT8_BINS] = x;
+        }
+        __syncthreads();
+        if (needcf) {
+            const uint32_t pos = base[bin] + inbin;
+            q_x[pos] = c_x; q_v[pos] = c_v; q_f[pos] = c_f; q_d[pos] = c_d;
+            q_row[pos] = (b0 + j) | (lower ? 1ull << 63 : 0ull);
+        }
+        __syncthreads();
+        if (threadIdx.x < base[TT8_BINS]) {
+            const uint32_t i = threadIdx.x;
+            const unsigned long long rw = q_row[i];
+            const bool lw = (rw >> 63) != 0;
+            const double v = q_v[i];
+            double A, B;
+            dk_beta_cf2(lw ? v : 0.5, lw ? 0.5 : v, q_x[i], A, B);
+            const double res = q_f[i] * A / (q_d[i] * B);
+            p_raw[rw & ~(1ull << 63)] = lw ? res : 1.0 - res;
+        }
+        // (the next tile's first barrier orders these reads before the queue is rewritten)
     }
     if (ties) atomicAdd(tie_sd, ties);
 }
@@ -375,23 +460,25 @@ extern "C" int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf, 
     for (int s = 0; s < S; s++) if (!(nf[s] >= 1e-30 && nf[s] <= 1e30)) nf_ok = false;
     const char *force_old = getenv("DK_TTEST_OLD");
     if (ident && nf_ok && nA <= TT8_N && nB <= TT8_N && nA + nB <= S && !(force_old && atoi(force_old)) &&
-        (size_t)S * TT8_TN * 16 + 16 * S + 256 <= 100 * 1024) {
+        (size_t)S * TT8_TN * 16 + 16 * S + (size_t)TT8_THREADS * 104 + 1024 <= 110 * 1024) {
         double2 *tab2 = (double2 *)dk_dev_alloc(ctx, sizeof(double2) * (size_t)S * TT8_TN2);
         if (!tab2) { dk_ttest_release(ctx, t); return DK_ERR_NOMEM; }
         k_tt8_table<<<(unsigned)(((size_t)S * TT8_TN2 + 255) / 256), 256, 0, st>>>(t->nf_dev, S, tab2); DK_LAUNCHED(ctx);
-        const size_t smem8 = (size_t)S * TT8_TN * 16 + 16 * S;
-        DK_CUDA(ctx, cudaFuncSetAttribute(k_ttest_rows8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem8));
+        const bool vec = (S % 4 == 0) && (nA % 4 == 0) && S <= 16;
+        auto k8 = vec ? k_ttest_rows8<true> : k_ttest_rows8<false>;
+        const size_t smem8 = (size_t)S * TT8_TN * 16 + 16 * S + (size_t)TT8_THREADS * 40 + (2 * TT8_BINS + 4) * 4 + (vec ? (size_t)TT8_THREADS * 64 : 0);
+        DK_CUDA(ctx, cudaFuncSetAttribute(k8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem8));
         const uint32_t nch8 = (uint32_t)m->n_chunks;
         if (nch8) {
             const unsigned cpb = TT8_THREADS / DK_CH;
             unsigned grid = (nch8 + cpb - 1) / cpb;
             int per_sm = 1;
-            DK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ttest_rows8, TT8_THREADS, smem8));
+            DK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k8, TT8_THREADS, smem8));
             if (per_sm < 1) per_sm = 1;
             if (grid > (unsigned)(ctx->sm_count * per_sm)) grid = (unsigned)(ctx->sm_count * per_sm);
             TT8Consts K;
             K.rnA = 1.0 / nA; K.rnB = 1.0 / nB; K.rnA1 = 1.0 / (nA - 1); K.rnB1 = 1.0 / (nB - 1);
-            k_ttest_rows8<<<grid, TT8_THREADS, smem8, st>>>(m->cnts, m->order, m->lbase, nch8, S, t->nf_dev, tab2, nA, nB, K,
+            k8<<<grid, TT8_THREADS, smem8, st>>>(m->cnts, m->order, m->lbase, nch8, S, t->nf_dev, tab2, nA, nB, K,
                                                             t->p_raw, t->log2fc, (unsigned long long *)(t->tie_counts + 2));
             DK_LAUNCHED(ctx);
         }
