@@ -78,6 +78,7 @@ def load_library():
         "dk_ttest_adjust_global": (i32, [vp, vp, vp, u64, u64]),
         "dk_ttest_adjust": (i32, [vp, vp, dbl]),
         "dk_bh_rank_slice": (i32, [vp, vp, u64, u64, u64, vp, vp]),
+        "dk_bh_rank_slice_noalloc": (i32, [vp, vp, u64, u64, u64, vp, vp]),
         "dk_ttest_apply_adjusted": (i32, [vp, vp, vp, vp, u64]),
         "dk_ttest_filter": (i32, [vp, vp, dbl, dbl, P(u64), P(u64)]),
         "dk_ttest_export_survivors": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp]),

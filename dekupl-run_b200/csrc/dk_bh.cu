@@ -190,6 +190,59 @@ extern "C" int dk_bh_rank_slice(dk_ctx *ctx, const double *p_dev, uint64_t n, ui
     return DK_OK;
 }
 
+// ---- dk_bh_rank_slice without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops). The scratch the
+// allocating entry point takes from the context's cache (two key buffers, the sort's tile counters, the tile minima)
+// lives in ONE file-scope device array of fixed size: every GPU that loads the library holds these ~4.3 MB until exit.
+// In host code `g_bh_scratch` is only a host-side stand-in for the symbol: its device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+#define BHN_MAX DK_BH_NOALLOC_MAX
+#define BHN_TILES ((BHN_MAX + 4095) / 4096)                    /* tiles of the radix sort (RS_TILE = 4096) */
+#define BHN_OFF_K1 ((size_t)8 * BHN_MAX)
+#define BHN_OFF_CNT ((size_t)16 * BHN_MAX)
+#define BHN_OFF_TMIN (BHN_OFF_CNT + (size_t)4 * 256 * BHN_TILES)
+#define BHN_BYTES (BHN_OFF_TMIN + (size_t)8 * ((BHN_MAX + SM_T * SM_V - 1) / (SM_T * SM_V)) + 256)
+static __device__ __align__(256) unsigned char g_bh_scratch[BHN_BYTES];
+#define BHN_MAX_DEVICES 64
+static unsigned char *g_bh_scratch_addr[BHN_MAX_DEVICES];       // device address of the array, per device ordinal
+
+extern "C" int dk_bh_rank_slice_noalloc(dk_ctx *ctx, const double *p_dev, uint64_t n, uint64_t n_below, uint64_t R_global,
+                                        double *sorted_p_dev, double *F_dev)
+{
+    if (!ctx || (n && (!p_dev || !sorted_p_dev || !F_dev))) return dk_fail(ctx, DK_ERR_ARG, "bh_rank_slice_noalloc: NULL argument");
+    if (n > (uint64_t)BHN_MAX)
+        return dk_fail(ctx, DK_ERR_ARG, "bh_rank_slice_noalloc: %llu p-values exceed the fixed scratch (DK_BH_NOALLOC_MAX = %d); "
+                       "use dk_bh_rank_slice", (unsigned long long)n, (int)BHN_MAX);
+    if (n == 0) return DK_OK;
+    int cur = -1;
+    DK_CUDA(ctx, cudaGetDevice(&cur));
+    if (cur != ctx->device || cur < 0 || cur >= BHN_MAX_DEVICES)
+        return dk_fail(ctx, DK_ERR_ARG, "bh_rank_slice_noalloc: current device %d is not the context's device %d", cur, ctx->device);
+    if (!g_bh_scratch_addr[cur]) {                              // set-up, once per device, that device current
+        void *ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_bh_scratch);
+        if (e != cudaSuccess || !ptr)
+            return dk_fail(ctx, DK_ERR_CUDA, "bh_rank_slice_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        g_bh_scratch_addr[cur] = (unsigned char *)ptr;
+    }
+    unsigned char *sc = g_bh_scratch_addr[cur];
+    uint64_t *k0 = (uint64_t *)sc, *k1 = (uint64_t *)(sc + BHN_OFF_K1);
+    uint32_t *cnt = (uint32_t *)(sc + BHN_OFF_CNT);
+    double *tmin = (double *)(sc + BHN_OFF_TMIN);
+    cudaStream_t st = ctx->stream;
+    // every scratch region is fully written before it is read (keys copied in, counters rewritten by each sort pass,
+    // tile minima written by k_sufmin_tiles): nothing of the previous call's contents is ever consumed
+    const uint64_t nt = (n + SM_T * SM_V - 1) / (SM_T * SM_V);
+    DK_CUDA(ctx, cudaMemcpyAsync(k0, p_dev, 8 * n, cudaMemcpyDeviceToDevice, st));
+    DK_TRY(dk_sort_keys_u64_scratch(ctx, k0, k1, n, cnt));      // positive doubles order like their bit patterns
+    k_bh_v<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(k0, n, (double)R_global, n_below, F_dev); DK_LAUNCHED(ctx);
+    k_sufmin_tiles<<<(unsigned)nt, SM_T, 0, st>>>(F_dev, n, tmin); DK_LAUNCHED(ctx);
+    k_sufmin_scan_tiles<<<1, 32, 0, st>>>(tmin, nt); DK_LAUNCHED(ctx);
+    k_sufmin_apply<<<(unsigned)nt, SM_T, 0, st>>>(F_dev, n, tmin); DK_LAUNCHED(ctx);
+    DK_CUDA(ctx, cudaMemcpyAsync(sorted_p_dev, k0, 8 * n, cudaMemcpyDeviceToDevice, st));
+    return DK_OK;                                               // asynchronous on the context's stream: dk_sync before reading
+}
+
 // adjusted p of this shard's candidates from the global ascending candidate list and its F values
 extern "C" int dk_ttest_apply_adjusted(dk_ctx *ctx, dk_ttest *t, const double *sorted_p_dev, const double *F_dev, uint64_t n_all)
 {

@@ -110,3 +110,47 @@ int dk_sort_pairs_u64(dk_ctx *ctx, uint64_t *keys, uint32_t *vals, uint64_t *key
     dk_dev_release(ctx, hist); dk_dev_release(ctx, cnt);
     return DK_OK;
 }
+
+// ---- key-only sort on caller-supplied scratch: no allocation, no host round trip (dk_bh_rank_slice_noalloc) -----
+// exclusive scan of n <= a few 10^4 counters by ONE block (the allocating dk_scan_excl_u32 is not used here)
+__global__ void k_rs_scan_small(uint32_t *v, uint32_t n)
+{
+    __shared__ uint32_t wsum[32];
+    __shared__ uint32_t carry;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t b = 0; b < n; b += blockDim.x) {
+        const uint32_t i = b + threadIdx.x;
+        const uint32_t x = i < n ? v[i] : 0u;
+        uint32_t incl = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+        if (lane == 31) wsum[w] = incl;
+        __syncthreads();
+        uint32_t woff = 0, tot = 0;
+        for (int q = 0; q < nw; q++) { const uint32_t c = wsum[q]; if (q < w) woff += c; tot += c; }
+        const uint32_t base = carry;
+        if (i < n) v[i] = base + woff + incl - x;
+        __syncthreads();
+        if (threadIdx.x == 0) carry = base + tot;
+        __syncthreads();
+    }
+}
+// all 8 digit passes (no constant-digit skip: that needs a host read-back); 8 is even, so the result lands in `keys`.
+// cnt: 256 * ceil(n / RS_TILE) counters, fully rewritten by every pass (nothing has to start at zero).
+int dk_sort_keys_u64_scratch(dk_ctx *ctx, uint64_t *keys, uint64_t *keys_tmp, size_t n, uint32_t *cnt)
+{
+    if (n < 2) return DK_OK;
+    if (n >= 0xFFFFFFFFull) return dk_fail(ctx, DK_ERR_ARG, "sort: n too large");
+    cudaStream_t st = ctx->stream;
+    const uint32_t ntiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);
+    uint64_t *src = keys, *dst = keys_tmp;
+    for (int d = 0; d < 8; d++) {
+        k_rs_tile_hist<<<ntiles, RS_THREADS, 0, st>>>(src, n, 8 * d, ntiles, cnt); DK_LAUNCHED(ctx);
+        k_rs_scan_small<<<1, 1024, 0, st>>>(cnt, 256u * ntiles); DK_LAUNCHED(ctx);
+        k_rs_scatter<<<ntiles, RS_THREADS, 0, st>>>(src, nullptr, n, 8 * d, ntiles, cnt, dst, nullptr); DK_LAUNCHED(ctx);
+        uint64_t *t = src; src = dst; dst = t;
+    }
+    return DK_OK;
+}

@@ -172,6 +172,17 @@ int dk_ttest_adjust(dk_ctx *ctx, dk_ttest *t, double p_cut);
 int dk_bh_rank_slice(dk_ctx *ctx, const double *p_dev, uint64_t n, uint64_t n_below, uint64_t R_global,
                      double *sorted_p_dev /* out [n] ascending */, double *F_dev /* out [n] running minimum inside the slice */);
 int dk_ttest_apply_adjusted(dk_ctx *ctx, dk_ttest *t, const double *sorted_p_dev, const double *F_dev, uint64_t n_all);
+/* dk_bh_rank_slice for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc). NO counterpart in the reference. Same arguments and same
+ * results as dk_bh_rank_slice, for n <= DK_BH_NOALLOC_MAX p-values (a larger n is refused with DK_ERR_ARG). It calls no
+ * cudaMalloc / cudaFree and no allocating routine: its scratch is one fixed device array inside the library (about
+ * 4.3 MB, held by every GPU that loads the library until exit). The context's device must be the current device.
+ * The work is only ENQUEUED on the context's stream (no synchronisation): dk_sync before reading the outputs.
+ * All calls on one GPU share the scratch, so calls that overlap on that GPU (two contexts or two streams) race;
+ * calls on one stream are ordered and need nothing cleared between them. */
+#define DK_BH_NOALLOC_MAX (1 << 18)
+int dk_bh_rank_slice_noalloc(dk_ctx *ctx, const double *p_dev, uint64_t n, uint64_t n_below, uint64_t R_global,
+                             double *sorted_p_dev /* out [n] ascending */, double *F_dev /* out [n] */);
 /* TtestFilter.c:486: survivors = adj_p <= pmax && fabs(log2FC) >= fmin; returns D in *n_keep.
  * pmax must not exceed the p_cut the adjusted values were computed for (dk_ttest_adjust / _candidates): they are exact
  * only up to it and absent beyond it, so a larger pmax is refused with DK_ERR_ARG.
