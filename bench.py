@@ -52,6 +52,7 @@ def parse():
     ap.add_argument("--no-mask", action="store_true", help="skip the reference-transcript mask measurement")
     ap.add_argument("--no-ingest", action="store_true", help="skip the k-mer counting measurement")
     ap.add_argument("--cpu-rows", type=int, default=6_000_000, help="union rows of the CPU-baseline sample")
+    ap.add_argument("--ref-rows-per-core", type=int, default=1_000_000, help="--impl reference: union rows of the sample per host core")
     return ap.parse_args()
 
 
@@ -161,32 +162,137 @@ def make_cpu_sample(cfg, rows, row0=0, **eff):
     return [x.cpu().numpy().view(np.uint64) for x in k], [x.cpu().numpy() for x in c]
 
 
+# ---- the reference's own tools on plain text (SURVEY §8d / BASELINE.md §3) -------------------------------------
+REF_DIR = os.path.join(ROOT, "oracle", "_ref")
+
+
+def _host_cores():
+    try:
+        return sorted(os.sched_getaffinity(0))
+    except AttributeError:
+        return list(range(os.cpu_count() or 1))
+
+
+def stage_text_sample(keys, cnts, P, workdir):
+    """OUTSIDE the timed region: cut the sample into P key ranges (rows are independent across key ranges, the merge is
+    prefix-separable) and write every range of every dump as the plain text joinCounts reads ("KMER<tab>COUNT" lines)."""
+    import numpy as np
+    import oracle_lib as orc
+    os.makedirs(workdir, exist_ok=True)
+    if P > 1:
+        allk = np.concatenate([k[:: max(1, len(k) // 4096)] for k in keys if len(k)])
+        edges = np.quantile(allk, np.linspace(0, 1, P + 1)[1:-1]).astype(np.uint64)
+        cuts = [np.concatenate([[0], np.searchsorted(k, edges), [len(k)]]) for k in keys]
+    else:
+        cuts = [np.array([0, len(k)]) for k in keys]
+    files, nbytes = [], 0
+    for p in range(P):
+        fs = []
+        for s, (k, c) in enumerate(zip(keys, cnts)):
+            f = os.path.join(workdir, f"part{p}_sample{s}.txt")
+            nbytes += orc.write_dump_text(f, k[cuts[s][p]:cuts[s][p + 1]], c[cuts[s][p]:cuts[s][p + 1]])
+            fs.append(f)
+        files.append(fs)
+    return files, nbytes
+
+
+def cpu_reference_text(files, cfg, nA, workdir, cores):
+    """ONE timed pass of the reference's CPU path over the staged text: P = len(files) processes, one per key range,
+    each pinned to its own core with taskset:  joinCounts (UNMODIFIED binary, share/joinCounts) -> cat behind a header
+    line (Snakefile:594-596) -> computeNF (UNMODIFIED binary, on the whole table: it stops early by itself) -> the
+    TtestFilter row pass per range (port: Boost is absent, oracle/oracle_ttest_cli.c) -> BH + filter on the concatenated
+    p-values in one process, like the reference (TtestFilter.c:456-497). Returns (R, D, seconds)."""
+    import numpy as np
+    import oracle_lib as orc
+    S, P = cfg["S"], len(files)
+    jc, nfb, tt = (os.path.join(REF_DIR, x) for x in ("joinCounts", "computeNF", "ttest_text"))
+    pin = lambda i: ["taskset", "-c", str(cores[i % len(cores)])]
+    t0 = time.perf_counter()
+    raws, procs = [], []
+    for p in range(P):
+        raw = os.path.join(workdir, f"raw{p}.tsv")
+        raws.append(raw)
+        procs.append(subprocess.Popen(pin(p) + [jc, "-r", str(cfg["r"]), "-a", str(cfg["a"])] + files[p], stdout=open(raw, "wb")))
+    if any(q.wait() != 0 for q in procs):
+        raise RuntimeError("reference joinCounts failed")
+    table = os.path.join(workdir, "raw-counts.tsv")
+    with open(table, "wb") as out:
+        out.write(("tag\t" + "\t".join(f"s{i}" for i in range(S)) + "\n").encode())
+        for raw in raws:
+            with open(raw, "rb") as f:
+                while True:
+                    b = f.read(1 << 24)
+                    if not b:
+                        break
+                    out.write(b)
+    r = subprocess.run(pin(0) + [nfb, table], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("reference computeNF failed: " + r.stderr[-200:])
+    nf = [ln.split("\t")[1] for ln in r.stdout.strip().splitlines()[1:]]          # "%f" text, as TtestFilter reads it
+    procs = []
+    for p in range(P):
+        procs.append(subprocess.Popen(pin(p) + [tt, raws[p], str(S), str(nA), raws[p] + ".p", raws[p] + ".fc"] + nf,
+                                      stdout=subprocess.DEVNULL))
+    if any(q.wait() != 0 for q in procs):
+        raise RuntimeError("ttest_text failed")
+    pv = np.concatenate([np.fromfile(raw + ".p") for raw in raws])
+    fc = np.concatenate([np.fromfile(raw + ".fc") for raw in raws])
+    adj = orc.bh(pv)
+    D = int(((adj <= PMAX) & (np.abs(fc) >= FMIN)).sum())
+    dt = time.perf_counter() - t0
+    cpu_reference_text.nf = [float(x) for x in nf]
+    return len(pv), D, dt
+
+
+def _union_size(keys):
+    import numpy as np
+    return int(len(np.unique(np.concatenate(keys)))) if keys else 0
+
+
+def _workdir():
+    base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+    import tempfile
+    return tempfile.mkdtemp(prefix="dk_cpu_ref_", dir=base)
+
+
 def run_reference(args):
-    """--impl reference: rank 0 alone; the other ranks exit 0 without work"""
+    """--impl reference: rank 0 alone; the other ranks exit 0 without work. The reference's CPU tools on plain text,
+    one process per host core (see cpu_reference_text)."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
+    import shutil
     cfg = CONFIGS[args.config]
     S = cfg["S"]
-    idxA, idxB = list(range(S // 2)), list(range(S // 2, S))
-    threads = os.cpu_count() or 1
-    rows = args.cpu_rows * min(threads, 8)
+    cores = _host_cores()
+    P = len(cores)
+    rows = args.ref_rows_per_core * P
     keys, cnts = make_cpu_sample(cfg, rows)
-    times, U = [], 0
-    for i in range(args.warmup + args.steps):
-        U, R, D, dt = cpu_path(keys, cnts, cfg, idxA, idxB, threads)
-        if i >= args.warmup:
-            times.append(dt)
+    U = _union_size(keys)
+    wd = _workdir()
+    try:
+        files, nbytes = stage_text_sample(keys, cnts, P, wd)
+        times, R, D = [], 0, 0
+        for i in range(args.warmup + args.steps):
+            R, D, dt = cpu_reference_text(files, cfg, S // 2, wd, cores)
+            if i >= args.warmup:
+                times.append(dt)
+    finally:
+        shutil.rmtree(wd, ignore_errors=True)
     ms = 1e3 * sum(times) / len(times)
     val = U / (ms / 1e3)
-    sample = f"first {rows} of {cfg['U']} union rows of the same generator (prefix shard), {sum(len(k) for k in keys)} records"
+    sample = (f"first {rows} of {cfg['U']} union rows of the same generator (prefix shard: {U} union k-mers, "
+              f"{sum(len(k) for k in keys)} records, {nbytes / 1e9:.2f} GB of plain-text dumps staged outside the timed region), "
+              f"cut into {P} key ranges")
     print(json.dumps({
         "impl": "reference", "metric": "union k-mers/s merged+tested", "value": val, "unit": "k-mers/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u64 keys / i32 counts / f64 statistics", "data": "synthetic",
-        "config": {"workload": cfg["name"], "sample": sample},
-        "cpu_baseline": {"value": val, "unit": "k-mers/s", "cores": threads, "kind": "port", "sample": sample,
-                         "note": "oracle C port of joinCounts+computeNF+TtestFilter (TtestFilter needs Boost: unbuildable here), "
-                                 "prefix-split over all host threads"},
+        "config": {"workload": cfg["name"], "sample": sample, "filtered_rows": R, "survivors": D},
+        "cpu_baseline": {"value": val, "unit": "k-mers/s", "cores": P, "kind": "reference+port", "sample": sample,
+                         "note": "UNMODIFIED reference joinCounts and computeNF binaries (oracle/_ref, built from /root/reference/share) "
+                                 "on plain text, one taskset-pinned process per core and key range; TtestFilter needs Boost "
+                                 "(unbuildable here): its row pass is the oracle port as a process over the same text "
+                                 "(oracle/_ref/ttest_text), BH + filter single-threaded as in the reference"},
         "e2e": {"value": val, "unit": "k-mers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
@@ -320,11 +426,24 @@ def run_ours(args):
         out["parity_check"] = parity_checks(args, cfg, ctx, dev, rank, world, dist, keys, cnts, kp, cp, n, rows_total, rows_rank,
                                             idxA, idxB, nf_mode)
     if rank == 0 and not args.no_cpu:
+        import shutil
         ck, cc = make_cpu_sample(cfg, args.cpu_rows)
-        cU, cR, cD, dt = cpu_path(ck, cc, cfg, idxA, idxB, 1)
-        out["cpu_baseline"] = {"value": cU / dt, "unit": "k-mers/s", "cores": 1, "kind": "port", "seconds": dt,
-                               "sample": f"first {args.cpu_rows} of {cfg['U']} rows of the same generator ({cU} union k-mers), "
-                                         "oracle C port of the three single-threaded reference tools"}
+        cU = _union_size(ck)
+        wd = _workdir()
+        try:
+            files, nbytes = stage_text_sample(ck, cc, 1, wd)
+            cR, cD, dt = cpu_reference_text(files, cfg, S // 2, wd, _host_cores()[:1])
+        finally:
+            shutil.rmtree(wd, ignore_errors=True)
+        out["cpu_baseline"] = {"value": cU / dt, "unit": "k-mers/s", "cores": 1, "kind": "reference+port", "seconds": dt,
+                               "sample": f"first {args.cpu_rows} of {cfg['U']} rows of the same generator ({cU} union k-mers, "
+                                         f"{nbytes / 1e9:.2f} GB of plain-text dumps staged outside the timed region): the UNMODIFIED "
+                                         "reference joinCounts and computeNF binaries + the TtestFilter port (Boost absent) as "
+                                         "processes over text, taskset to one core"}
+        pU, pR, pD, pdt = cpu_path(ck, cc, cfg, idxA, idxB, 1)
+        out["cpu_baseline_port"] = {"value": pU / pdt, "unit": "k-mers/s", "cores": 1, "kind": "port", "seconds": pdt,
+                                    "sample": "the same sample as packed arrays through the oracle C port (no text, no processes)",
+                                    "agrees_with_reference_tools": bool(pR == cR and pD == cD)}
     # ---- e2e last: it releases the device-resident dumps to make room for nothing, but pins host copies of them
     if not args.no_e2e and world == 1:
         out["e2e"] = run_e2e(args, cfg, ctx, keys, cnts, n, idxA, idxB, nf_mode)
