@@ -317,16 +317,26 @@ def run_ours(args):
     strong = bool(cfg.get("strong"))                    # cfg3 does not fit one GPU: its U is split over the ranks
     rows_rank = int(cfg["U"] * args.scale) // (world if strong else 1)
     rows_total = rows_rank * world                      # weak scaling (default): every rank owns a full-size prefix shard
+    ctx = dk.Context(local)
+    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     t0 = time.time()
-    keys, cnts = synth.gen_shard(S, rows_total, rank * rows_rank, (rank + 1) * rows_rank, device=dev, model=cfg["model"],
+    row_lo, row_hi, splitter_info = rank * rows_rank, (rank + 1) * rows_rank, None
+    if world > 1:
+        # shards are k-mer ranges with equal record counts: every rank derives the same boundaries from a coarse
+        # sample of the whole input (1 row in ~5000) with dk_key_splitters and generates the rows of its own k-mer range
+        smp = synth.gen_row_sample(S, rows_total, 250_000, device=dev, model=cfg["model"], q=cfg["q"], alpha=cfg["alpha"])
+        spl = ctx.key_splitters([k.data_ptr() for k in smp], [int(k.numel()) for k in smp], world)
+        bounds = [0] + [int(int(x) // synth.key_stride(rows_total)) for x in spl] + [rows_total]
+        row_lo, row_hi = bounds[rank], bounds[rank + 1]
+        splitter_info = {"kmer_boundaries": [int(x) for x in spl], "rows_of_rank0": bounds[1]}
+        del smp
+    keys, cnts = synth.gen_shard(S, rows_total, row_lo, row_hi, device=dev, model=cfg["model"],
                                  q=cfg["q"], alpha=cfg["alpha"])
     torch.cuda.synchronize()
     t_gen = time.time() - t0
     n = [int(k.numel()) for k in keys]
     n_rec = sum(n)
     kp, cp = [k.data_ptr() for k in keys], [c.data_ptr() for c in cnts]
-    ctx = dk.Context(local)
-    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     nf_mode = dk.NF_REFERENCE if args.nf == "reference" else dk.NF_FULL
 
     if world == 1:
@@ -371,6 +381,11 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     U, R = stats["U"], stats["R"]
+    n_rec_all = n_rec
+    if dist:
+        t = torch.tensor([n_rec], dtype=torch.int64, device=dev)
+        dist.all_reduce(t)
+        n_rec_all = int(t.item())
     value = U / (ms / 1e3)
     R_loc = stats.get("R_local", R)
     b_all, b_merge = algorithmic_bytes(n_rec, R_loc, S)
@@ -399,9 +414,11 @@ def run_ours(args):
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None,
         "dtype": "u64 keys / i32 counts / f64 statistics", "data": "synthetic",
         "config": {"workload": cfg["name"] + (f" (scale {args.scale})" if args.scale != 1.0 else ""), "rows_per_gpu": rows_rank,
-                   "union_kmers": U, "records": n_rec * world if world > 1 else n_rec, "filtered_rows": R, "survivors": stats["D"],
+                   "union_kmers": U, "records": n_rec_all, "filtered_rows": R, "survivors": stats["D"],
                    "nf_mode": args.nf, "pmax": PMAX, "l2": "inputs (%.1f GB/GPU) far larger than the 126 MB L2" % (12 * n_rec / 1e9),
-                   "gen_s": round(t_gen, 1), "ties": list(stats["ties"])},
+                   "gen_s": round(t_gen, 1), "ties": list(stats["ties"]),
+                   **({"shards": "k-mer ranges with equal record counts (dk_key_splitters on a 1-in-%d row sample)" % max(1, rows_total // 250_000),
+                       "records_rank0": n_rec} if world > 1 else {})},
         "gpu_launches": int(launches),
         "stage_ms": {"join": stage_avg[0], "merge_kernel": mk, "nf": stage_avg[1], "ttest": stage_avg[2],
                      "bh_filter": stage_avg[3], **({"note": "rank 0; bh_filter = step - other stages (includes the collectives" + (" and the all-reduced NF select)" if args.nf == "full" else ")")}
@@ -423,7 +440,7 @@ def run_ours(args):
     # with a planted group effect (so that survivors exist) through the same code path as the timed run — run_path at N=1,
     # run_sharded over all ranks at N>1 — against the CPU oracle on rank 0: U, R, D, NFs, matrix checksums, survivor set.
     if not args.no_parity:
-        out["parity_check"] = parity_checks(args, cfg, ctx, dev, rank, world, dist, keys, cnts, kp, cp, n, rows_total, rows_rank,
+        out["parity_check"] = parity_checks(args, cfg, ctx, dev, rank, world, dist, keys, cnts, kp, cp, n, rows_total, (row_lo, row_hi),
                                             idxA, idxB, nf_mode)
     if rank == 0 and not args.no_cpu:
         import shutil
@@ -462,7 +479,7 @@ def _xor_fold(vals):
     return x
 
 
-def parity_checks(args, cfg, ctx, dev, rank, world, dist, keys, cnts, kp, cp, n, rows_total, rows_rank, idxA, idxB, nf_mode):
+def parity_checks(args, cfg, ctx, dev, rank, world, dist, keys, cnts, kp, cp, n, rows_total, row_range, idxA, idxB, nf_mode):
     import numpy as np
     import torch
     import dekupl_run_b200 as dk
@@ -485,7 +502,7 @@ def parity_checks(args, cfg, ctx, dev, rank, world, dist, keys, cnts, kp, cp, n,
         gx, gs = be.m.checksum()
         gU, gR = st["U_local"], st["R_local"]
         be.free()
-    exp = synth.expected_invariants(S, rows_total, rank * rows_rank, (rank + 1) * rows_rank, cfg["r"], cfg["a"], device=dev,
+    exp = synth.expected_invariants(S, rows_total, row_range[0], row_range[1], cfg["r"], cfg["a"], device=dev,
                                     model=cfg["model"], q=cfg["q"], alpha=cfg["alpha"])
     ok = (gU == exp["U"] and gR == exp["R"] and (gx & M64) == exp["key_xor"] and (gs & M64) == exp["count_sum"]
           and exp["records"] == sum(n))

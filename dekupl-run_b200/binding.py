@@ -51,6 +51,7 @@ def load_library():
         "dk_launch_count": (u64, [vp]), "dk_stage_ms": (dbl, [vp, i32]),
         "dk_join_counts": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, P(vp)]),
         "dk_join_counts_dev": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, P(vp)]),
+        "dk_key_splitters": (i32, [vp, i32, P(vp), P(u64), i32, i32, vp]),
         "dk_matrix_from_host": (i32, [vp, i32, u64, vp, vp, P(vp)]),
         "dk_matrix_rows": (u64, [vp]), "dk_matrix_union": (u64, [vp]), "dk_matrix_samples": (i32, [vp]),
         "dk_matrix_export": (i32, [vp, vp, u64, u64, vp, vp]),
@@ -286,6 +287,14 @@ class Context:
         out = C.c_void_p(0)
         self._chk(self.L.dk_join_counts_dev(self.h, S, kp, cp, nn, min_rec, min_abund, int(emit_stale_tail), C.byref(out)))
         return Matrix(self, out)
+
+    def key_splitters(self, key_ptrs, n, G, device_inputs=True):
+        """G-1 count-balanced shard boundaries (uint64 k-mers) for dumps given by pointers (device unless told otherwise)"""
+        S = len(key_ptrs)
+        kp, nn = (C.c_void_p * S)(*key_ptrs), (C.c_uint64 * S)(*n)
+        out = np.zeros(max(G - 1, 1), np.uint64)
+        self._chk(self.L.dk_key_splitters(self.h, S, kp, nn, int(device_inputs), G, _np_ptr(out)))
+        return out[: G - 1]
 
     def matrix_from_host(self, cnts, keys=None):
         cnts = np.ascontiguousarray(cnts, dtype=np.int32)

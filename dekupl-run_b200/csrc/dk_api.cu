@@ -1,6 +1,8 @@
 // dk_api.cu — C-ABI glue: host-buffer entry points, matrix import/export, whole-path driver.
 #include <math.h>
 #include <stdlib.h>
+#include <algorithm>
+#include <utility>
 #include "dk_common.cuh"
 
 void dk_matrix_release(dk_ctx *ctx, dk_matrix *m);
@@ -175,6 +177,56 @@ extern "C" int dk_join_counts(dk_ctx *ctx, int S, const uint64_t *const *keys, c
     cudaStreamSynchronize(ctx->stream);
     dk_dev_release(ctx, slab);
     return rc;
+}
+
+// ---- count-balanced shard boundaries --------------------------------------------------------------
+// Shards are k-mer ranges; real dumps are far from uniform in the key (low-complexity sequence clusters), so equal
+// slices of the key SPACE give unequal work. Every dump is sampled at regular positions (a sample stands for the
+// n_s / m_s records around it), the samples of all dumps are ordered by key and the boundaries are read off where the
+// cumulative record count crosses g/G of the total. The error per boundary is at most one sampling stride per dump.
+__global__ void k_sample_keys(const uint64_t *keys, uint64_t n, uint32_t m, uint64_t *out)
+{
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < m) out[j] = keys[(uint64_t)(((double)j + 0.5) * (double)n / (double)m)];
+}
+
+extern "C" int dk_key_splitters(dk_ctx *ctx, int S, const uint64_t *const *keys, const uint64_t *n, int device_inputs, int G,
+                                uint64_t *splitters)
+{
+    if (!ctx || !keys || !n || (G > 1 && !splitters)) return dk_fail(ctx, DK_ERR_ARG, "key_splitters: NULL argument");
+    if (S < 1 || S > DK_MAX_SAMPLES || G < 1 || G > 4096) return dk_fail(ctx, DK_ERR_ARG, "key_splitters: S=%d G=%d out of range", S, G);
+    if (G == 1) return DK_OK;
+    const uint32_t MS = 16384;                                   // samples per dump
+    std::vector<std::pair<uint64_t, double>> smp;
+    smp.reserve((size_t)S * MS);
+    std::vector<uint64_t> h(MS);
+    uint64_t *d = device_inputs ? (uint64_t *)dk_dev_alloc(ctx, sizeof(uint64_t) * MS) : nullptr;
+    if (device_inputs && !d) return DK_ERR_NOMEM;
+    double total = 0;
+    for (int s = 0; s < S; s++) {
+        if (!n[s]) continue;
+        const uint32_t m = n[s] < MS ? (uint32_t)n[s] : MS;
+        if (device_inputs) {
+            k_sample_keys<<<(m + 255) / 256, 256, 0, ctx->stream>>>(keys[s], n[s], m, d); DK_LAUNCHED(ctx);
+            DK_CUDA(ctx, cudaMemcpyAsync(h.data(), d, sizeof(uint64_t) * m, cudaMemcpyDeviceToHost, ctx->stream));
+            DK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        } else
+            for (uint32_t j = 0; j < m; j++) h[j] = keys[s][(uint64_t)(((double)j + 0.5) * (double)n[s] / (double)m)];
+        const double w = (double)n[s] / (double)m;
+        for (uint32_t j = 0; j < m; j++) smp.emplace_back(h[j], w);
+        total += (double)n[s];
+    }
+    dk_dev_release(ctx, d);
+    std::sort(smp.begin(), smp.end(), [](const std::pair<uint64_t, double> &a, const std::pair<uint64_t, double> &b) { return a.first < b.first; });
+    double cum = 0;
+    size_t i = 0;
+    for (int g = 1; g < G; g++) {
+        const double want = total * (double)g / (double)G;
+        while (i < smp.size() && cum + smp[i].second <= want) cum += smp[i++].second;
+        // shard g starts at this key: records with key < splitters[g-1] belong to shards < g (equal keys never straddle)
+        splitters[g - 1] = i < smp.size() ? smp[i].first : DK_SENTINEL;
+    }
+    return DK_OK;
 }
 
 // ---- matrix ---------------------------------------------------------------------

@@ -166,7 +166,6 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
     const bool owner = tid < S;                      // S <= 32: all dump owners sit in warp 0
     const int ps = tid >> TPSL, psub = tid & (TPS - 1);
     const int gl = lane & (SP - 1);
-    const uint32_t gmask = SP == 32 ? 0xffffffffu : (((1u << SP) - 1u) << (lane & ~(SP - 1)));
     const int gidx = lane >> LV;
     const int min_ab = P.min_abund, min_rec = P.min_rec;
     const uint32_t hth = (uint32_t)(min_rec < 3 ? (min_rec < 1 ? 1 : min_rec) : 3);   // dumps present from which a group gathers
@@ -378,61 +377,69 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                 {
                     unsigned char *lst = lists + warp * M5_LB;
                     const uint32_t wb0 = (uint32_t)warp * M5_LB;
-                    uint32_t hcnt = 0;
+                    uint32_t hcnt = 0, lcnt = 0;                        // heavy list from the front of lst, light list from its back
 #pragma unroll
-                    for (int q = 0; q < M5_MB; q++) {
+                    for (int q = 0; q < M5_MB; q++) {                   // classification only: straight-line code
                         const uint32_t bq = wb0 + q * 32 + lane;
-                        unsigned char *trow = Tb + (size_t)bq * SP;
-                        uint32_t xw[TW], tw[TW], np = 0;
-                        m5_load_row<TW>(trow, xw);
+                        uint32_t xw[TW], np = 0;
+                        m5_load_row<TW>(Tb + (size_t)bq * SP, xw);
 #pragma unroll
-                        for (int w = 0; w < TW; w++) { tw[w] = m5_present_msb(xw[w]); np += __popc(tw[w]); }
+                        for (int w = 0; w < TW; w++) np += __popc(m5_present_msb(xw[w]));
+                        const bool runs = mflag[bq] != 0;
                         const bool heavy = np >= hth;
-                        if (np && !heavy) {                             // L: rec <= np < r, no row can pass (joinCounts.c:104): count the rows
+                        const bool easy = !heavy && np == 1 && !runs;   // one record: one row that cannot pass (rec <= 1 < r)
+                        const bool light = np != 0 && !heavy && !easy;
+                        urows += easy ? 1u : 0u;
+                        const uint32_t hb = __ballot_sync(0xffffffffu, heavy), lb = __ballot_sync(0xffffffffu, light);
+                        const uint32_t below = (1u << lane) - 1u;
+                        if (heavy) lst[hcnt + __popc(hb & below)] = (unsigned char)(q * 32 + lane);
+                        if (light) lst[M5_LB - 1 - (lcnt + __popc(lb & below))] = (unsigned char)(q * 32 + lane);
+                        hcnt += __popc(hb); lcnt += __popc(lb);
+                    }
+                    __syncwarp();
+                    // L: buckets with fewer dumps present than a passing row needs (rec <= np < r, joinCounts.c:104) only have
+                    // their rows COUNTED; one lane per listed bucket
+                    for (uint32_t e0 = 0; e0 < lcnt; e0 += 32) {
+                        if (e0 + lane < lcnt) {
+                            const uint32_t bq = wb0 + lst[M5_LB - 1 - (e0 + lane)];
+                            unsigned char *trow = Tb + (size_t)bq * SP;
+                            uint32_t xw[TW], tw[TW], np = 0, pm = 0;
+                            m5_load_row<TW>(trow, xw);
+#pragma unroll
+                            for (int w = 0; w < TW; w++) {
+                                tw[w] = m5_present_msb(xw[w]); np += __popc(tw[w]);
+                                pm |= (((tw[w] >> 7) * 0x10204080u) >> 28) << (4 * w);
+                            }
                             const bool runs = mflag[bq] != 0;
-                            if (np == 1 && !runs) urows += 1;           // one record: one row
-                            else if (np == 2 && !runs) {                // two records of two dumps: one row if they hold one k-mer
-                                uint32_t pm = 0;
-#pragma unroll
-                                for (int w = 0; w < TW; w++) pm |= (((tw[w] >> 7) * 0x10204080u) >> 28) << (4 * w);
+                            if (np == 2 && !runs) {                     // two records of two dumps: one row if they hold one k-mer
                                 const uint32_t s1 = __ffs(pm) - 1, s2 = 31 - __clz(pm);
-                                urows += bufK[s1 * ks + trow[s1]] == bufK[s2 * ks + trow[s2]] ? 1u : 2u;
-                            } else if (np == 1) {
-                                uint32_t s = 0, i = 0;
-#pragma unroll
-                                for (int w = 0; w < TW; w++)
-                                    if (tw[w]) { const uint32_t by = (uint32_t)(__ffs(tw[w]) - 1) >> 3; s = 4u * w + by; i = (xw[w] >> (8u * by)) & 0xffu; }
-                                const unsigned char *f = fb + s * FBS + i;
+                                const uint32_t i1 = trow[s1], i2 = trow[s2];
+                                urows += bufK[s1 * ks + i1] == bufK[s2 * ks + i2] ? 1u : 2u;
+                            } else if (np == 1) {                       // a run of one dump: as many rows as records
+                                const uint32_t s1 = __ffs(pm) - 1, i1 = trow[s1];
+                                const unsigned char *f = fb + s1 * FBS + i1;
                                 uint32_t rows = 1;
                                 while (!f[rows]) { if (++rows > (uint32_t)FBS) __trap(); }   // (a run ends at the look-ahead slot at the latest)
                                 urows += rows;
-                            } else {
-                                uint32_t pm = 0;
-#pragma unroll
-                                for (int w = 0; w < TW; w++) pm |= (((tw[w] >> 7) * 0x10204080u) >> 28) << (4 * w);
+                            } else {                                    // walk the rows in k-mer order (cursors in the table row)
                                 for (uint32_t guard = 0; pm; guard++) {
                                     if (guard > (uint32_t)(SP * FBS)) __trap();
                                     unsigned long long kmin = DK_SENTINEL;
                                     for (uint32_t m = pm; m; m &= m - 1) {
-                                        const uint32_t s = __ffs(m) - 1;
-                                        const unsigned long long k = bufK[s * ks + trow[s]];
+                                        const uint32_t s2 = __ffs(m) - 1;
+                                        const unsigned long long k = bufK[s2 * ks + trow[s2]];
                                         kmin = k < kmin ? k : kmin;
                                     }
                                     for (uint32_t m = pm; m; m &= m - 1) {
-                                        const uint32_t s = __ffs(m) - 1, i = trow[s];
-                                        if (bufK[s * ks + i] == kmin) {
-                                            if (!fb[s * FBS + i + 1]) trow[s] = (unsigned char)(i + 1); else pm &= ~(1u << s);
+                                        const uint32_t s2 = __ffs(m) - 1, i = trow[s2];
+                                        if (bufK[s2 * ks + i] == kmin) {
+                                            if (!fb[s2 * FBS + i + 1]) trow[s2] = (unsigned char)(i + 1); else pm &= ~(1u << s2);
                                         }
                                     }
                                     urows++;
                                 }
                             }
-                            m5_clear_row<TW>(trow);
-                            if (runs) mflag[bq] = 0;
                         }
-                        const uint32_t hb = __ballot_sync(0xffffffffu, heavy);
-                        if (heavy) lst[hcnt + __popc(hb & ((1u << lane) - 1u))] = (unsigned char)(q * 32 + lane);
-                        hcnt += __popc(hb);
                     }
                     __syncwarp();
                     M5_MARK(5);
@@ -482,7 +489,6 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                                 }
                                 binfo[b] = pass ? 1 : 0;
                                 urows++;
-                                m5_clear_row<TW>(trow);
                             }
                         }
                     }
@@ -541,10 +547,7 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                             if (member) { present = !fg[i]; i++; }                                   // next record of the run, if any
                             pw = __ballot_sync(0xffffffffu, present);
                         }
-                        if (act) {
-                            Tb[(size_t)b * SP + gl] = (unsigned char)M5_EMPTY;
-                            if (gl == 0) { binfo[b] = (uint16_t)npass; mflag[b] = 0; urows += rows; }
-                        }
+                        if (act && gl == 0) { binfo[b] = (uint16_t)npass; urows += rows; }
                     }
                 }
                 {
@@ -552,6 +555,12 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                     if (lane == 0 && ut) atomicAdd(&sm.uround, ut);
                 }
                 __syncthreads();                                        // B4
+                {   // every bucket has been read: table and run flags are emptied for the next pass in one sweep
+                    uint4 *t4 = reinterpret_cast<uint4 *>(Tb);
+#pragma unroll
+                    for (int i = 0; i < M5_M * SP / 16 / M5_NT; i++) t4[tid + i * M5_NT] = make_uint4(~0u, ~0u, ~0u, ~0u);
+                    if (tid < M5_M / 16) reinterpret_cast<uint4 *>(mflag)[tid] = make_uint4(0u, 0u, 0u, 0u);
+                }
                 M5_MARK(7);
                 const uint32_t nst = sm.nstage;
                 if (nst > (uint32_t)M5_CAP) {                           // more survivors than staging slots: smaller round

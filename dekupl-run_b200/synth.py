@@ -40,11 +40,12 @@ def sample_depths(S, seed=SEED):
     return (0.5 + 1.5 * torch.rand(S, generator=g, dtype=torch.float64)).tolist()
 
 
-def _rows(S, U_total, a, b, *, device, model, q, alpha, group_b, seed, eff=4.0, eff_frac=0.01):
-    """rows [a,b) of the implicit union: (key, [(present, count) per sample]) — the one place the generator is defined"""
+def _rows(S, U_total, a, b, *, device, model, q, alpha, group_b, seed, eff=4.0, eff_frac=0.01, index=None):
+    """rows [a,b) of the implicit union (or the rows listed in `index`): (key, [(present, count) per sample]) — the one
+    place the generator is defined"""
     stride = (1 << 62) // U_total
     depths = sample_depths(S, seed)
-    i = torch.arange(a, b, device=device, dtype=torch.int64)
+    i = torch.arange(a, b, device=device, dtype=torch.int64) if index is None else index
     h = mix64(i + seed)
     key = i * stride + (_lsr(h, 2) % stride)
     cls = _lsr(mix64(h ^ 0x5851F42D), 40).to(torch.float64) / float(1 << 24)     # row class uniform [0,1)
@@ -132,3 +133,18 @@ def expected_invariants(S, U_total, row0, row1, r, a, *, device, model="two_clas
             kx ^= v[0]
         csum = (csum + int(tot[keep].sum().item())) & ((1 << 64) - 1)
     return dict(U=U, R=R, key_xor=int(kx.item()) & ((1 << 64) - 1), count_sum=csum, records=n_rec)
+
+
+def key_stride(U_total):
+    """row i of the union owns the keys [i*stride, (i+1)*stride): a k-mer boundary maps back to a generator row"""
+    return (1 << 62) // U_total
+
+
+def gen_row_sample(S, U_total, n_sample, *, device, model="two_class", q=0.075, alpha=2.0, seed=SEED):
+    """every (U_total // n_sample)-th row of the whole union, as per-sample sorted key tensors: the coarse global view
+    from which every rank derives the same count-balanced shard boundaries (dk_key_splitters)"""
+    step = max(1, U_total // n_sample)
+    idx = torch.arange(0, U_total, step, device=device, dtype=torch.int64)
+    key, sample = _rows(S, U_total, 0, 0, device=device, model=model, q=q, alpha=alpha, group_b=set(range(S // 2, S)),
+                        seed=seed, index=idx)
+    return [key[sample(s)[0]].contiguous() for s in range(S)]

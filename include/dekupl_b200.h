@@ -72,6 +72,15 @@ int dk_join_counts_dev(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, cons
                        const uint64_t *n, int min_rec, int min_abund, int emit_stale_tail,
                        dk_matrix **out);
 
+/* ---- shard boundaries for the multi-GPU path ("equal-count splitters"; the reference is one process and
+ * has no counterpart, its order of output rows — ascending k-mers, joinCounts.c:72-115 — is what sharding by k-mer
+ * range preserves). Writes G-1 ascending k-mers: shard g takes the records with splitters[g-1] <= key < splitters[g]
+ * (shard 0 from the smallest key, shard G-1 to the largest). The boundaries are chosen so that every shard holds about
+ * 1/G of ALL records of all dumps, whatever the distribution of the k-mers (every dump is sampled at 16384 regular
+ * positions). Host pointers unless device_inputs. */
+int dk_key_splitters(dk_ctx *ctx, int S, const uint64_t *const *keys, const uint64_t *n, int device_inputs, int G,
+                     uint64_t *splitters /* out [G-1] */);
+
 /* ---- k-mer counting of one sample (replaces `jellyfish count -L L -m K [-C]` on the two mates with
  * bin/revCompFastq.pl:33-44 on one of them, `jellyfish dump -c` and `sort -k1`: Snakefile:523-582) ----
  * bases: the sequence lines of all reads back to back (host); read r is bases[offsets[r] .. offsets[r+1]).

@@ -587,3 +587,46 @@ def test_sharded_c_abi_path_on_one_device(ctx, G, flow):
     np.testing.assert_allclose(got_adj, oadj[got_rows], rtol=RTOL, atol=1e-300)
     for be in bes:
         be.free()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("G,on_device", [(2, True), (8, True), (5, False)])
+def test_key_splitters_balance_records_on_clustered_kmers(ctx, G, on_device):
+    """dk_key_splitters: shards of equal RECORD counts on k-mers that are far from uniform (nested clusters,
+    dumps of very different sizes): every shard within 3 % of 1/G of all records, where an equal split of the key space
+    is off by a large factor; joining the shards one by one and concatenating equals joining everything at once."""
+    import torch
+    rng = np.random.default_rng(77 + G)
+    allk = _clustered_keys(rng, 400_000, 5)
+    keys, cnts = [], []
+    for s in range(6):
+        m = rng.random(len(allk)) < (0.9 if s < 2 else 0.15)
+        keys.append(allk[m]); cnts.append(rng.integers(1, 30, size=int(m.sum())).astype(np.int32))
+    n = [len(k) for k in keys]
+    if on_device:
+        tk = [torch.from_numpy(k.view(np.int64).copy()).cuda() for k in keys]
+        spl = ctx.key_splitters([t.data_ptr() for t in tk], n, G, device_inputs=True)
+    else:
+        spl = ctx.key_splitters([k.ctypes.data for k in keys], n, G, device_inputs=False)
+    assert len(spl) == G - 1 and np.all(np.diff(spl.astype(np.float64)) >= 0)
+    edges = np.concatenate([[0], spl, [np.iinfo(np.uint64).max]]).astype(np.uint64)
+    per = np.array([sum(int(np.searchsorted(k, edges[g + 1]) - np.searchsorted(k, edges[g])) for k in keys) for g in range(G)], float)
+    per[-1] += sum(int((k == np.iinfo(np.uint64).max).sum()) for k in keys)
+    assert per.sum() == sum(n)
+    assert np.max(np.abs(per / per.sum() * G - 1.0)) < 0.03, per / per.sum()
+    naive = np.linspace(float(allk.min()), float(allk.max()), G + 1)[1:-1].astype(np.uint64)
+    ne = np.concatenate([[0], naive, [np.iinfo(np.uint64).max]]).astype(np.uint64)
+    nper = np.array([sum(int(np.searchsorted(k, ne[g + 1]) - np.searchsorted(k, ne[g])) for k in keys) for g in range(G)], float)
+    assert np.max(nper) / np.mean(nper) > 1.5                       # the key-space split really is unbalanced here
+    parts_k, parts_c = [], []
+    for g in range(G):
+        sk, sc = [], []
+        for k, c in zip(keys, cnts):
+            lo, hi = np.searchsorted(k, edges[g]), (np.searchsorted(k, edges[g + 1]) if g + 1 < G else len(k))
+            sk.append(k[lo:hi]); sc.append(c[lo:hi])
+        m = ctx.join_counts(sk, sc, 2, 5)
+        gk, gc = m.export(); m.free()
+        parts_k.append(gk); parts_c.append(gc)
+    ok, oc, _ = orc.join(keys, cnts, 2, 5)
+    np.testing.assert_array_equal(np.concatenate(parts_k), ok)
+    np.testing.assert_array_equal(np.concatenate(parts_c), oc)
