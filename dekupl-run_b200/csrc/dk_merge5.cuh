@@ -41,6 +41,7 @@
 #define M5_M (M5_MB * M5_NT)
 #define M5_LB (32 * M5_MB)         // buckets a warp gathers
 #define M5_EMPTY 0xFFu
+#define M5_BK 32                   // the thread that keeps the partition's chunk bookkeeping (first lane of warp 1)
 
 struct M5Cfg {
     int S;
@@ -236,7 +237,7 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
         if (tid == 0) { sm.chunk_cur = CHUNK_NONE; sm.rowpos = 0; sm.seq = 0; sm.prow = 0; sm.puni = 0; }
         if (owner) issue();
         bool stop = false;
-        // thread 0: the chunk allocation of a round's rows is ISSUED when the round ends and CONSUMED at the top of the next
+        // thread M5_BK: the chunk allocation of a round's rows is ISSUED when the round ends and CONSUMED at the top of the next
         // round (its latency hides behind the scan, the copies' wait and the pivot); the rows are copied out there too
         bool pend = false;
         uint32_t a_have = 0, a_nnew = 0, a_nb = 0, p_nout = 0;
@@ -263,27 +264,27 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                 lastk = m5_warp_max64(lastk);
                 if (firstk != DK_SENTINEL && lastk + 1ull < candk) candk = lastk + 1ull;   // span of the keys staged
                 if (lane < SP) ss.ncm[lane] = ncm;
-                if (lane == 0) {
-                    sm.pivot = candk; sm.base = firstk;
-                    uint32_t cpn = 0;
-                    if (pend) {
-                        for (uint32_t k = 0; k < a_nnew; k++) {
-                            const uint32_t id = a_nb + k;
-                            if (id < P.max_chunks) { P.chunk_part[id] = part; P.chunk_seq[id] = sm.seq + k; P.chunk_rows[id] = DK_CH; }
-                        }
-                        sm.cp_have = a_have; sm.cp_nb = a_nb; sm.cp_rp = a_have ? sm.rowpos : 0u; sm.cp_ccur = sm.chunk_cur;
-                        cpn = p_nout;
-                        const uint32_t v = (a_have ? sm.rowpos : 0u) + p_nout;
-                        if (a_nnew) {
-                            sm.chunk_cur = a_nb + a_nnew - 1;
-                            sm.seq += a_nnew;
-                            sm.rowpos = v - (a_have + a_nnew - 1) * DK_CH;
-                        } else sm.rowpos = v;
-                        if (sm.chunk_cur != CHUNK_NONE && sm.rowpos == DK_CH) { sm.chunk_cur = CHUNK_NONE; sm.rowpos = 0; }
-                        pend = false;
+                if (lane == 0) { sm.pivot = candk; sm.base = firstk; }
+            }
+            if (tid == M5_BK) {   // chunk bookkeeping on warp 1: warp 0 is the round's critical path (pivot, copy issue)
+                uint32_t cpn = 0;
+                if (pend) {
+                    for (uint32_t k = 0; k < a_nnew; k++) {
+                        const uint32_t id = a_nb + k;
+                        if (id < P.max_chunks) { P.chunk_part[id] = part; P.chunk_seq[id] = sm.seq + k; P.chunk_rows[id] = DK_CH; }
                     }
-                    sm.cp_nout = cpn;
+                    sm.cp_have = a_have; sm.cp_nb = a_nb; sm.cp_rp = a_have ? sm.rowpos : 0u; sm.cp_ccur = sm.chunk_cur;
+                    cpn = p_nout;
+                    const uint32_t v = (a_have ? sm.rowpos : 0u) + p_nout;
+                    if (a_nnew) {
+                        sm.chunk_cur = a_nb + a_nnew - 1;
+                        sm.seq += a_nnew;
+                        sm.rowpos = v - (a_have + a_nnew - 1) * DK_CH;
+                    } else sm.rowpos = v;
+                    if (sm.chunk_cur != CHUNK_NONE && sm.rowpos == DK_CH) { sm.chunk_cur = CHUNK_NONE; sm.rowpos = 0; }
+                    pend = false;
                 }
+                sm.cp_nout = cpn;
             }
             __syncthreads();                                            // B1
             M5_MARK(2);
@@ -586,7 +587,7 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
             if (shrink && nout < (uint32_t)M5_CAP / 4u) shrink--;
             // the next round's windows start flying now; the chunk allocation of this round's rows too
             if (owner) { ss.cur[tid] += ss.n[tid]; issue(); }
-            if (tid == 0) {
+            if (tid == M5_BK) {
                 a_have = (sm.chunk_cur != CHUNK_NONE) ? 1u : 0u;
                 const uint32_t slots = a_have ? (DK_CH - sm.rowpos) : 0u;
                 a_nnew = nout > slots ? (nout - slots + DK_CH - 1) / DK_CH : 0u;
