@@ -34,7 +34,7 @@ CONFIGS = {
 PMAX, FMIN = 0.05, 0.0
 
 
-MERGE_KERNEL_NAME = {"4": "k_merge4", "3": "k_merge3", "2": "k_merge2", "1": "k_merge"}
+MERGE_KERNEL_NAME = {"5": "k_merge5", "4": "k_merge4", "3": "k_merge3", "2": "k_merge2", "1": "k_merge"}
 
 
 def parse():
@@ -334,6 +334,7 @@ def run_ours(args):
                                  q=cfg["q"], alpha=cfg["alpha"])
     torch.cuda.synchronize()
     t_gen = time.time() - t0
+    torch.cuda.empty_cache()                            # the generator's temporaries go back to the device, not to torch's cache
     n = [int(k.numel()) for k in keys]
     n_rec = sum(n)
     kp, cp = [k.data_ptr() for k in keys], [c.data_ptr() for c in cnts]
@@ -423,7 +424,7 @@ def run_ours(args):
         "stage_ms": {"join": stage_avg[0], "merge_kernel": mk, "nf": stage_avg[1], "ttest": stage_avg[2],
                      "bh_filter": stage_avg[3], **({"note": "rank 0; bh_filter = step - other stages (includes the collectives" + (" and the all-reduced NF select)" if args.nf == "full" else ")")}
                                                    if world > 1 else {})},
-        "roofline": {"bound": "hbm", "kernel": MERGE_KERNEL_NAME.get(os.environ.get("DK_MERGE", "4"), "k_merge") + " (k-way merge + recurrence filter, joinCounts.c:72-115; kernel_ms spans the probe launch, its host round trip and the main launch)", "achieved": ach, "peak": peak,
+        "roofline": {"bound": "hbm", "kernel": MERGE_KERNEL_NAME.get(os.environ.get("DK_MERGE", "5" if S <= 32 else "4"), "k_merge") + " (k-way merge + recurrence filter, joinCounts.c:72-115; kernel_ms spans the probe launch, its host round trip and the main launch)", "achieved": ach, "peak": peak,
                      "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)",
                      "alg_bytes_per_launch": b_merge, "kernel_ms": mk,
                      "whole_path": {"alg_bytes": b_all, "achieved": b_all / (ms / 1e3) / 1e9, "frac": b_all / (ms / 1e3) / 1e9 / peak}},

@@ -557,6 +557,16 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     // ---- output capacity: previous need, else a guess; retried with the exact need on overflow
     uint64_t guess = ctx->chunk_hint ? ctx->chunk_hint + ctx->chunk_hint / 16 + 64
                                   : (total / (uint64_t)(min_rec > 1 ? min_rec : 1) / 4) / DK_CH + NPmax / 4 + 64;
+    if (!ctx->chunk_hint) {
+        // a first guess must not eat the device: at most half of what is free now (cached blocks of this context count as
+        // free). Too small a guess costs one more pass with the exact need (the kernel keeps counting past the capacity).
+        size_t mfree = 0, mtot = 0;
+        if (cudaMemGetInfo(&mfree, &mtot) == cudaSuccess) {
+            const size_t per_chunk = (size_t)DK_CH * (8 + 4 * (size_t)S) + 12;
+            const uint64_t fit = (uint64_t)((mfree + ctx->cached_bytes) / 2 / per_chunk);
+            if (guess > fit && fit > 1024) guess = fit;
+        }
+    }
     dk_matrix *m = new dk_matrix();
     m->S = S;
     uint32_t *chunk_part = nullptr, *chunk_seq = nullptr;
