@@ -28,6 +28,8 @@ CONFIGS = {
             S=16, U=1_200_000_000, r=3, a=5, model="two_class", q=0.075, alpha=2.0),
     3: dict(name="cfg3: 48 samples (24v24), U=1.0G union, r=4 a=5", S=48, U=1_000_000_000, r=4, a=5, model="two_class",
             q=0.075, alpha=2.0, strong=True),
+    4: dict(name="cfg4: 200-sample cohort (100v100), U=1.0G union, dumps in pinned host memory streamed in chunks, r=12 a=5",
+            S=200, U=1_000_000_000, r=12, a=5, model="two_class", q=0.075, alpha=2.0, strong=True, streamed=True),
     5: dict(name="cfg5: 16 samples genome-like (90% recurrence-1), heavy tail, U=1.0G, r=3 a=5", S=16, U=1_000_000_000,
             r=3, a=5, model="genome", q=0.0, alpha=1.3),
 }
@@ -46,6 +48,7 @@ def parse():
     ap.add_argument("--config", type=int, default=2, choices=sorted(CONFIGS))
     ap.add_argument("--scale", type=float, default=1.0, help="fraction of the config's U (1.0 = the named workload)")
     ap.add_argument("--nf", default="reference", choices=["reference", "full"])
+    ap.add_argument("--chunk-records", type=int, default=1_000_000_000, help="config 4: records per streamed chunk (12 B each, two chunks in flight)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the full-size invariants and the seeded-sample oracle check")
@@ -294,6 +297,228 @@ def run_reference(args):
                                  "(unbuildable here): its row pass is the oracle port as a process over the same text "
                                  "(oracle/_ref/ttest_text), BH + filter single-threaded as in the reference"},
         "e2e": {"value": val, "unit": "k-mers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+# ---------------------------------------------------------------- config 4: chunk-streamed cohort ---
+def gen_shard_pinned(S, U_total, row_lo, row_hi, *, device, model, q, alpha, rows_per_pass=8_000_000):
+    """this rank's dumps in PINNED host memory, generated pass by pass on the device (never resident there as a whole)"""
+    import torch
+    from dekupl_run_b200 import synth
+    rows = row_hi - row_lo
+    p_present = 0.2 * 0.95 + 0.8 * q if model == "two_class" else 0.2
+    cap = int(rows * p_present * 1.02) + 100_000
+    hk = [torch.empty(cap, dtype=torch.int64).pin_memory() for _ in range(S)]
+    hc = [torch.empty(cap, dtype=torch.int32).pin_memory() for _ in range(S)]
+    fill = [0] * S
+    for a in range(row_lo, row_hi, rows_per_pass):
+        b = min(row_hi, a + rows_per_pass)
+        k, c = synth.gen_shard(S, U_total, a, b, device=device, model=model, q=q, alpha=alpha, chunk=rows_per_pass)
+        for s2 in range(S):
+            m = int(k[s2].numel())
+            if fill[s2] + m > cap:
+                raise RuntimeError("pinned dump buffer too small")
+            hk[s2][fill[s2]:fill[s2] + m].copy_(k[s2], non_blocking=True)
+            hc[s2][fill[s2]:fill[s2] + m].copy_(c[s2], non_blocking=True)
+            fill[s2] += m
+        torch.cuda.synchronize()
+        del k, c
+    return hk, hc, fill
+
+
+def pinned_h2d_peak(dev, nbytes=2 << 30):
+    """GB/s of one large pinned host -> device copy (the denominator of the streamed path's H2D rate)"""
+    import torch
+    h = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    d = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    best = 0.0
+    for _ in range(3):
+        torch.cuda.synchronize()
+        e0.record(); d.copy_(h, non_blocking=True); e1.record()
+        torch.cuda.synchronize()
+        best = max(best, nbytes / (e0.elapsed_time(e1) / 1e3) / 1e9)
+    del h, d
+    return best
+
+
+def run_streamed_config(args, cfg):
+    """--config 4: every rank keeps its k-mer range of the 200 dumps in pinned host memory and walks it in chunks"""
+    import numpy as np
+    import psutil
+    import torch
+    import dekupl_run_b200 as dk
+    from dekupl_run_b200 import synth
+    from dekupl_run_b200.distributed import StreamBackend, nf_text_round, run_streamed
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    else:                                              # the same driver at N = 1: a one-rank group on the CPU backend for the handshakes
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1"); os.environ.setdefault("MASTER_PORT", "29533")
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
+    S = cfg["S"]
+    idxA, idxB = list(range(S // 2)), list(range(S // 2, S))
+    # what the host can pin: 12 B per record, about 0.25 * S records per union row; leave half of the free RAM alone
+    rows_total = int(cfg["U"] * args.scale)
+    bytes_per_row = 12 * S * (0.2 * 0.95 + 0.8 * cfg["q"]) * 1.03
+    budget = psutil.virtual_memory().available * 0.5
+    frac = min(1.0, budget / (rows_total * bytes_per_row))
+    ft = torch.tensor([frac], dtype=torch.float64, device=dev)
+    dist.all_reduce(ft, op=dist.ReduceOp.MIN)
+    frac = float(ft.item())
+    rows_total = int(rows_total * frac)
+    ctx = dk.Context(local)
+    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    t0 = time.time()
+    bounds = [rows_total * g // world for g in range(world + 1)]
+    if world > 1:
+        smp = synth.gen_row_sample(S, rows_total, 250_000, device=dev, model=cfg["model"], q=cfg["q"], alpha=cfg["alpha"])
+        spl = ctx.key_splitters([k.data_ptr() for k in smp], [int(k.numel()) for k in smp], world)
+        bounds = [0] + [int(int(x) // synth.key_stride(rows_total)) for x in spl] + [rows_total]
+        del smp
+    row_lo, row_hi = bounds[rank], bounds[rank + 1]
+    hk, hc, n = gen_shard_pinned(S, rows_total, row_lo, row_hi, device=dev, model=cfg["model"], q=cfg["q"], alpha=cfg["alpha"])
+    torch.cuda.empty_cache()
+    t_gen = time.time() - t0
+    kp, cp = [k.data_ptr() for k in hk], [c.data_ptr() for c in hc]
+    n_rec = sum(n)
+    be = StreamBackend(ctx, dev, args.chunk_records)
+    peak_h2d = pinned_h2d_peak(dev)
+
+    def step():
+        st = run_streamed(be, kp, cp, n, cfg["r"], cfg["a"], idxA, idxB, PMAX, FMIN, device=dev)
+        be.free()
+        return st
+
+    def barrier():
+        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        stats = step()
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    acc = dict(h2d_seconds=0.0, ms_join=0.0, ms_merge=0.0, ms_ttest=0.0, ms_total=0.0, wall_ms_nf_head=0.0, wall_ms_sweep=0.0, wall_ms_bh=0.0)
+    e0.record()
+    for _ in range(args.steps):
+        stats = step()
+        for k in acc:
+            acc[k] += stats["stream"][k]
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    launches = (ctx.launches - l0) // args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    red = torch.tensor([ms], dtype=torch.float64, device=dev)
+    dist.all_reduce(red, op=dist.ReduceOp.MAX)
+    ms = float(red.item())
+    tot = torch.tensor([n_rec, stats["stream"]["h2d_bytes"]], dtype=torch.int64, device=dev)
+    dist.all_reduce(tot)
+    n_rec_all, h2d_all = int(tot[0].item()), int(tot[1].item())
+    for k in acc:
+        acc[k] /= args.steps
+    U, R = stats["U"], stats["R"]
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    b_merge = 12 * n_rec + stats["R_local"] * (8 + 4 * S)
+    ach = b_merge / (acc["ms_merge"] / 1e3) / 1e9 if acc["ms_merge"] else 0.0
+    h2d_rank = 12 * n_rec / (ms / 1e3) / 1e9
+    # parity: U and R of the timed run against the generator's model (the matrix itself is never kept), per rank
+    exp = synth.expected_invariants(S, rows_total, row_lo, row_hi, cfg["r"], cfg["a"], device=dev, model=cfg["model"], q=cfg["q"],
+                                    alpha=cfg["alpha"], chunk=1 << 22)
+    okv = torch.tensor([1 if (exp["U"] == stats["U_local"] and exp["R"] == stats["R_local"] and exp["records"] == n_rec) else 0],
+                       dtype=torch.int64, device=dev)
+    dist.all_reduce(okv)
+    parity = {"full_size": {"what": "U and R per rank against the generator's presence/count model (the matrix is dropped chunk by chunk)",
+                            "gpu": {"U": U, "R": R}, "ranks_equal": int(okv.item()), "equal": bool(int(okv.item()) == world)}}
+    if not args.no_parity:
+        parity.update(streamed_sample_parity(args, cfg, ctx, dev, rank, world, dist, idxA, idxB))
+        if rank == 0:
+            parity["equal"] = bool(parity["full_size"]["equal"] and parity.get("sample_equal"))
+    out = {
+        "metric": "union k-mers/s merged+tested", "value": U / (ms / 1e3), "unit": "k-mers/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "u64 keys / i32 counts / f64 statistics", "data": "synthetic",
+        "config": {"workload": cfg["name"] + (f" (scaled to {frac * args.scale:.3f} of U: what the host can pin)" if frac * args.scale != 1.0 else ""),
+                   "union_kmers": U, "records": n_rec_all, "filtered_rows": R, "survivors": stats["D"], "candidates": stats["n_cand"],
+                   "nf_mode": "reference (head of the table = first chunk of rank 0)", "pmax": PMAX,
+                   "chunk_records": args.chunk_records, "chunks_rank0": stats["stream"]["chunks"], "gen_s": round(t_gen, 1),
+                   "l2": "inputs stream from host memory; every chunk (>= GBs) is far larger than the 126 MB L2"},
+        "gpu_launches": int(launches),
+        "stage_ms": {"join": acc["ms_join"], "merge_kernel": acc["ms_merge"], "ttest": acc["ms_ttest"], "h2d_copy_stream": acc["h2d_seconds"] * 1e3,
+                     "wall_nf_head": acc["wall_ms_nf_head"], "wall_sweep": acc["wall_ms_sweep"], "wall_bh_filter": acc["wall_ms_bh"],
+                     "note": "rank 0; sums over the chunks of one step; copies run beside the kernels on a second stream"},
+        "stream": {"bound": "pcie_h2d", "h2d_bytes_per_step": h2d_all, "h2d_gbs_rank0": h2d_rank, "h2d_gbs_aggregate": h2d_all / (ms / 1e3) / 1e9,
+                   "h2d_peak_gbs": peak_h2d, "frac_of_h2d_peak": h2d_rank / peak_h2d,
+                   "copy_stream_busy_frac": acc["h2d_seconds"] * 1e3 / ms,
+                   "peak_source": "one 2 GiB pinned host->device copy on this GPU, best of 3 (measured in this run)"},
+        "roofline": {"bound": "hbm", "kernel": "k_merge3 (merge-path tree, any S <= 256; k-way merge + recurrence filter, joinCounts.c:72-115)",
+                     "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                     "alg_bytes_per_launch": b_merge / max(1, stats["stream"]["chunks"]), "kernel_ms": acc["ms_merge"],
+                     "note": "the step is bound by the host->device copies, see stream"},
+        "e2e": {"value": U / (ms / 1e3), "unit": "k-mers/s", "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": 64 * world,
+                "note": "this configuration IS the host-buffer path: value and e2e are the same measurement"},
+        "parity_check": parity, "clocks": clocks,
+    }
+    if rank == 0:
+        print(json.dumps(out))
+    dist.destroy_process_group()
+
+
+def streamed_sample_parity(args, cfg, ctx, dev, rank, world, dist, idxA, idxB):
+    """a seeded sample with a planted effect through run_streamed (several chunks per rank) against the oracle on rank 0"""
+    import numpy as np
+    import torch
+    from dekupl_run_b200 import synth
+    from dekupl_run_b200.distributed import StreamBackend, run_streamed
+    S, M64 = cfg["S"], (1 << 64) - 1
+    rows, step = min(args.cpu_rows, 1_500_000), 50_000
+    r0, r1 = rank * rows // world, (rank + 1) * rows // world
+    sk, sc = synth.gen_shard(S, cfg["U"], r0, r1, device=dev, model=cfg["model"], q=cfg["q"], alpha=cfg["alpha"], chunk=1 << 20, **PARITY_EFF)
+    hk, hc = [k.cpu().pin_memory() for k in sk], [c.cpu().pin_memory() for c in sc]
+    del sk, sc
+    n = [int(k.numel()) for k in hk]
+    be = StreamBackend(ctx, dev, max(4096, sum(n) // 3))
+    st = run_streamed(be, [k.data_ptr() for k in hk], [c.data_ptr() for c in hc], n, cfg["r"], cfg["a"], idxA, idxB, PMAX, FMIN,
+                      nf_step=step, device=dev)
+    surv = be.t.export_survivors() if be.t is not None and st["D_local"] else {"key": np.zeros(0, np.uint64), "p_adj": np.zeros(0)}
+    sx = _xor_fold(surv["key"])
+    loc = torch.tensor([sx & 0x7FFFFFFFFFFFFFFF, sx >> 63], dtype=torch.int64, device=dev)
+    allv = [torch.zeros_like(loc) for _ in range(world)]
+    dist.all_gather(allv, loc)
+    adj = torch.tensor([float(np.sum(surv["p_adj"]))], dtype=torch.float64, device=dev)
+    dist.all_reduce(adj)
+    be.free()
+    res = {}
+    if rank == 0:
+        import oracle_lib as orc
+        ck, cc = make_cpu_sample(cfg, rows, **PARITY_EFF)
+        ok, oc, oU = orc.join(ck, cc, cfg["r"], cfg["a"])
+        onf, used, uz = orc.nf_reference(oc, step)
+        nf_used = np.array([float("%f" % v) for v in onf])
+        op, _, _, ofc = orc.ttest_rows(oc, nf_used, idxA, idxB)
+        oadj = orc.bh(op)
+        keep = (oadj <= PMAX) & (np.abs(ofc) >= FMIN)
+        c = dict(U=oU, R=len(ok), D=int(keep.sum()), surv_xor=int(np.bitwise_xor.reduce(ok[keep])) if keep.any() else 0,
+                 surv_adj_sum=float(oadj[keep].sum()))
+        allv = [[int(x) for x in v.tolist()] for v in allv]
+        g = dict(U=st["U"], R=st["R"], D=st["D"], surv_xor=_xor_fold(v[0] | (v[1] << 63) for v in allv), surv_adj_sum=float(adj.item()))
+        nf_err = float(np.max(np.abs(st["nf"] - onf) / onf))
+        adj_err = abs(g["surv_adj_sum"] - c["surv_adj_sum"]) / max(c["surv_adj_sum"], 1e-300)
+        res = {"sample_rows": rows, "planted_effect": PARITY_EFF, "nf_step_rows": step, "cpu": c, "gpu": g, "nf_max_rel_err": nf_err,
+               "surv_adj_sum_rel_err": adj_err,
+               "sample_equal": bool(all(g[k] == c[k] for k in ("U", "R", "D", "surv_xor")) and nf_err <= 1e-9 and adj_err <= 1e-9 and c["D"] > 0)}
+    return res
 
 
 # ----------------------------------------------------------------------------- our arm ---
@@ -744,5 +969,7 @@ if __name__ == "__main__":
             _builtin_print(*args, **kw)
     if a.impl == "reference":
         run_reference(a)
+    elif CONFIGS[a.config].get("streamed"):
+        run_streamed_config(a, CONFIGS[a.config])
     else:
         run_ours(a)

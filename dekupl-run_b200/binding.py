@@ -34,6 +34,12 @@ class PathStats(C.Structure):
                 ("ms_join", C.c_double), ("ms_nf", C.c_double), ("ms_ttest", C.c_double), ("ms_bh", C.c_double)]
 
 
+class StreamStats(C.Structure):
+    _fields_ = [("U", C.c_uint64), ("R", C.c_uint64), ("n_cand", C.c_uint64), ("chunks", C.c_uint64), ("h2d_bytes", C.c_uint64),
+                ("h2d_seconds", C.c_double), ("ms_join", C.c_double), ("ms_merge", C.c_double), ("ms_ttest", C.c_double),
+                ("ms_total", C.c_double)]
+
+
 def load_library():
     """Load the CUDA library. Fails loudly when it has not been built (no fallback)."""
     global _LIB
@@ -85,6 +91,9 @@ def load_library():
         "dk_ttest_export_survivors": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp]),
         "dk_ttest_export_rows": (i32, [vp, vp, vp, vp, vp]),
         "dk_ttest_rows_count": (u64, [vp]), "dk_ttest_free": (None, [vp, vp]),
+        "dk_stream_nf_reference": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, u64, u64, P(dbl), P(u64)]),
+        "dk_stream_path": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, u64, P(dbl), P(i32), i32, P(i32), i32, dbl,
+                                 P(StreamStats), P(vp), P(vp)]),
         "dk_run_path": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, i32, P(i32), i32, P(i32), i32, dbl, dbl, i32,
                               P(PathStats), P(vp), P(vp)]),
     }
@@ -386,6 +395,28 @@ class Context:
         out, info = C.c_void_p(0), (C.c_uint64 * 3)()
         self._chk(self.L.dk_poisson_rows(self.h, m.h, a, len(idxA), b, len(idxB), C.byref(out), info))
         return TtestResult(self, out, m), tuple(int(x) for x in info)
+
+    # ---- chunk-streamed path (host dumps larger than device memory) ----------------
+    def stream_nf_reference(self, key_ptrs, cnt_ptrs, n, min_rec, min_abund, chunk_records, step_rows=0):
+        S, kp, cp, nn = self._tables(key_ptrs, cnt_ptrs, n)
+        nf, info = (C.c_double * S)(), (C.c_uint64 * 4)()
+        self._chk(self.L.dk_stream_nf_reference(self.h, S, kp, cp, nn, min_rec, min_abund, int(chunk_records), int(step_rows), nf, info))
+        return np.array(nf[:]), dict(consumed=int(info[0]), steps=int(info[1]), undefined_zone=int(info[2]), n_pos=int(info[3]))
+
+    def stream_path(self, key_ptrs, cnt_ptrs, n, min_rec, min_abund, chunk_records, nf, idxA, idxB, p_cut):
+        """-> (stats dict, Matrix of the candidate rows or None, TtestResult over them or None)"""
+        S, kp, cp, nn = self._tables(key_ptrs, cnt_ptrs, n)
+        nf = np.ascontiguousarray(nf, dtype=np.float64)
+        a, b = (C.c_int * len(idxA))(*idxA), (C.c_int * len(idxB))(*idxB)
+        st, om, ot = StreamStats(), C.c_void_p(0), C.c_void_p(0)
+        self._chk(self.L.dk_stream_path(self.h, S, kp, cp, nn, min_rec, min_abund, int(chunk_records),
+                                        nf.ctypes.data_as(C.POINTER(C.c_double)), a, len(idxA), b, len(idxB), float(p_cut),
+                                        C.byref(st), C.byref(om), C.byref(ot)))
+        stats = {k: getattr(st, k) for k, _ in StreamStats._fields_}
+        if not om.value:
+            return stats, None, None
+        m = Matrix(self, om)
+        return stats, m, TtestResult(self, ot, m)
 
     # ---- whole path -----------------------------------------------------------
     def run_path(self, key_ptrs, cnt_ptrs, n, device_inputs, min_rec, min_abund, nf_mode, idxA, idxB, pmax, fmin,

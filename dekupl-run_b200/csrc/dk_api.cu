@@ -85,22 +85,34 @@ static int concat_matrices(dk_ctx *ctx, std::vector<dk_matrix *> &parts, dk_matr
     return DK_OK;
 }
 
-static int join_host_pipelined(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
-                               int min_rec, int min_abund, int nslices, dk_matrix **out)
+// cut[s][c] .. cut[s][c+1] = the records of dump s in key-range slice c. Slice edges are k-mers, so equal k-mers of
+// different dumps never straddle a slice.
+typedef std::vector<std::vector<uint64_t>> dk_cuts;
+static void cuts_from_edges(int S, const uint64_t *const *keys, const uint64_t *n, const std::vector<uint64_t> &edges, dk_cuts &cut)
 {
-    // slice edges: quantiles of the longest dump; per dump a binary search on the host arrays
-    int big = 0;
-    for (int s = 1; s < S; s++) if (n[s] > n[big]) big = s;
-    std::vector<std::vector<uint64_t>> cut(S, std::vector<uint64_t>(nslices + 1, 0));
-    for (int s = 0; s < S; s++) cut[s][nslices] = n[s];
-    for (int c = 1; c < nslices; c++) {
-        const uint64_t edge = keys[big][n[big] / nslices * c];
-        for (int s = 0; s < S; s++) {
+    const int ns = (int)edges.size() + 1;
+    cut.assign(S, std::vector<uint64_t>(ns + 1, 0));
+    for (int s = 0; s < S; s++) {
+        cut[s][ns] = n[s];
+        for (int c = 1; c < ns; c++) {
             uint64_t lo = cut[s][c - 1], hi = n[s];
+            const uint64_t edge = edges[c - 1];
             while (lo < hi) { uint64_t mid = (lo + hi) >> 1; if (keys[s][mid] < edge) lo = mid + 1; else hi = mid; }
             cut[s][c] = lo;
         }
     }
+}
+
+struct dk_h2d_stats { double seconds = 0; uint64_t bytes = 0; };
+
+// Walks the slices: while slice c is joined (and handed to on_part) on the compute stream, slice c+1 is copied
+// host->device on a second stream into the other half of a double buffer. on_part owns the matrix it receives.
+// first_only: stop after slice 0 (the head of the table, for the reference-mode NF).
+template <class F>
+static int join_host_slices(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const dk_cuts &cut,
+                            int min_rec, int min_abund, bool first_only, dk_h2d_stats *hs, F on_part)
+{
+    const int nslices = first_only ? 1 : (int)cut[0].size() - 1;
     size_t slab_bytes = 0;
     for (int c = 0; c < nslices; c++) {
         size_t b = 0;
@@ -110,16 +122,16 @@ static int join_host_pipelined(dk_ctx *ctx, int S, const uint64_t *const *keys, 
     unsigned char *slab[2] = {(unsigned char *)dk_dev_alloc(ctx, slab_bytes), (unsigned char *)dk_dev_alloc(ctx, slab_bytes)};
     if (!slab[0] || !slab[1]) { dk_dev_release(ctx, slab[0]); dk_dev_release(ctx, slab[1]); return DK_ERR_NOMEM; }
     cudaStream_t cs = nullptr;
-    cudaEvent_t up[2] = {nullptr, nullptr};
+    cudaEvent_t up[2] = {nullptr, nullptr}, t0[2] = {nullptr, nullptr};
     DK_CUDA(ctx, cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
-    DK_CUDA(ctx, cudaEventCreateWithFlags(&up[0], cudaEventDisableTiming));
-    DK_CUDA(ctx, cudaEventCreateWithFlags(&up[1], cudaEventDisableTiming));
+    for (int i = 0; i < 2; i++) { DK_CUDA(ctx, cudaEventCreate(&up[i])); DK_CUDA(ctx, cudaEventCreate(&t0[i])); }
     std::vector<std::vector<const uint64_t *>> kd(2, std::vector<const uint64_t *>(S));
     std::vector<std::vector<const int32_t *>> cd(2, std::vector<const int32_t *>(S));
     std::vector<uint64_t> nn(S);
     auto enqueue = [&](int c) -> int {
         const int b = c & 1;
         size_t off = 0;
+        DK_CUDA(ctx, cudaEventRecord(t0[b], cs));
         for (int s = 0; s < S; s++) {
             const uint64_t k0 = cut[s][c], k = cut[s][c + 1] - k0;
             kd[b][s] = (const uint64_t *)(slab[b] + off);
@@ -128,27 +140,50 @@ static int join_host_pipelined(dk_ctx *ctx, int S, const uint64_t *const *keys, 
             cd[b][s] = (const int32_t *)(slab[b] + off);
             if (k) DK_CUDA(ctx, cudaMemcpyAsync(slab[b] + off, cnts[s] + k0, k * 4, cudaMemcpyHostToDevice, cs));
             off += dk_round_up(k * 4 + 16, 256);
+            if (hs) hs->bytes += k * 12;
         }
         DK_CUDA(ctx, cudaEventRecord(up[b], cs));
         return DK_OK;
     };
-    std::vector<dk_matrix *> parts;
     int rc = enqueue(0);
     double ms_join = 0, ms_merge = 0;
     for (int c = 0; c < nslices && rc == DK_OK; c++) {
-        // slice c+1 goes into the other buffer: its previous user (join c-1) has returned, i.e. finished on the device
+        // slice c+1 goes into the other buffer: its previous user (slice c-1) has been joined AND consumed by on_part
         if (c + 1 < nslices) rc = enqueue(c + 1);
         if (rc != DK_OK) break;
         if (cudaStreamWaitEvent(ctx->stream, up[c & 1], 0) != cudaSuccess) { rc = dk_fail(ctx, DK_ERR_CUDA, "join: stream wait failed"); break; }
         for (int s = 0; s < S; s++) nn[s] = cut[s][c + 1] - cut[s][c];
         dk_matrix *m = nullptr;
         rc = dk_join_impl(ctx, S, kd[c & 1].data(), cd[c & 1].data(), nn.data(), min_rec, min_abund, 0, &m);
-        if (rc == DK_OK) { parts.push_back(m); ms_join += ctx->stage_ms[0]; ms_merge += ctx->stage_ms[4]; }
+        if (rc == DK_OK) {
+            ms_join += ctx->stage_ms[0]; ms_merge += ctx->stage_ms[4];
+            if (hs) { float ms = 0; if (cudaEventElapsedTime(&ms, t0[c & 1], up[c & 1]) == cudaSuccess) hs->seconds += ms * 1e-3; }
+            rc = on_part(m, c);
+        }
     }
     cudaStreamSynchronize(cs);
     cudaStreamSynchronize(ctx->stream);
-    cudaEventDestroy(up[0]); cudaEventDestroy(up[1]); cudaStreamDestroy(cs);
+    for (int i = 0; i < 2; i++) { cudaEventDestroy(up[i]); cudaEventDestroy(t0[i]); }
+    cudaStreamDestroy(cs);
     dk_dev_release(ctx, slab[0]); dk_dev_release(ctx, slab[1]);
+    ctx->stage_ms[0] = ms_join; ctx->stage_ms[4] = ms_merge;
+    return rc;
+}
+
+static int join_host_pipelined(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                               int min_rec, int min_abund, int nslices, dk_matrix **out)
+{
+    // slice edges: quantiles of the longest dump; per dump a binary search on the host arrays
+    int big = 0;
+    for (int s = 1; s < S; s++) if (n[s] > n[big]) big = s;
+    std::vector<uint64_t> edges;
+    for (int c = 1; c < nslices; c++) edges.push_back(keys[big][n[big] / nslices * c]);
+    dk_cuts cut;
+    cuts_from_edges(S, keys, n, edges, cut);
+    std::vector<dk_matrix *> parts;
+    int rc = join_host_slices(ctx, S, keys, cnts, cut, min_rec, min_abund, false, nullptr,
+                              [&](dk_matrix *m, int) -> int { parts.push_back(m); return DK_OK; });
+    const double ms_join = ctx->stage_ms[0], ms_merge = ctx->stage_ms[4];
     if (rc != DK_OK) { for (auto *p : parts) dk_matrix_release(ctx, p); return rc; }
     rc = concat_matrices(ctx, parts, out);
     ctx->stage_ms[0] = ms_join; ctx->stage_ms[4] = ms_merge;
@@ -196,7 +231,10 @@ extern "C" int dk_key_splitters(dk_ctx *ctx, int S, const uint64_t *const *keys,
     if (!ctx || !keys || !n || (G > 1 && !splitters)) return dk_fail(ctx, DK_ERR_ARG, "key_splitters: NULL argument");
     if (S < 1 || S > DK_MAX_SAMPLES || G < 1 || G > 4096) return dk_fail(ctx, DK_ERR_ARG, "key_splitters: S=%d G=%d out of range", S, G);
     if (G == 1) return DK_OK;
-    const uint32_t MS = 16384;                                   // samples per dump
+    // samples per dump: a boundary is off by at most one sampling stride per dump, i.e. total/MS records in all,
+    // which is G/MS of a shard: 256 samples per shard and dump keep that below 0.4 %
+    uint32_t MS = 256u * (uint32_t)G;
+    MS = MS < 1024u ? 1024u : (MS > 16384u ? 16384u : MS);
     std::vector<std::pair<uint64_t, double>> smp;
     smp.reserve((size_t)S * MS);
     std::vector<uint64_t> h(MS);
@@ -226,6 +264,218 @@ extern "C" int dk_key_splitters(dk_ctx *ctx, int S, const uint64_t *const *keys,
         // shard g starts at this key: records with key < splitters[g-1] belong to shards < g (equal keys never straddle)
         splitters[g - 1] = i < smp.size() ? smp[i].first : DK_SENTINEL;
     }
+    return DK_OK;
+}
+
+__global__ void k_identity_chunks(uint32_t *order, uint64_t *lbase, uint32_t *chunk_rows, uint32_t n_chunks, uint64_t R);
+
+// ---- chunk-streamed path for inputs larger than HBM (BASELINE.json configs[3]) ----------------------------------
+// The dumps stay in (pinned) host memory. The key space is cut into chunks of about chunk_records records (equal-count
+// boundaries, dk_key_splitters); chunk c+1 is copied in on a second stream while chunk c is joined, tested and reduced
+// to its CANDIDATE rows (raw p <= p_cut): k-mer, counts, p, log2FC of those rows are appended to compact device arrays
+// in k-mer order and the chunk's matrix is dropped. BH needs nothing else (dk_bh.cu: rows with p > p_cut can never
+// reach an adjusted p <= p_cut), so the result is an ordinary (matrix, test) pair over the candidate rows that the
+// existing BH / filter / export entry points take — with R_global = all filtered rows of all chunks and ranks.
+__global__ void k_flag_le(const double *p, uint64_t n, double cut, uint32_t *flag)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flag[i] = p[i] <= cut ? 1u : 0u;
+}
+// one warp per flagged row: its key, counts, p and log2FC go to position pos[row] of the compact arrays
+__global__ void k_gather_flagged(const uint64_t *keys, const int32_t *cnts, const uint64_t *lbase, const uint32_t *order,
+                                 uint32_t n_chunks, int S, uint64_t R, const double *p, const double *fc, const uint32_t *pos,
+                                 uint64_t base, uint64_t *okeys, int32_t *ocnts, double *op, double *ofc)
+{
+    const uint64_t row = (uint64_t)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
+    if (row >= R) return;
+    const uint32_t o = pos[row];
+    if (pos[row + 1] == o) return;                               // not flagged (pos = exclusive scan of the flags)
+    uint32_t lo = 0, hi = n_chunks;
+    while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (lbase[mid] <= row) lo = mid; else hi = mid; }
+    const size_t ph = (size_t)order[lo] * DK_CH + (size_t)(row - lbase[lo]);
+    const int lane = threadIdx.x & 31;
+    const uint64_t d = base + o;
+    for (int j = lane; j < S; j += 32) ocnts[d * (size_t)S + j] = cnts[ph * (size_t)S + j];
+    if (lane == 0) { okeys[d] = keys[ph]; op[d] = p[row]; ofc[d] = fc[row]; }
+}
+
+struct dk_cand_acc {
+    uint64_t n = 0, cap = 0;
+    uint64_t *keys = nullptr; int32_t *cnts = nullptr; double *p = nullptr, *fc = nullptr;
+};
+static int acc_reserve(dk_ctx *ctx, dk_cand_acc &a, int S, uint64_t need)
+{
+    if (need + 2 * DK_CH <= a.cap) return DK_OK;
+    uint64_t cap = a.cap ? a.cap : (1u << 16);
+    while (cap < need + 2 * DK_CH) cap *= 2;
+    cap = dk_round_up(cap, DK_CH);
+    uint64_t *k = (uint64_t *)dk_dev_alloc(ctx, 8 * cap);
+    int32_t *c = (int32_t *)dk_dev_alloc(ctx, 4 * cap * S);
+    double *pp = (double *)dk_dev_alloc(ctx, 8 * cap), *f = (double *)dk_dev_alloc(ctx, 8 * cap);
+    if (!k || !c || !pp || !f) { dk_dev_release(ctx, k); dk_dev_release(ctx, c); dk_dev_release(ctx, pp); dk_dev_release(ctx, f); return DK_ERR_NOMEM; }
+    if (a.n) {
+        cudaStream_t st = ctx->stream;
+        DK_CUDA(ctx, cudaMemcpyAsync(k, a.keys, 8 * a.n, cudaMemcpyDeviceToDevice, st));
+        DK_CUDA(ctx, cudaMemcpyAsync(c, a.cnts, 4 * a.n * S, cudaMemcpyDeviceToDevice, st));
+        DK_CUDA(ctx, cudaMemcpyAsync(pp, a.p, 8 * a.n, cudaMemcpyDeviceToDevice, st));
+        DK_CUDA(ctx, cudaMemcpyAsync(f, a.fc, 8 * a.n, cudaMemcpyDeviceToDevice, st));
+        DK_CUDA(ctx, cudaStreamSynchronize(st));
+    }
+    dk_dev_release(ctx, a.keys); dk_dev_release(ctx, a.cnts); dk_dev_release(ctx, a.p); dk_dev_release(ctx, a.fc);
+    a.keys = k; a.cnts = c; a.p = pp; a.fc = f; a.cap = cap;
+    return DK_OK;
+}
+static void acc_drop(dk_ctx *ctx, dk_cand_acc &a)
+{
+    dk_dev_release(ctx, a.keys); dk_dev_release(ctx, a.cnts); dk_dev_release(ctx, a.p); dk_dev_release(ctx, a.fc);
+    a = dk_cand_acc();
+}
+
+static int stream_cuts(dk_ctx *ctx, int S, const uint64_t *const *keys, const uint64_t *n, uint64_t chunk_records, dk_cuts &cut)
+{
+    uint64_t total = 0;
+    for (int s = 0; s < S; s++) total += n[s];
+    if (chunk_records < 4096) chunk_records = 4096;
+    uint64_t G = (total + chunk_records - 1) / chunk_records;
+    if (G < 1) G = 1;
+    if (G > 4096) return dk_fail(ctx, DK_ERR_ARG, "stream: %llu chunks; raise chunk_records", (unsigned long long)G);
+    std::vector<uint64_t> spl(G > 1 ? G - 1 : 0), edges;
+    if (G > 1) DK_TRY(dk_key_splitters(ctx, S, keys, n, 0, (int)G, spl.data()));
+    for (uint64_t e : spl) if (e != DK_SENTINEL && (edges.empty() || e > edges.back())) edges.push_back(e);
+    cuts_from_edges(S, keys, n, edges, cut);
+    return DK_OK;
+}
+
+extern "C" int dk_stream_nf_reference(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                                      int min_rec, int min_abund, uint64_t chunk_records, uint64_t step_rows, double *nf_out,
+                                      uint64_t *info)
+{
+    if (!ctx || !keys || !cnts || !n || !nf_out) return dk_fail(ctx, DK_ERR_ARG, "stream_nf_reference: NULL argument");
+    if (S < 1 || S > DK_MAX_SAMPLES) return dk_fail(ctx, DK_ERR_ARG, "stream: S=%d outside [1,%d]", S, DK_MAX_SAMPLES);
+    dk_cuts cut;
+    DK_TRY(stream_cuts(ctx, S, keys, n, chunk_records, cut));
+    const int nch = (int)cut[0].size() - 1;
+    uint64_t inf[4] = {0, 0, 0, 0};
+    // computeNF.c:138-168 reads the table from its first row until its early stop: a head of the table answers for the
+    // whole table only if the stop fired inside it (rows consumed < rows of the head) and outside the reference's
+    // undefined zone. The head is the first chunk; when the stop does not fire there it is widened to 2, 4, 8 ... chunks.
+    for (int k = 1;; k *= 2) {
+        const int kk = k < nch ? k : nch;
+        dk_cuts head(S, std::vector<uint64_t>(2, 0));
+        for (int s = 0; s < S; s++) head[s][1] = cut[s][kk];
+        uint64_t Rc = 0;
+        int rc = join_host_slices(ctx, S, keys, cnts, head, min_rec, min_abund, true, nullptr, [&](dk_matrix *m, int) -> int {
+            Rc = m->R;
+            int r = m->R ? dk_compute_nf(ctx, m, DK_NF_REFERENCE, step_rows, nf_out, inf)
+                         : dk_fail(ctx, DK_ERR_UNSUPPORTED, "stream_nf_reference: the head of the table has no rows");
+            dk_matrix_release(ctx, m);
+            return r;
+        });
+        if (rc != DK_OK) return rc;
+        if (kk == nch || (inf[0] < Rc && !inf[2])) break;       // the whole table, or the stop fired inside the head
+    }
+    if (info) memcpy(info, inf, sizeof inf);
+    return DK_OK;
+}
+
+extern "C" int dk_stream_path(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                              int min_rec, int min_abund, uint64_t chunk_records, const double *nf, const int *idxA, int nA,
+                              const int *idxB, int nB, double p_cut, dk_stream_stats *stats, dk_matrix **cand_matrix,
+                              dk_ttest **cand_test)
+{
+    if (!ctx || !keys || !cnts || !n || !nf || !idxA || !idxB || !cand_matrix || !cand_test)
+        return dk_fail(ctx, DK_ERR_ARG, "stream_path: NULL argument");
+    *cand_matrix = nullptr; *cand_test = nullptr;
+    if (S < 1 || S > DK_MAX_SAMPLES) return dk_fail(ctx, DK_ERR_ARG, "stream: S=%d outside [1,%d]", S, DK_MAX_SAMPLES);
+    dk_cuts cut;
+    DK_TRY(stream_cuts(ctx, S, keys, n, chunk_records, cut));
+    dk_stream_stats st;
+    memset(&st, 0, sizeof st);
+    st.chunks = cut[0].size() - 1;
+    dk_cand_acc acc;
+    dk_h2d_stats hs;
+    cudaEvent_t e0, e1;
+    DK_CUDA(ctx, cudaEventCreate(&e0)); DK_CUDA(ctx, cudaEventCreate(&e1));
+    cudaEventRecord(e0, ctx->stream);
+    double ms_ttest = 0;
+    int rc = join_host_slices(ctx, S, keys, cnts, cut, min_rec, min_abund, false, &hs, [&](dk_matrix *m, int) -> int {
+        st.U += m->U; st.R += m->R;
+        int r = DK_OK;
+        dk_ttest *t = nullptr;
+        uint32_t *flag = nullptr;
+        if (m->R) {
+            r = dk_ttest_rows(ctx, m, nf, idxA, nA, idxB, nB, &t);
+            if (r == DK_OK) {
+                ms_ttest += ctx->stage_ms[2];
+                const uint64_t R = m->R;
+                flag = (uint32_t *)dk_dev_alloc(ctx, 4 * (R + 2));
+                if (!flag) r = DK_ERR_NOMEM;
+                if (r == DK_OK) {
+                    k_flag_le<<<(unsigned)((R + 255) / 256), 256, 0, ctx->stream>>>(t->p_raw, R, p_cut, flag);
+                    ctx->launches++;
+                    r = dk_scan_excl_u32(ctx, flag, flag, R);                  // flag[R] = candidates of this chunk
+                }
+                uint32_t nc = 0;
+                if (r == DK_OK) {
+                    if (cudaMemcpyAsync(&nc, flag + R, 4, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+                        cudaStreamSynchronize(ctx->stream) != cudaSuccess) r = dk_fail(ctx, DK_ERR_CUDA, "stream: candidate count");
+                }
+                if (r == DK_OK && nc) r = acc_reserve(ctx, acc, S, acc.n + nc);
+                if (r == DK_OK && nc) {
+                    k_gather_flagged<<<(unsigned)((R + 7) / 8), 256, 0, ctx->stream>>>(m->keys, m->cnts, m->lbase, m->order, (uint32_t)m->n_chunks,
+                                                                                       S, R, t->p_raw, t->log2fc, flag, acc.n, acc.keys,
+                                                                                       acc.cnts, acc.p, acc.fc);
+                    ctx->launches++;
+                    if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) r = dk_fail(ctx, DK_ERR_CUDA, "stream: gather");
+                    acc.n += nc;
+                }
+            }
+        }
+        dk_dev_release(ctx, flag);
+        dk_ttest_release(ctx, t);
+        dk_matrix_release(ctx, m);
+        return r;
+    });
+    cudaEventRecord(e1, ctx->stream);
+    cudaStreamSynchronize(ctx->stream);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (rc != DK_OK) { acc_drop(ctx, acc); return rc; }
+    st.n_cand = acc.n; st.h2d_bytes = hs.bytes; st.h2d_seconds = hs.seconds;
+    st.ms_join = ctx->stage_ms[0]; st.ms_merge = ctx->stage_ms[4]; st.ms_ttest = ms_ttest; st.ms_total = ms;
+    ctx->stage_ms[2] = ms_ttest;
+    if (stats) *stats = st;
+    if (acc.n == 0) { acc_drop(ctx, acc); return DK_OK; }        // no candidate anywhere: *cand_matrix and *cand_test stay NULL
+    // the candidate rows as an ordinary dense matrix + test object
+    cudaStream_t cs = ctx->stream;
+    dk_matrix *m = new dk_matrix();
+    m->S = S; m->R = acc.n; m->U = st.U;
+    m->n_chunks = (acc.n + DK_CH - 1) / DK_CH; m->cap_chunks = acc.cap / DK_CH;
+    m->keys = acc.keys; m->cnts = acc.cnts;
+    m->chunk_rows = (uint32_t *)dk_dev_alloc(ctx, 4 * m->cap_chunks);
+    m->order = (uint32_t *)dk_dev_alloc(ctx, 4 * (m->n_chunks + 2));
+    m->lbase = (uint64_t *)dk_dev_alloc(ctx, 8 * (m->n_chunks + 3));
+    dk_ttest *t = new dk_ttest();
+    t->m = m; t->R = acc.n; t->S = S; t->nA = nA; t->nB = nB;
+    t->p_raw = acc.p; t->log2fc = acc.fc;
+    t->nf_dev = (double *)dk_dev_alloc(ctx, sizeof(double) * S);
+    t->idx_dev = (int *)dk_dev_alloc(ctx, sizeof(int) * (nA + nB));
+    t->tie_counts = (uint64_t *)dk_dev_alloc(ctx, 64);
+    if (!m->chunk_rows || !m->order || !m->lbase || !t->nf_dev || !t->idx_dev || !t->tie_counts) {
+        dk_ttest_release(ctx, t); dk_matrix_release(ctx, m);
+        return DK_ERR_NOMEM;
+    }
+    std::vector<int> idx(nA + nB);
+    memcpy(idx.data(), idxA, sizeof(int) * nA);
+    memcpy(idx.data() + nA, idxB, sizeof(int) * nB);
+    k_identity_chunks<<<(unsigned)((m->n_chunks + 255) / 256), 256, 0, cs>>>(m->order, m->lbase, m->chunk_rows, (uint32_t)m->n_chunks, m->R);
+    ctx->launches++;
+    DK_CUDA(ctx, cudaMemcpyAsync(t->nf_dev, nf, sizeof(double) * S, cudaMemcpyHostToDevice, cs));
+    DK_CUDA(ctx, cudaMemcpyAsync(t->idx_dev, idx.data(), sizeof(int) * (nA + nB), cudaMemcpyHostToDevice, cs));
+    DK_CUDA(ctx, cudaMemsetAsync(t->tie_counts, 0, 64, cs));
+    DK_CUDA(ctx, cudaStreamSynchronize(cs));
+    *cand_matrix = m; *cand_test = t;
     return DK_OK;
 }
 

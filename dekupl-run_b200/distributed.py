@@ -150,6 +150,48 @@ def _all_gather_var(x, group=None):
     return torch.cat([o[:s] for o, s in zip(out, sizes)])
 
 
+def _bh_global(backend, R_glob, pmax):
+    """Benjamini-Hochberg over the candidates of all ranks (TtestFilter.c:456-476): leaves the adjusted values on
+    backend.t; returns the global candidate count"""
+    rank, world = dist.get_rank(), dist.get_world_size()
+    cand = backend.candidates(pmax)
+    if world == 1:
+        backend.adjust_global(cand, R_glob)
+        n_cand = int(cand.numel())
+    else:
+        # BH is split by p-value range: rank g owns the candidates in (g*P/world, (g+1)*P/world] (equal values share a
+        # range; under the null p is uniform, so the ranges are balanced). Every rank ROUTES its candidates to their
+        # owners (all-to-all), the owner ranks its range and answers with the adjusted values (all-to-all back): the
+        # traffic and the sort per rank stay those of one shard however many ranks there are.
+        edges = torch.tensor([pmax * g / world for g in range(1, world)], dtype=torch.float64, device=cand.device)
+        send, _ = torch.sort(cand)                                    # ranges become contiguous: edges[g-1] < p <= edges[g] -> g
+        cuts = torch.searchsorted(send, edges, right=True)            # elements <= edges[g]
+        zero = torch.zeros(1, dtype=cuts.dtype, device=cand.device)
+        full = torch.full((1,), send.numel(), dtype=cuts.dtype, device=cand.device)
+        counts = torch.diff(torch.cat([zero, cuts, full])).to(torch.int64)
+        table = [torch.zeros_like(counts) for _ in range(world)]
+        dist.all_gather(table, counts)
+        table = torch.stack(table).cpu()                              # table[src][dst]
+        send_n = [int(x) for x in table[rank].tolist()]
+        recv_n = [int(x) for x in table[:, rank].tolist()]
+        n_below = int(table[:, :rank].sum().item())
+        n_cand = int(table.sum().item())
+        mine = _exchange(send, send_n, recv_n)
+        sp, F = backend.bh_rank_slice(mine, n_below, R_glob)
+        # the running minimum crosses range borders: lower F by the smallest F of all higher ranges
+        first = F[:1] if F.numel() else torch.full((1,), float("inf"), dtype=torch.float64, device=cand.device)
+        mins = [torch.empty_like(first) for _ in range(world)]
+        dist.all_gather(mins, first.contiguous())
+        above = torch.cat(mins[rank + 1:]).min() if rank + 1 < world else None
+        if above is not None and F.numel():
+            F = torch.minimum(F, above)
+        # adjusted value of every routed candidate: adj depends on the value only, so any member of a tie run will do
+        adj_mine = F[torch.searchsorted(sp, mine)] if mine.numel() else mine
+        adj_send = _exchange(adj_mine.contiguous(), recv_n, send_n)   # back to the senders, in `send` order
+        backend.apply_adjusted(send, adj_send)                        # `send` is this rank's candidate list, sorted
+    return n_cand
+
+
 def run_sharded(backend, key_ptrs, cnt_ptrs, n, r, a, idxA, idxB, pmax, fmin, nf_mode="reference", nf_step=0,
                 nf_text_roundtrip=True, device=None):
     """one pass of the whole path on this rank's shard; returns the global stats (identical on every rank)"""
@@ -187,43 +229,81 @@ def run_sharded(backend, key_ptrs, cnt_ptrs, n, r, a, idxA, idxB, pmax, fmin, nf
         nf = backend.nf_result()
     nf_used = nf_text_round(nf) if nf_text_roundtrip else nf
     backend.ttest_rows(nf_used, idxA, idxB)
-    cand = backend.candidates(pmax)
-    if world == 1:
-        backend.adjust_global(cand, R_glob)
-        n_cand = int(cand.numel())
-    else:
-        # BH is split by p-value range: rank g owns the candidates in (g*P/world, (g+1)*P/world] (equal values share a
-        # range; under the null p is uniform, so the ranges are balanced). Every rank ROUTES its candidates to their
-        # owners (all-to-all), the owner ranks its range and answers with the adjusted values (all-to-all back): the
-        # traffic and the sort per rank stay those of one shard however many ranks there are.
-        edges = torch.tensor([pmax * g / world for g in range(1, world)], dtype=torch.float64, device=cand.device)
-        send, _ = torch.sort(cand)                                    # ranges become contiguous: edges[g-1] < p <= edges[g] -> g
-        cuts = torch.searchsorted(send, edges, right=True)            # elements <= edges[g]
-        zero = torch.zeros(1, dtype=cuts.dtype, device=cand.device)
-        full = torch.full((1,), send.numel(), dtype=cuts.dtype, device=cand.device)
-        counts = torch.diff(torch.cat([zero, cuts, full])).to(torch.int64)
-        table = [torch.zeros_like(counts) for _ in range(world)]
-        dist.all_gather(table, counts)
-        table = torch.stack(table).cpu()                              # table[src][dst]
-        send_n = [int(x) for x in table[rank].tolist()]
-        recv_n = [int(x) for x in table[:, rank].tolist()]
-        n_below = int(table[:, :rank].sum().item())
-        n_cand = int(table.sum().item())
-        mine = _exchange(send, send_n, recv_n)
-        sp, F = backend.bh_rank_slice(mine, n_below, R_glob)
-        # the running minimum crosses range borders: lower F by the smallest F of all higher ranges
-        first = F[:1] if F.numel() else torch.full((1,), float("inf"), dtype=torch.float64, device=cand.device)
-        mins = [torch.empty_like(first) for _ in range(world)]
-        dist.all_gather(mins, first.contiguous())
-        above = torch.cat(mins[rank + 1:]).min() if rank + 1 < world else None
-        if above is not None and F.numel():
-            F = torch.minimum(F, above)
-        # adjusted value of every routed candidate: adj depends on the value only, so any member of a tie run will do
-        adj_mine = F[torch.searchsorted(sp, mine)] if mine.numel() else mine
-        adj_send = _exchange(adj_mine.contiguous(), recv_n, send_n)   # back to the senders, in `send` order
-        backend.apply_adjusted(send, adj_send)                        # `send` is this rank's candidate list, sorted
+    n_cand = _bh_global(backend, R_glob, pmax)
     D_loc, ties = backend.filter(pmax, fmin)
     d = torch.tensor([D_loc, ties[0], ties[1], ties[2]], dtype=torch.int64, device=device)
     dist.all_reduce(d)
     return dict(U=U_glob, R=R_glob, D=int(d[0].item()), ties=tuple(int(x) for x in d[1:].tolist()), nf=nf,
                 R_local=R_loc, U_local=U_loc, D_local=D_loc, n_cand=n_cand)
+
+
+
+class StreamBackend(GpuBackend):
+    """per-rank compute of the chunk-streamed path: the dumps of this rank's k-mer range stay in pinned host memory"""
+
+    def __init__(self, ctx, device, chunk_records):
+        super().__init__(ctx, device)
+        self.chunk_records = int(chunk_records)
+        self.stream_stats = None
+
+    # a rank whose chunks held no candidate row has no test object; it still takes part in every collective
+    def candidates(self, p_cut):
+        if self.t is None:
+            return torch.empty(0, dtype=torch.float64, device=self.device)
+        return super().candidates(p_cut)
+
+    def adjust_global(self, all_p, R_global):
+        if self.t is not None:
+            super().adjust_global(all_p, R_global)
+
+    def apply_adjusted(self, sp, F):
+        if self.t is not None:
+            super().apply_adjusted(sp, F)
+
+    def free(self):
+        if self.t is not None:
+            self.t.free()
+        if self.m is not None:
+            self.m.free()
+        self.t = self.m = None
+
+
+def run_streamed(backend, key_ptrs, cnt_ptrs, n, r, a, idxA, idxB, pmax, fmin, nf_step=0, nf_text_roundtrip=True, device=None):
+    """One pass of the chunk-streamed path (BASELINE.json configs[3]) on this rank's shard of HOST dumps. computeNF's
+    factors come from the head of the whole table = the first chunk of rank 0 (computeNF.c:138-168), one broadcast;
+    every rank then walks its chunks (copy in / merge / filter / test / keep the candidate rows) with no collective;
+    R and U are all-reduced and BH runs over the candidates of all ranks exactly as in run_sharded."""
+    import time
+    rank, world = dist.get_rank(), dist.get_world_size()
+    ctx = backend.ctx
+    S = len(key_ptrs)
+    nf = torch.zeros(S, dtype=torch.float64, device=device)
+    ok = torch.ones(1, dtype=torch.int64, device=device)
+    err = None
+    t_0 = time.perf_counter()
+    if rank == 0:
+        try:
+            v, _ = ctx.stream_nf_reference(key_ptrs, cnt_ptrs, n, r, a, backend.chunk_records, nf_step)
+            nf = torch.tensor(v, dtype=torch.float64, device=device)
+        except Exception as e:                                    # every rank must leave together
+            ok[0], err = 0, e
+    dist.broadcast(ok, src=0)
+    if int(ok.item()) == 0:
+        raise RuntimeError(f"reference-mode NF failed on rank 0: {err}")
+    dist.broadcast(nf, src=0)
+    nf = nf.cpu().numpy()
+    nf_used = nf_text_round(nf) if nf_text_roundtrip else nf
+    t_1 = time.perf_counter()
+    st, backend.m, backend.t = ctx.stream_path(key_ptrs, cnt_ptrs, n, r, a, backend.chunk_records, nf_used, idxA, idxB, pmax)
+    t_2 = time.perf_counter()
+    backend.stream_stats = st
+    tot = torch.tensor([st["R"], st["U"]], dtype=torch.int64, device=device)
+    dist.all_reduce(tot)
+    R_glob, U_glob = int(tot[0].item()), int(tot[1].item())
+    n_cand = _bh_global(backend, R_glob, pmax)
+    D_loc, ties = backend.filter(pmax, fmin) if backend.t is not None else (0, (0, 0, 0))
+    d = torch.tensor([D_loc, ties[0], ties[1], ties[2]], dtype=torch.int64, device=device)
+    dist.all_reduce(d)
+    st["wall_ms_nf_head"], st["wall_ms_sweep"], st["wall_ms_bh"] = 1e3 * (t_1 - t_0), 1e3 * (t_2 - t_1), 1e3 * (time.perf_counter() - t_2)
+    return dict(U=U_glob, R=R_glob, D=int(d[0].item()), ties=tuple(int(x) for x in d[1:].tolist()), nf=nf,
+                R_local=st["R"], U_local=st["U"], D_local=D_loc, n_cand=n_cand, stream=st)

@@ -76,8 +76,8 @@ int dk_join_counts_dev(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, cons
  * has no counterpart, its order of output rows — ascending k-mers, joinCounts.c:72-115 — is what sharding by k-mer
  * range preserves). Writes G-1 ascending k-mers: shard g takes the records with splitters[g-1] <= key < splitters[g]
  * (shard 0 from the smallest key, shard G-1 to the largest). The boundaries are chosen so that every shard holds about
- * 1/G of ALL records of all dumps, whatever the distribution of the k-mers (every dump is sampled at 16384 regular
- * positions). Host pointers unless device_inputs. */
+ * 1/G of ALL records of all dumps, whatever the distribution of the k-mers (every dump is sampled at 256 * G regular
+ * positions, at least 1024 and at most 16384: a shard is off by < 0.4 %). Host pointers unless device_inputs. */
 int dk_key_splitters(dk_ctx *ctx, int S, const uint64_t *const *keys, const uint64_t *n, int device_inputs, int G,
                      uint64_t *splitters /* out [G-1] */);
 
@@ -245,6 +245,31 @@ int dk_run_path_masked(dk_ctx *ctx, int S, const uint64_t *const *keys, const in
                        int nf_text_roundtrip, const uint64_t *mask_keys, uint64_t n_mask, int mask_on_device,
                        dk_path_stats *stats, uint64_t *rows_masked /* may be NULL */,
                        dk_matrix **out_matrix /* may be NULL */, dk_ttest **out_test /* may be NULL */);
+
+/* ---- chunk-streamed path: dumps larger than device memory, kept in (pinned) HOST memory -----------------------
+ * The reference streams too: joinCounts holds one record per input (joinCounts.c:43-69), TtestFilter reads the table
+ * row by row (TtestFilter.c:340-444). Here the key space is cut into chunks of about chunk_records records (all dumps
+ * together; equal-count k-mer boundaries); chunk c+1 is copied in on a second stream while chunk c is merged, filtered,
+ * tested and reduced to its candidate rows (raw p <= p_cut), in k-mer order; the chunk's matrix is then dropped.
+ * dk_stream_nf_reference: computeNF's factors (computeNF.c:138-168) from the head of the table = the first chunk; when
+ *   computeNF's early stop does not fire inside it the head is widened to the first 2, 4, 8 ... chunks (the whole table
+ *   at the latest), so the factors always equal computeNF's on the whole table. info as dk_compute_nf.
+ * dk_stream_path: nf = the factors as TtestFilter sees them (after the "%f" round trip). On return *cand_matrix /
+ *   *cand_test hold the candidate rows only (both NULL when there is none) and take the ordinary calls
+ *   dk_ttest_candidates -> dk_ttest_adjust_global(..., R_global = stats->R summed over all ranks) -> dk_ttest_filter ->
+ *   dk_ttest_export_survivors; row indices they report count candidate rows. Free both with their *_free. */
+typedef struct {
+    uint64_t U, R, n_cand, chunks, h2d_bytes;      /* union rows, filtered rows, candidate rows, chunks walked, bytes copied in */
+    double   h2d_seconds;                          /* time the copy stream spent copying (sum over chunks) */
+    double   ms_join, ms_merge, ms_ttest, ms_total;
+} dk_stream_stats;
+int dk_stream_nf_reference(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                           int min_rec, int min_abund, uint64_t chunk_records, uint64_t step_rows /* 0 = 1,000,000 */,
+                           double *nf_out, uint64_t *info /* may be NULL */);
+int dk_stream_path(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                   int min_rec, int min_abund, uint64_t chunk_records, const double *nf,
+                   const int *idxA, int nA, const int *idxB, int nB, double p_cut,
+                   dk_stream_stats *stats /* may be NULL */, dk_matrix **cand_matrix, dk_ttest **cand_test);
 
 #ifdef __cplusplus
 }

@@ -609,13 +609,14 @@ def test_key_splitters_balance_records_on_clustered_kmers(ctx, G, on_device):
     else:
         spl = ctx.key_splitters([k.ctypes.data for k in keys], n, G, device_inputs=False)
     assert len(spl) == G - 1 and np.all(np.diff(spl.astype(np.float64)) >= 0)
-    edges = np.concatenate([[0], spl, [np.iinfo(np.uint64).max]]).astype(np.uint64)
+    UMAX = np.array([np.iinfo(np.uint64).max], np.uint64)
+    edges = np.concatenate([np.zeros(1, np.uint64), spl.astype(np.uint64), UMAX])
     per = np.array([sum(int(np.searchsorted(k, edges[g + 1]) - np.searchsorted(k, edges[g])) for k in keys) for g in range(G)], float)
     per[-1] += sum(int((k == np.iinfo(np.uint64).max).sum()) for k in keys)
     assert per.sum() == sum(n)
     assert np.max(np.abs(per / per.sum() * G - 1.0)) < 0.03, per / per.sum()
     naive = np.linspace(float(allk.min()), float(allk.max()), G + 1)[1:-1].astype(np.uint64)
-    ne = np.concatenate([[0], naive, [np.iinfo(np.uint64).max]]).astype(np.uint64)
+    ne = np.concatenate([np.zeros(1, np.uint64), naive, UMAX])
     nper = np.array([sum(int(np.searchsorted(k, ne[g + 1]) - np.searchsorted(k, ne[g])) for k in keys) for g in range(G)], float)
     assert np.max(nper) / np.mean(nper) > 1.5                       # the key-space split really is unbalanced here
     parts_k, parts_c = [], []
@@ -630,3 +631,57 @@ def test_key_splitters_balance_records_on_clustered_kmers(ctx, G, on_device):
     ok, oc, _ = orc.join(keys, cnts, 2, 5)
     np.testing.assert_array_equal(np.concatenate(parts_k), ok)
     np.testing.assert_array_equal(np.concatenate(parts_c), oc)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("S,nA,chunk", [(8, 4, 60_000), (20, 10, 250_000), (12, 6, 10 ** 9)])
+def test_chunk_streamed_path_equals_the_oracle(ctx, S, nA, chunk):
+    """dk_stream_nf_reference + dk_stream_path (host dumps walked in key-range chunks, only candidate rows kept) + the
+    ordinary BH / filter / export calls == oracle on the whole input: U, R, NFs, survivor k-mers, adjusted p, means,
+    log2FC, normalised counts (joinCounts.c:72-115, computeNF.c:138-168, TtestFilter.c:373-497)."""
+    from common import plant_effect
+    rng = np.random.default_rng(S * 13 + nA)
+    r, a, pmax, step = 2, 3, 0.05, 5000
+    idxA, idxB = list(range(nA)), list(range(nA, S))
+    keys, cnts = random_dumps(rng, S, 120_000, 62, 0.2, 50, p_core=0.35)
+    cnts = plant_effect(rng, keys, cnts, set(idxB), frac=0.04, factor=25)
+    kp, cp, n = [k.ctypes.data for k in keys], [c.ctypes.data for c in cnts], [len(k) for k in keys]
+    ok, oc, oU = orc.join(keys, cnts, r, a)
+    onf, used, uz = orc.nf_reference(oc, step)
+    assert not uz
+    # whether computeNF's early stop fires inside the first chunk, inside a widened head, or never (whole table): same factors
+    nf, info = ctx.stream_nf_reference(kp, cp, n, r, a, chunk, step)
+    np.testing.assert_allclose(nf, onf, rtol=RTOL)
+    assert info["consumed"] == used or (used == len(oc) and info["consumed"] >= used)
+    nf_used = np.array([float("%f" % v) for v in onf])
+    st, m, t = ctx.stream_path(kp, cp, n, r, a, chunk, nf_used, idxA, idxB, pmax)
+    total = sum(n)
+    assert st["chunks"] == max(1, -(-total // max(chunk, 4096))) or st["chunks"] >= 1
+    assert (st["U"], st["R"]) == (oU, len(ok)) and st["h2d_bytes"] == 12 * total
+    op, omA, omB, ofc = orc.ttest_rows(oc, nf_used, idxA, idxB)
+    cand = np.nonzero(op <= pmax)[0]
+    near_p = np.abs(op - pmax) <= 1e-9 * pmax
+    assert abs(st["n_cand"] - len(cand)) <= int(near_p.sum()) and st["n_cand"] > 50
+    gk, gc = m.export()
+    if not near_p.any():
+        np.testing.assert_array_equal(gk, ok[cand])            # candidate rows in k-mer order, counts intact
+        np.testing.assert_array_equal(gc, oc[cand])
+    nc, ptr = t.candidates(pmax)
+    t.adjust_global(ptr, nc, st["R"])                          # R_global = ALL filtered rows, not the candidate count
+    D = t.filter(pmax, 0.0)
+    sv = t.export_survivors()
+    oadj = orc.bh(op)
+    near = np.abs(oadj - pmax) <= 1e-9 * pmax
+    keep = np.nonzero((oadj <= pmax) & ~near)[0]
+    assert D > 20 and set(ok[keep].tolist()) <= set(sv["key"].tolist()) <= set(ok[np.nonzero((oadj <= pmax) | near)[0]].tolist())
+    rows = np.searchsorted(ok, sv["key"])
+    assert np.all(np.diff(rows) > 0)                           # survivors come out in the reference's order
+    np.testing.assert_allclose(sv["p_adj"], oadj[rows], rtol=RTOL, atol=1e-300)
+    np.testing.assert_allclose(sv["meanA"], omA[rows], rtol=RTOL)
+    np.testing.assert_allclose(sv["meanB"], omB[rows], rtol=RTOL)
+    np.testing.assert_allclose(sv["log2fc"], ofc[rows], rtol=RTOL, atol=1e-12)
+    np.testing.assert_allclose(sv["norm"], oc[rows] / nf_used, rtol=RTOL)
+    t.free(); m.free()
+    # a first chunk too small for computeNF's early stop: the head of the table is widened until the stop fires
+    nf2, info2 = ctx.stream_nf_reference(kp, cp, n, r, a, 8000, step)
+    np.testing.assert_allclose(nf2, onf, rtol=RTOL)
