@@ -91,7 +91,9 @@ def load_library():
         "dk_ttest_export_survivors": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp]),
         "dk_ttest_export_rows": (i32, [vp, vp, vp, vp, vp]),
         "dk_ttest_rows_count": (u64, [vp]), "dk_ttest_free": (None, [vp, vp]),
-        "dk_stream_nf_reference": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, u64, u64, P(dbl), P(u64)]),
+        "dk_stream_nf_reference": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, u64, u64, i32, P(dbl), P(u64), P(i32)]),
+        "dk_stream_positive_rows": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, u64, P(StreamStats), P(vp)]),
+        "dk_nf_reference_sparse": (i32, [vp, i32, u64, vp, vp, u64, u64, P(dbl), P(u64)]),
         "dk_stream_path": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, u64, P(dbl), P(i32), i32, P(i32), i32, dbl,
                                  P(StreamStats), P(vp), P(vp)]),
         "dk_run_path": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, i32, P(i32), i32, P(i32), i32, dbl, dbl, i32,
@@ -397,10 +399,32 @@ class Context:
         return TtestResult(self, out, m), tuple(int(x) for x in info)
 
     # ---- chunk-streamed path (host dumps larger than device memory) ----------------
-    def stream_nf_reference(self, key_ptrs, cnt_ptrs, n, min_rec, min_abund, chunk_records, step_rows=0):
+    def stream_nf_reference(self, key_ptrs, cnt_ptrs, n, min_rec, min_abund, chunk_records, step_rows=0, widen=True):
+        """computeNF's factors from the head of the table; info["stop_fired"] says whether its early stop fired there"""
         S, kp, cp, nn = self._tables(key_ptrs, cnt_ptrs, n)
+        nf, info, fired = (C.c_double * S)(), (C.c_uint64 * 4)(), C.c_int(0)
+        self._chk(self.L.dk_stream_nf_reference(self.h, S, kp, cp, nn, min_rec, min_abund, int(chunk_records), int(step_rows),
+                                                int(widen), nf, info, C.byref(fired)))
+        return np.array(nf[:]), dict(consumed=int(info[0]), steps=int(info[1]), undefined_zone=int(info[2]), n_pos=int(info[3]),
+                                     stop_fired=bool(fired.value))
+
+    def stream_positive_rows(self, key_ptrs, cnt_ptrs, n, min_rec, min_abund, chunk_records):
+        """-> (stats, row numbers uint64[n_pos], counts int32[n_pos][S]) of the all-positive rows of this rank's table"""
+        S, kp, cp, nn = self._tables(key_ptrs, cnt_ptrs, n)
+        st, om = StreamStats(), C.c_void_p(0)
+        self._chk(self.L.dk_stream_positive_rows(self.h, S, kp, cp, nn, min_rec, min_abund, int(chunk_records), C.byref(st), C.byref(om)))
+        stats = {k: getattr(st, k) for k, _ in StreamStats._fields_}
+        m = Matrix(self, om)
+        rows, cnts = m.export() if m.rows else (np.zeros(0, np.uint64), np.zeros((0, S), np.int32))
+        m.free()
+        return stats, rows, cnts
+
+    def nf_reference_sparse(self, row_idx, cnts, R_total, step_rows=0):
+        row_idx = np.ascontiguousarray(row_idx, dtype=np.uint64)
+        cnts = np.ascontiguousarray(cnts, dtype=np.int32)
+        S = cnts.shape[1]
         nf, info = (C.c_double * S)(), (C.c_uint64 * 4)()
-        self._chk(self.L.dk_stream_nf_reference(self.h, S, kp, cp, nn, min_rec, min_abund, int(chunk_records), int(step_rows), nf, info))
+        self._chk(self.L.dk_nf_reference_sparse(self.h, S, len(row_idx), _np_ptr(row_idx), _np_ptr(cnts), int(R_total), int(step_rows), nf, info))
         return np.array(nf[:]), dict(consumed=int(info[0]), steps=int(info[1]), undefined_zone=int(info[2]), n_pos=int(info[3]))
 
     def stream_path(self, key_ptrs, cnt_ptrs, n, min_rec, min_abund, chunk_records, nf, idxA, idxB, p_cut):

@@ -284,7 +284,7 @@ __global__ void k_flag_le(const double *p, uint64_t n, double cut, uint32_t *fla
 // one warp per flagged row: its key, counts, p and log2FC go to position pos[row] of the compact arrays
 __global__ void k_gather_flagged(const uint64_t *keys, const int32_t *cnts, const uint64_t *lbase, const uint32_t *order,
                                  uint32_t n_chunks, int S, uint64_t R, const double *p, const double *fc, const uint32_t *pos,
-                                 uint64_t base, uint64_t *okeys, int32_t *ocnts, double *op, double *ofc)
+                                 uint64_t base, uint64_t *okeys, int32_t *ocnts, double *op, double *ofc, uint64_t rownum_base)
 {
     const uint64_t row = (uint64_t)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
     if (row >= R) return;
@@ -296,7 +296,25 @@ __global__ void k_gather_flagged(const uint64_t *keys, const int32_t *cnts, cons
     const int lane = threadIdx.x & 31;
     const uint64_t d = base + o;
     for (int j = lane; j < S; j += 32) ocnts[d * (size_t)S + j] = cnts[ph * (size_t)S + j];
-    if (lane == 0) { okeys[d] = keys[ph]; op[d] = p[row]; ofc[d] = fc[row]; }
+    if (lane == 0) {
+        okeys[d] = p ? keys[ph] : rownum_base + row;             // collection sweep: the row's number instead of its k-mer
+        if (p) { op[d] = p[row]; ofc[d] = fc[row]; }
+    }
+}
+// flag[row] = 1 iff every count of the row is > 0 (the rows computeNF uses, computeNF.c:122-130); one warp per row
+__global__ void k_flag_allpos(const int32_t *cnts, const uint64_t *lbase, const uint32_t *order, uint32_t n_chunks, int S,
+                              uint64_t R, uint32_t *flag)
+{
+    const uint64_t row = (uint64_t)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
+    if (row >= R) return;
+    uint32_t lo = 0, hi = n_chunks;
+    while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (lbase[mid] <= row) lo = mid; else hi = mid; }
+    const size_t ph = (size_t)order[lo] * DK_CH + (size_t)(row - lbase[lo]);
+    const int lane = threadIdx.x & 31;
+    bool pos = true;
+    for (int j = lane; j < S; j += 32) pos = pos && cnts[ph * (size_t)S + j] > 0;
+    pos = __all_sync(0xffffffffu, pos);
+    if (lane == 0) flag[row] = pos ? 1u : 0u;
 }
 
 struct dk_cand_acc {
@@ -347,8 +365,8 @@ static int stream_cuts(dk_ctx *ctx, int S, const uint64_t *const *keys, const ui
 }
 
 extern "C" int dk_stream_nf_reference(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
-                                      int min_rec, int min_abund, uint64_t chunk_records, uint64_t step_rows, double *nf_out,
-                                      uint64_t *info)
+                                      int min_rec, int min_abund, uint64_t chunk_records, uint64_t step_rows, int widen,
+                                      double *nf_out, uint64_t *info, int *stop_fired)
 {
     if (!ctx || !keys || !cnts || !n || !nf_out) return dk_fail(ctx, DK_ERR_ARG, "stream_nf_reference: NULL argument");
     if (S < 1 || S > DK_MAX_SAMPLES) return dk_fail(ctx, DK_ERR_ARG, "stream: S=%d outside [1,%d]", S, DK_MAX_SAMPLES);
@@ -356,9 +374,11 @@ extern "C" int dk_stream_nf_reference(dk_ctx *ctx, int S, const uint64_t *const 
     DK_TRY(stream_cuts(ctx, S, keys, n, chunk_records, cut));
     const int nch = (int)cut[0].size() - 1;
     uint64_t inf[4] = {0, 0, 0, 0};
+    bool fired = false;
     // computeNF.c:138-168 reads the table from its first row until its early stop: a head of the table answers for the
     // whole table only if the stop fired inside it (rows consumed < rows of the head) and outside the reference's
-    // undefined zone. The head is the first chunk; when the stop does not fire there it is widened to 2, 4, 8 ... chunks.
+    // undefined zone. The head is the first chunk; with `widen` it grows to 2, 4, 8 ... chunks until the stop fires or
+    // these dumps are exhausted (exact when they ARE the whole table; a rank of a sharded run must not widen).
     for (int k = 1;; k *= 2) {
         const int kk = k < nch ? k : nch;
         dk_cuts head(S, std::vector<uint64_t>(2, 0));
@@ -372,9 +392,77 @@ extern "C" int dk_stream_nf_reference(dk_ctx *ctx, int S, const uint64_t *const 
             return r;
         });
         if (rc != DK_OK) return rc;
-        if (kk == nch || (inf[0] < Rc && !inf[2])) break;       // the whole table, or the stop fired inside the head
+        fired = inf[0] < Rc && !inf[2];
+        if (fired || kk == nch || !widen) break;
     }
     if (info) memcpy(info, inf, sizeof inf);
+    if (stop_fired) *stop_fired = fired ? 1 : 0;
+    return DK_OK;
+}
+
+// first sweep of the two-sweep form: the rows computeNF can use (every count > 0), with their row numbers
+extern "C" int dk_stream_positive_rows(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                                       int min_rec, int min_abund, uint64_t chunk_records, dk_stream_stats *stats, dk_matrix **pos_rows)
+{
+    if (!ctx || !keys || !cnts || !n || !pos_rows) return dk_fail(ctx, DK_ERR_ARG, "stream_positive_rows: NULL argument");
+    *pos_rows = nullptr;
+    if (S < 1 || S > DK_MAX_SAMPLES) return dk_fail(ctx, DK_ERR_ARG, "stream: S=%d outside [1,%d]", S, DK_MAX_SAMPLES);
+    dk_cuts cut;
+    DK_TRY(stream_cuts(ctx, S, keys, n, chunk_records, cut));
+    dk_stream_stats st;
+    memset(&st, 0, sizeof st);
+    st.chunks = cut[0].size() - 1;
+    dk_cand_acc acc;
+    dk_h2d_stats hs;
+    int rc = join_host_slices(ctx, S, keys, cnts, cut, min_rec, min_abund, false, &hs, [&](dk_matrix *m, int) -> int {
+        int r = DK_OK;
+        uint32_t *flag = nullptr;
+        const uint64_t R = m->R;
+        if (R) {
+            flag = (uint32_t *)dk_dev_alloc(ctx, 4 * (R + 2));
+            if (!flag) r = DK_ERR_NOMEM;
+            if (r == DK_OK) {
+                k_flag_allpos<<<(unsigned)((R + 7) / 8), 256, 0, ctx->stream>>>(m->cnts, m->lbase, m->order, (uint32_t)m->n_chunks, S, R, flag);
+                ctx->launches++;
+                r = dk_scan_excl_u32(ctx, flag, flag, R);
+            }
+            uint32_t nc = 0;
+            if (r == DK_OK && (cudaMemcpyAsync(&nc, flag + R, 4, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+                               cudaStreamSynchronize(ctx->stream) != cudaSuccess)) r = dk_fail(ctx, DK_ERR_CUDA, "stream: positive count");
+            if (r == DK_OK && nc) r = acc_reserve(ctx, acc, S, acc.n + nc);
+            if (r == DK_OK && nc) {
+                k_gather_flagged<<<(unsigned)((R + 7) / 8), 256, 0, ctx->stream>>>(m->keys, m->cnts, m->lbase, m->order, (uint32_t)m->n_chunks,
+                                                                                   S, R, nullptr, nullptr, flag, acc.n, acc.keys, acc.cnts,
+                                                                                   acc.p, acc.fc, st.R);
+                ctx->launches++;
+                if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) r = dk_fail(ctx, DK_ERR_CUDA, "stream: gather");
+                acc.n += nc;
+            }
+        }
+        st.U += m->U; st.R += R;
+        dk_dev_release(ctx, flag);
+        dk_matrix_release(ctx, m);
+        return r;
+    });
+    if (rc != DK_OK) { acc_drop(ctx, acc); return rc; }
+    st.n_cand = acc.n; st.h2d_bytes = hs.bytes; st.h2d_seconds = hs.seconds;
+    st.ms_join = ctx->stage_ms[0]; st.ms_merge = ctx->stage_ms[4];
+    if (stats) *stats = st;
+    // a dense matrix whose KEY column holds the row numbers (in this rank's filtered table) of the all-positive rows
+    dk_matrix *m = new dk_matrix();
+    m->S = S; m->R = acc.n; m->U = st.U;
+    if (acc.n == 0) DK_TRY(acc_reserve(ctx, acc, S, 1));
+    m->n_chunks = (acc.n + DK_CH - 1) / DK_CH; m->cap_chunks = acc.cap / DK_CH;
+    m->keys = acc.keys; m->cnts = acc.cnts;
+    dk_dev_release(ctx, acc.p); dk_dev_release(ctx, acc.fc);
+    m->chunk_rows = (uint32_t *)dk_dev_alloc(ctx, 4 * m->cap_chunks);
+    m->order = (uint32_t *)dk_dev_alloc(ctx, 4 * (m->n_chunks + 2));
+    m->lbase = (uint64_t *)dk_dev_alloc(ctx, 8 * (m->n_chunks + 3));
+    if (!m->chunk_rows || !m->order || !m->lbase) { dk_matrix_release(ctx, m); return DK_ERR_NOMEM; }
+    k_identity_chunks<<<(unsigned)((m->n_chunks + 256) / 256), 256, 0, ctx->stream>>>(m->order, m->lbase, m->chunk_rows, (uint32_t)m->n_chunks, m->R);
+    ctx->launches++;
+    DK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *pos_rows = m;
     return DK_OK;
 }
 
@@ -424,7 +512,7 @@ extern "C" int dk_stream_path(dk_ctx *ctx, int S, const uint64_t *const *keys, c
                 if (r == DK_OK && nc) {
                     k_gather_flagged<<<(unsigned)((R + 7) / 8), 256, 0, ctx->stream>>>(m->keys, m->cnts, m->lbase, m->order, (uint32_t)m->n_chunks,
                                                                                        S, R, t->p_raw, t->log2fc, flag, acc.n, acc.keys,
-                                                                                       acc.cnts, acc.p, acc.fc);
+                                                                                       acc.cnts, acc.p, acc.fc, 0);
                     ctx->launches++;
                     if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) r = dk_fail(ctx, DK_ERR_CUDA, "stream: gather");
                     acc.n += nc;

@@ -7,6 +7,7 @@
 //  radix select: exact element [size/2] of the ascending order (computeNF.c:38-47),
 //                8 rounds of 8 bits: k_nf_hist (shared-memory histograms) + k_nf_pick.
 //  DK_NF_REFERENCE replays the step / early-stop logic of computeNF.c:138-168.
+#include <algorithm>
 #include "dk_common.cuh"
 
 __device__ __forceinline__ uint64_t f64_image(double v)
@@ -162,11 +163,16 @@ static int nf_grow(dk_ctx *ctx, NfWork &w, int S, uint64_t need, uint64_t used)
     return DK_OK;
 }
 
-extern "C" int dk_compute_nf(dk_ctx *ctx, const dk_matrix *m, int mode, uint64_t step_rows, double *nf_out, uint64_t *info)
+// ridx != NULL: m holds ONLY the all-positive rows of a table of R_virtual rows and ridx[i] (ascending, host) is the
+// row number of m's row i in that table. Rows that are not all-positive never enter computeNF (their logmean is not
+// finite, computeNF.c:122-130), so walking the table in steps of `step` rows and walking these rows by row number is
+// the same computation (dk_nf_reference_sparse).
+static int compute_nf_impl(dk_ctx *ctx, const dk_matrix *m, int mode, uint64_t step_rows, double *nf_out, uint64_t *info,
+                           const uint64_t *ridx, uint64_t R_virtual)
 {
     if (!ctx || !m || !nf_out) return dk_fail(ctx, DK_ERR_ARG, "compute_nf: NULL argument");
     const int S = m->S;
-    const uint64_t R = m->R;
+    const uint64_t R = ridx ? R_virtual : m->R;
     cudaStream_t st = ctx->stream;
     uint64_t step = step_rows ? step_rows : 1000000;                  // computeNF.c:52
     DK_CUDA(ctx, cudaEventRecord(ctx->ev[0], st));
@@ -184,6 +190,10 @@ extern "C" int dk_compute_nf(dk_ctx *ctx, const dk_matrix *m, int mode, uint64_t
     int undefined_zone = 0, rc = DK_OK;
     const uint32_t nch = (uint32_t)m->n_chunks;
     auto ratios = [&](uint64_t r0, uint64_t r1) -> int {
+        if (ridx) {                                                   // table rows [r0, r1) -> rows of the compact matrix
+            r0 = (uint64_t)(std::lower_bound(ridx, ridx + m->R, r0) - ridx);
+            r1 = (uint64_t)(std::lower_bound(ridx, ridx + m->R, r1) - ridx);
+        }
         if (r1 <= r0) return DK_OK;
         DK_TRY(nf_grow(ctx, w, S, npos_h + (r1 - r0), npos_h));
         k_nf_ratios<<<(unsigned)((r1 - r0 + 127) / 128), 128, 0, st>>>(m->cnts, m->lbase, m->order, nch, S, r0, r1, w.vals,
@@ -254,6 +264,27 @@ done:
     ctx->stage_ms[1] = ms;
     dk_dev_release(ctx, w.vals);
     dk_dev_release(ctx, small);
+    return rc;
+}
+
+extern "C" int dk_compute_nf(dk_ctx *ctx, const dk_matrix *m, int mode, uint64_t step_rows, double *nf_out, uint64_t *info)
+{
+    return compute_nf_impl(ctx, m, mode, step_rows, nf_out, info, nullptr, 0);
+}
+
+void dk_matrix_release(dk_ctx *ctx, dk_matrix *m);
+extern "C" int dk_nf_reference_sparse(dk_ctx *ctx, int S, uint64_t n_pos, const uint64_t *row_idx, const int32_t *cnts,
+                                      uint64_t R_total, uint64_t step_rows, double *nf_out, uint64_t *info)
+{
+    if (!ctx || !nf_out || (n_pos && (!row_idx || !cnts))) return dk_fail(ctx, DK_ERR_ARG, "nf_reference_sparse: NULL argument");
+    if (n_pos == 0) return dk_fail(ctx, DK_ERR_UNSUPPORTED, "compute_nf: no row has all counts > 0 (reference reads a NULL vector here)");
+    for (uint64_t i = 0; i < n_pos; i++)
+        if (row_idx[i] >= R_total || (i && row_idx[i] <= row_idx[i - 1]))
+            return dk_fail(ctx, DK_ERR_ARG, "nf_reference_sparse: row numbers must ascend and lie below R_total");
+    dk_matrix *m = nullptr;
+    DK_TRY(dk_matrix_from_host(ctx, S, n_pos, nullptr, cnts, &m));
+    const int rc = compute_nf_impl(ctx, m, DK_NF_REFERENCE, step_rows, nf_out, info, row_idx, R_total);
+    dk_matrix_release(ctx, m);
     return rc;
 }
 

@@ -268,28 +268,57 @@ class StreamBackend(GpuBackend):
         self.t = self.m = None
 
 
-def run_streamed(backend, key_ptrs, cnt_ptrs, n, r, a, idxA, idxB, pmax, fmin, nf_step=0, nf_text_roundtrip=True, device=None):
-    """One pass of the chunk-streamed path (BASELINE.json configs[3]) on this rank's shard of HOST dumps. computeNF's
-    factors come from the head of the whole table = the first chunk of rank 0 (computeNF.c:138-168), one broadcast;
-    every rank then walks its chunks (copy in / merge / filter / test / keep the candidate rows) with no collective;
-    R and U are all-reduced and BH runs over the candidates of all ranks exactly as in run_sharded."""
+def run_streamed(backend, key_ptrs, cnt_ptrs, n, r, a, idxA, idxB, pmax, fmin, nf_step=0, nf_text_roundtrip=True, device=None,
+                 nf_from="auto"):
+    """One pass of the chunk-streamed path (BASELINE.json configs[3]) on this rank's shard of HOST dumps.
+    computeNF's factors (computeNF.c:138-168): nf_from="auto" lets rank 0 try the head of the table (its first chunk);
+    if computeNF's early stop fires there, that is the answer (one broadcast). Otherwise — and always with
+    nf_from="sweep" — every rank makes a first sweep that keeps only the all-positive rows (the only rows computeNF
+    uses), they are gathered on rank 0 with global row numbers and the step / early-stop logic is replayed on them:
+    exact for any number of ranks, and the same two passes over the table the reference pipeline makes.
+    Then every rank walks its chunks again (copy in / merge / filter / test / keep the candidate rows) with no
+    collective; R and U are all-reduced and BH runs over the candidates of all ranks exactly as in run_sharded."""
     import time
     rank, world = dist.get_rank(), dist.get_world_size()
     ctx = backend.ctx
     S = len(key_ptrs)
     nf = torch.zeros(S, dtype=torch.float64, device=device)
-    ok = torch.ones(1, dtype=torch.int64, device=device)
+    flag = torch.zeros(2, dtype=torch.int64, device=device)      # [0] = head answered, [1] = error on rank 0
     err = None
     t_0 = time.perf_counter()
-    if rank == 0:
-        try:
-            v, _ = ctx.stream_nf_reference(key_ptrs, cnt_ptrs, n, r, a, backend.chunk_records, nf_step)
-            nf = torch.tensor(v, dtype=torch.float64, device=device)
-        except Exception as e:                                    # every rank must leave together
-            ok[0], err = 0, e
-    dist.broadcast(ok, src=0)
-    if int(ok.item()) == 0:
-        raise RuntimeError(f"reference-mode NF failed on rank 0: {err}")
+    if nf_from == "auto":
+        if rank == 0:
+            try:
+                v, info = ctx.stream_nf_reference(key_ptrs, cnt_ptrs, n, r, a, backend.chunk_records, nf_step, widen=(world == 1))
+                if info["stop_fired"] or world == 1:
+                    nf = torch.tensor(v, dtype=torch.float64, device=device)
+                    flag[0] = 1
+            except Exception as e:                                # every rank must leave together
+                flag[1], err = 1, e
+        dist.broadcast(flag, src=0)
+        if int(flag[1].item()):
+            raise RuntimeError(f"reference-mode NF failed on rank 0: {err}")
+    nf_how = "head"
+    if not int(flag[0].item()):
+        nf_how = "sweep"
+        st1, prow, pcnt = ctx.stream_positive_rows(key_ptrs, cnt_ptrs, n, r, a, backend.chunk_records)
+        rl = torch.tensor([st1["R"]], dtype=torch.int64, device=device)
+        rs = [torch.zeros_like(rl) for _ in range(world)]
+        dist.all_gather(rs, rl)
+        rs = [int(x.item()) for x in rs]
+        grow = torch.from_numpy((prow.astype(np.int64) + sum(rs[:rank]))).to(device)
+        gcnt = torch.from_numpy(pcnt.reshape(-1).astype(np.int32)).to(device)
+        all_rows, all_cnts = _all_gather_var(grow), _all_gather_var(gcnt)
+        if rank == 0:
+            try:
+                v, _ = ctx.nf_reference_sparse(all_rows.cpu().numpy().astype(np.uint64), all_cnts.cpu().numpy().reshape(-1, S),
+                                               sum(rs), nf_step)
+                nf = torch.tensor(v, dtype=torch.float64, device=device)
+            except Exception as e:
+                flag[1], err = 1, e
+        dist.broadcast(flag, src=0)
+        if int(flag[1].item()):
+            raise RuntimeError(f"reference-mode NF failed on rank 0: {err}")
     dist.broadcast(nf, src=0)
     nf = nf.cpu().numpy()
     nf_used = nf_text_round(nf) if nf_text_roundtrip else nf
@@ -304,6 +333,8 @@ def run_streamed(backend, key_ptrs, cnt_ptrs, n, r, a, idxA, idxB, pmax, fmin, n
     D_loc, ties = backend.filter(pmax, fmin) if backend.t is not None else (0, (0, 0, 0))
     d = torch.tensor([D_loc, ties[0], ties[1], ties[2]], dtype=torch.int64, device=device)
     dist.all_reduce(d)
+    st["nf_sweep_h2d_bytes"] = st1["h2d_bytes"] if nf_how == "sweep" else 0
+    st["nf_sweep_h2d_seconds"] = st1["h2d_seconds"] if nf_how == "sweep" else 0.0
     st["wall_ms_nf_head"], st["wall_ms_sweep"], st["wall_ms_bh"] = 1e3 * (t_1 - t_0), 1e3 * (t_2 - t_1), 1e3 * (time.perf_counter() - t_2)
     return dict(U=U_glob, R=R_glob, D=int(d[0].item()), ties=tuple(int(x) for x in d[1:].tolist()), nf=nf,
-                R_local=st["R"], U_local=st["U"], D_local=D_loc, n_cand=n_cand, stream=st)
+                R_local=st["R"], U_local=st["U"], D_local=D_loc, n_cand=n_cand, stream=st, nf_from=nf_how)

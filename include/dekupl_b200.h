@@ -251,11 +251,18 @@ int dk_run_path_masked(dk_ctx *ctx, int S, const uint64_t *const *keys, const in
  * row by row (TtestFilter.c:340-444). Here the key space is cut into chunks of about chunk_records records (all dumps
  * together; equal-count k-mer boundaries); chunk c+1 is copied in on a second stream while chunk c is merged, filtered,
  * tested and reduced to its candidate rows (raw p <= p_cut), in k-mer order; the chunk's matrix is then dropped.
- * dk_stream_nf_reference: computeNF's factors (computeNF.c:138-168) from the head of the table = the first chunk; when
- *   computeNF's early stop does not fire inside it the head is widened to the first 2, 4, 8 ... chunks (the whole table
- *   at the latest), so the factors always equal computeNF's on the whole table. info as dk_compute_nf.
- * dk_stream_path: nf = the factors as TtestFilter sees them (after the "%f" round trip). On return *cand_matrix /
- *   *cand_test hold the candidate rows only (both NULL when there is none) and take the ordinary calls
+ * computeNF's factors (computeNF.c:138-168) come from the head of the table when its early stop fires there, else from
+ * ALL all-positive rows of the table, which the reference also reads to the end in that case:
+ * dk_stream_nf_reference: the head = the first chunk; *stop_fired says whether the stop fired inside it. With widen != 0
+ *   the head grows to the first 2, 4, 8 ... chunks until it fires or the dumps are exhausted — exact when these dumps are
+ *   the whole table; a rank of a sharded run passes widen = 0 and, when the stop did not fire, uses:
+ * dk_stream_positive_rows: one sweep that keeps only the rows computeNF can use (every count > 0; with many samples a
+ *   vanishing share of the table). *pos_rows is a dense matrix whose KEY column holds each row's number in this rank's
+ *   filtered table; stats->R / ->U are this rank's totals, stats->n_cand the rows kept.
+ * dk_nf_reference_sparse: computeNF's step / early-stop replay over such rows of a table of R_total rows (row numbers
+ *   ascending, made global by the caller: + the filtered rows of the ranks before). Host arrays. info as dk_compute_nf.
+ * dk_stream_path: the test sweep. nf = the factors as TtestFilter sees them (after the "%f" round trip). On return
+ *   *cand_matrix / *cand_test hold the candidate rows only (both NULL when there is none) and take the ordinary calls
  *   dk_ttest_candidates -> dk_ttest_adjust_global(..., R_global = stats->R summed over all ranks) -> dk_ttest_filter ->
  *   dk_ttest_export_survivors; row indices they report count candidate rows. Free both with their *_free. */
 typedef struct {
@@ -265,7 +272,12 @@ typedef struct {
 } dk_stream_stats;
 int dk_stream_nf_reference(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
                            int min_rec, int min_abund, uint64_t chunk_records, uint64_t step_rows /* 0 = 1,000,000 */,
-                           double *nf_out, uint64_t *info /* may be NULL */);
+                           int widen, double *nf_out, uint64_t *info /* may be NULL */, int *stop_fired /* may be NULL */);
+int dk_stream_positive_rows(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                            int min_rec, int min_abund, uint64_t chunk_records, dk_stream_stats *stats /* may be NULL */,
+                            dk_matrix **pos_rows);
+int dk_nf_reference_sparse(dk_ctx *ctx, int S, uint64_t n_pos, const uint64_t *row_idx, const int32_t *cnts /* [n_pos][S] */,
+                           uint64_t R_total, uint64_t step_rows, double *nf_out, uint64_t *info /* may be NULL */);
 int dk_stream_path(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
                    int min_rec, int min_abund, uint64_t chunk_records, const double *nf,
                    const int *idxA, int nA, const int *idxB, int nB, double p_cut,

@@ -685,3 +685,30 @@ def test_chunk_streamed_path_equals_the_oracle(ctx, S, nA, chunk):
     # a first chunk too small for computeNF's early stop: the head of the table is widened until the stop fires
     nf2, info2 = ctx.stream_nf_reference(kp, cp, n, r, a, 8000, step)
     np.testing.assert_allclose(nf2, onf, rtol=RTOL)
+    # without widening (a rank of a sharded run) the call reports honestly whether the stop fired inside the head
+    nf3, info3 = ctx.stream_nf_reference(kp, cp, n, r, a, 8000, step, widen=False)
+    assert info3["stop_fired"] == (used < len(oc) and used < info3["consumed"] + 1 and info3["consumed"] == used) or not info3["stop_fired"]
+    # the two-sweep form over three emulated ranks: all-positive rows of every rank's key range with global row numbers,
+    # computeNF's step logic replayed on them == computeNF on the whole table, whether or not its stop fires
+    edges = [0] + [int(ok[len(ok) * g // 3]) for g in (1, 2)] + [1 << 63]
+    rows_all, cnts_all, R_tot = [], [], 0
+    for g in range(3):
+        sk, sc = [], []
+        for k, c in zip(keys, cnts):
+            lo, hi = np.searchsorted(k, np.uint64(edges[g])), np.searchsorted(k, np.uint64(edges[g + 1]))
+            sk.append(np.ascontiguousarray(k[lo:hi])); sc.append(np.ascontiguousarray(c[lo:hi]))
+        st1, prow, pcnt = ctx.stream_positive_rows([x.ctypes.data for x in sk], [x.ctypes.data for x in sc], [len(x) for x in sk], r, a, 50_000)
+        rows_all.append(prow + np.uint64(R_tot)); cnts_all.append(pcnt)
+        R_tot += st1["R"]
+    assert R_tot == len(ok)
+    rows_all, cnts_all = np.concatenate(rows_all), np.concatenate(cnts_all)
+    want_pos = np.nonzero((oc > 0).all(axis=1))[0]
+    np.testing.assert_array_equal(rows_all, want_pos.astype(np.uint64))
+    np.testing.assert_array_equal(cnts_all, oc[want_pos])
+    for stp in (step, 3000, 10 ** 9):
+        want, wused, wuz = orc.nf_reference(oc, stp)
+        if wuz:
+            continue
+        got, ginfo = ctx.nf_reference_sparse(rows_all, cnts_all, R_tot, stp)
+        np.testing.assert_allclose(got, want, rtol=RTOL)
+        assert ginfo["consumed"] == wused
