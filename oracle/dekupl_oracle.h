@@ -53,6 +53,8 @@ void orc_nf_full(const int32_t *cnts, size_t R, int S, double *nf_out);
 /* Student-t two-sided tail 2*Q(|t|; df) — replaces the Boost call at
  * TtestFilter.c:146-147 (local regularised incomplete beta, fp64). */
 double orc_student_t_2tail(double t, double df);
+/* the same tail through Boost.Math's branch structure (v > 2t^2: ibetac(1/2, v/2, t^2/(v+t^2)); else ibeta(v/2, 1/2, v/(v+t^2))) */
+double orc_student_t_2tail_boost_branches(double t, double df);
 
 /* TtestFilter.c:373-440 per row (t-test mode): outputs have R entries each. */
 void orc_ttest_rows(const int32_t *cnts, size_t R, int S, const double *nf,

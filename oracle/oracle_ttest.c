@@ -66,6 +66,43 @@ double orc_student_t_2tail(double t, double df)
     return ibeta_half(0.5 * df, x, y);
 }
 
+/* ---- second evaluation path: the branch structure of Boost.Math's students_t cdf complement ----------
+ * cdf(complement(students_t(v), |t|)) with t2 = t*t:
+ *     v > 2 t2 :  z = t2 / (v + t2),  P = ibetac(1/2, v/2, z) / 2
+ *     else     :  z = v / (v + t2),   P = ibeta(v/2, 1/2, z) / 2
+ * and TtestFilter.c:146-147 doubles it. Each routine below receives ONLY its z (as Boost's does) and forms 1 - z itself;
+ * the branch keeps z <= 2/3, which is what makes that subtraction harmless. orc_student_t_2tail above always evaluates
+ * I_{v/(v+t2)}(v/2, 1/2) with both x and 1-x supplied exactly: a different route to the same number. The two must agree
+ * to ~1e-13 (tests/test_oracle.py); on a box with Boost, `make -C oracle ref` + the same grid closes the pin. */
+static double lbeta_half(double v) { return 0.57236494292470008707 - lgamma_ratio_half(v); }   /* log B(v, 1/2) */
+static double ibeta_v_half(double v, double z)          /* I_z(v, 1/2) from z alone */
+{
+    if (z <= 0.0) return 0.0;
+    if (z >= 1.0) return 1.0;
+    const double y = 1.0 - z;
+    const double bt = exp(v * log(z) + 0.5 * log1p(-z) - lbeta_half(v));
+    if (z < (v + 1.0) / (v + 2.5)) return bt * beta_cf(v, 0.5, z) / v;
+    return 1.0 - bt * beta_cf(0.5, v, y) / 0.5;
+}
+static double ibetac_half_v(double v, double z)         /* 1 - I_z(1/2, v) from z alone */
+{
+    if (z <= 0.0) return 1.0;
+    if (z >= 1.0) return 0.0;
+    const double y = 1.0 - z;
+    const double bt = exp(0.5 * log(z) + v * log1p(-z) - lbeta_half(v));   /* log1p: v * log(1 - z) must not lose the low bits of a tiny z */
+    if (z < 1.5 / (v + 2.5)) return 1.0 - bt * beta_cf(0.5, v, z) / 0.5;
+    return bt * beta_cf(v, 0.5, y) / v;
+}
+double orc_student_t_2tail_boost_branches(double t, double df)
+{
+    const double t2 = t * t;
+    if (isinf(df)) return erfc(fabs(t) / sqrt(2.0));
+    double P;
+    if (df > 2.0 * t2) P = ibetac_half_v(0.5 * df, t2 / (df + t2)) / 2.0;
+    else P = ibeta_v_half(0.5 * df, df / (df + t2)) / 2.0;
+    return 2.0 * P;
+}
+
 /* TtestFilter.c:77-98 */
 static double o_sum(const double *v, int n) { double s = 0; for (int i = 0; i < n; i++) s += v[i]; return s; }
 static double o_mean(const double *v, int n) { return o_sum(v, n) / n; }

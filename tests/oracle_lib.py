@@ -26,6 +26,8 @@ def load():
     L.orc_nf_full.argtypes = [vp, sz, i32, vp]
     L.orc_student_t_2tail.restype = dbl
     L.orc_student_t_2tail.argtypes = [dbl, dbl]
+    L.orc_student_t_2tail_boost_branches.restype = dbl
+    L.orc_student_t_2tail_boost_branches.argtypes = [dbl, dbl]
     L.orc_ttest_rows.restype = None
     L.orc_ttest_rows.argtypes = [vp, sz, i32, vp, vp, i32, vp, i32, vp, vp, vp, vp]
     L.orc_poisson_lr.restype = dbl
@@ -164,3 +166,7 @@ def parse_matrix_text(path, S, cap):
     R = load().orc_parse_matrix_text(path.encode(), S, out.ctypes.data, cap)
     assert R >= 0, path
     return out[:R]
+
+
+def student_t_2tail_boost_branches(t, df):
+    return load().orc_student_t_2tail_boost_branches(float(t), float(df))

@@ -712,3 +712,21 @@ def test_chunk_streamed_path_equals_the_oracle(ctx, S, nA, chunk):
         got, ginfo = ctx.nf_reference_sparse(rows_all, cnts_all, R_tot, stp)
         np.testing.assert_allclose(got, want, rtol=RTOL)
         assert ginfo["consumed"] == wused
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag", ["c1", "r88", "r35"])
+def test_ttest_kernels_vs_scipy_only_goldens(ctx, tag):
+    """the row kernels (fast 8-per-group kernel for r88 / c1, general kernel for r35) and the BH kernels against vectors
+    computed by scipy alone (tests/golden/make_ttest_independent.py): p, log2FC, adjusted p of every row"""
+    G = np.load(os.path.join(GOLD, "ttest_independent.npz"))
+    c, nf, iA, iB = G[f"{tag}_counts"], G[f"{tag}_nf"], G[f"{tag}_idxA"].tolist(), G[f"{tag}_idxB"].tolist()
+    m = ctx.matrix_from_host(c)
+    t = ctx.ttest_rows(m, nf, iA, iB)
+    t.adjust(2.0)                                              # every row is a candidate: the full adjusted vector
+    p, fc, adj = t.export_rows()
+    t.free(); m.free()
+    np.testing.assert_allclose(p, G[f"{tag}_p"], rtol=RTOL, atol=1e-300)
+    np.testing.assert_allclose(fc, G[f"{tag}_fc"], rtol=RTOL, atol=1e-12)
+    np.testing.assert_allclose(adj, G[f"{tag}_adj"], rtol=RTOL, atol=1e-300)
+    assert int((p == 0.5).sum()) == int((G[f"{tag}_p"] == 0.5).sum())

@@ -172,3 +172,41 @@ def test_poisson_lr_vs_scipy():
     # density underflow: logpoisson returns the reference's constant 0.001 (TtestFilter.c:157-161), the statistic turns
     # negative, Boost's chi-squared cdf throws and the reference aborts; the restatement (and the product) give p = 1
     assert orc.poisson_lr(5.0, 5000.0, 10**8, 10**8) == 1.0
+
+
+# ---- TtestFilter rows against vectors that share no code with the oracle (tests/golden/make_ttest_independent.py) ----
+INDEP = np.load(os.path.join(GOLD, "ttest_independent.npz"))
+
+
+@pytest.mark.parametrize("tag", ["c1", "r88", "r35"])
+def test_ttest_rows_and_bh_vs_scipy_only_goldens(tag):
+    """p (Welch on log(x/NF + 1), scipy.stats.ttest_ind), means, log2FC and BH (scipy false_discovery_control) computed
+    without the oracle: every config-1 row and 2 x 6000 random rows, including both-sds-zero rows (p = 0.5)"""
+    c, nf, iA, iB = INDEP[f"{tag}_counts"], INDEP[f"{tag}_nf"], INDEP[f"{tag}_idxA"].tolist(), INDEP[f"{tag}_idxB"].tolist()
+    p, mA, mB, fc = orc.ttest_rows(c, nf, iA, iB)
+    np.testing.assert_allclose(p, INDEP[f"{tag}_p"], rtol=1e-9, atol=1e-300)
+    np.testing.assert_allclose(mA, INDEP[f"{tag}_meanA"], rtol=1e-13)
+    np.testing.assert_allclose(mB, INDEP[f"{tag}_meanB"], rtol=1e-13)
+    np.testing.assert_allclose(fc, INDEP[f"{tag}_fc"], rtol=1e-12, atol=1e-14)
+    assert int((INDEP[f"{tag}_p"] == 0.5).sum()) == int((p == 0.5).sum())
+    np.testing.assert_allclose(orc.bh(p), INDEP[f"{tag}_adj"], rtol=1e-9, atol=1e-300)
+    np.testing.assert_allclose(orc.bh(INDEP[f"{tag}_p"]), INDEP[f"{tag}_adj"], rtol=1e-14)      # BH alone, same input
+
+
+def test_student_t_tail_two_evaluation_paths_agree():
+    """orc_student_t_2tail (always I_{v/(v+t^2)}(v/2, 1/2), x and 1-x both exact) against the branch structure of
+    Boost.Math's students_t complement (v > 2t^2: ibetac(1/2, v/2, t^2/(v+t^2)), else ibeta(v/2, 1/2, v/(v+t^2)), each
+    routine given its z alone): <= 1e-12 relative for every df a Welch test can produce here (df <= nA + nB - 2 <= 254),
+    and against the closed form for df = 1 (Cauchy) and df = 2"""
+    worst = 0.0
+    for df in np.concatenate([np.linspace(1, 30, 60), np.logspace(1.5, np.log10(2000), 40), [1.0001, 2, 2.5, 198, 254]]):
+        for t in np.concatenate([np.logspace(-6, 4, 60), [0.0, 0.5, 1, 2, 3.3]]):
+            a, b = orc.student_t_2tail(t, df), orc.student_t_2tail_boost_branches(t, df)
+            if a > 1e-300:
+                worst = max(worst, abs(a - b) / a)
+    assert worst <= 1e-12, worst
+    for t in (1e-6, 0.3, 1.0, 7.5, 1e3):
+        cauchy = 2 / np.pi * np.arctan(1 / t)                       # = 1 - (2/pi) atan(t), without the cancellation
+        np.testing.assert_allclose(orc.student_t_2tail(t, 1.0), cauchy, rtol=1e-13)
+        np.testing.assert_allclose(orc.student_t_2tail_boost_branches(t, 1.0), cauchy, rtol=1e-13)
+        np.testing.assert_allclose(orc.student_t_2tail(t, 2.0), 2 / (np.sqrt(2 + t * t) * (np.sqrt(2 + t * t) + t)), rtol=1e-13)
