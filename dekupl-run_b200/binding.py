@@ -96,6 +96,8 @@ def load_library():
         "dk_nf_reference_sparse": (i32, [vp, i32, u64, vp, vp, u64, u64, P(dbl), P(u64)]),
         "dk_stream_path": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, u64, P(dbl), P(i32), i32, P(i32), i32, dbl,
                                  P(StreamStats), P(vp), P(vp)]),
+        "dk_run_path_matrix_out": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, i32, P(i32), i32, P(i32), i32, dbl, dbl, i32,
+                                         vp, vp, u64, P(u64), P(PathStats), P(vp), P(vp)]),
         "dk_run_path": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, i32, P(i32), i32, P(i32), i32, dbl, dbl, i32,
                               P(PathStats), P(vp), P(vp)]),
     }
@@ -443,6 +445,24 @@ class Context:
         return stats, m, TtestResult(self, ot, m)
 
     # ---- whole path -----------------------------------------------------------
+    def run_path_matrix_out(self, key_ptrs, cnt_ptrs, n, device_inputs, min_rec, min_abund, nf_mode, idxA, idxB, pmax, fmin,
+                            matrix_keys_ptr, matrix_cnts_ptr, cap_rows, nf_text_roundtrip=True):
+        """run_path that also writes the filtered matrix (reference order) to host buffers given by pointer (pinned memory
+        keeps the copy asynchronous); returns (stats, Matrix, TtestResult or None, rows written)"""
+        S, kp, cp, nn = self._tables(key_ptrs, cnt_ptrs, n)
+        a, b = (C.c_int * len(idxA))(*idxA), (C.c_int * len(idxB))(*idxB)
+        st, om, ot, rows = PathStats(), C.c_void_p(0), C.c_void_p(0), C.c_uint64(0)
+        self._chk(self.L.dk_run_path_matrix_out(self.h, S, kp, cp, nn, int(device_inputs), min_rec, min_abund, nf_mode, a, len(idxA), b,
+                                                len(idxB), float(pmax), float(fmin), int(nf_text_roundtrip), C.c_void_p(matrix_keys_ptr),
+                                                C.c_void_p(matrix_cnts_ptr), int(cap_rows), C.byref(rows), C.byref(st), C.byref(om), C.byref(ot)))
+        stats = dict(U=int(st.U), R=int(st.R), R_pos=int(st.R_pos), D=int(st.D), ties=tuple(int(x) for x in st.ties),
+                     nf=np.array(st.nf[:S]), ms_join=st.ms_join, ms_nf=st.ms_nf, ms_ttest=st.ms_ttest, ms_bh=st.ms_bh)
+        m = Matrix(self, om)
+        t = TtestResult(self, ot, m) if ot.value else None
+        if t is not None:
+            t.D, t.ties = stats["D"], stats["ties"]
+        return stats, m, t, int(rows.value)
+
     def run_path(self, key_ptrs, cnt_ptrs, n, device_inputs, min_rec, min_abund, nf_mode, idxA, idxB, pmax, fmin,
                  nf_text_roundtrip=True, keep=False, mask=None, mask_on_device=False, n_mask=None):
         """mask: sorted uint64 k-mers of the reference transcripts (numpy array, or a device pointer with n_mask when

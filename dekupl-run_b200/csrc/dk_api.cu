@@ -170,8 +170,12 @@ static int join_host_slices(dk_ctx *ctx, int S, const uint64_t *const *keys, con
     return rc;
 }
 
+// optional copy of the filtered matrix to caller-owned (pinned) host buffers, in reference order, WHILE the join runs:
+// the rows of slice c leave on a third stream (device -> host) beside the host -> device copies of later slices
+struct dk_host_out { uint64_t *keys = nullptr; int32_t *cnts = nullptr; uint64_t cap = 0, written = 0; };
+
 static int join_host_pipelined(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
-                               int min_rec, int min_abund, int nslices, dk_matrix **out)
+                               int min_rec, int min_abund, int nslices, dk_matrix **out, dk_host_out *ho = nullptr)
 {
     // slice edges: quantiles of the longest dump; per dump a binary search on the host arrays
     int big = 0;
@@ -181,17 +185,58 @@ static int join_host_pipelined(dk_ctx *ctx, int S, const uint64_t *const *keys, 
     dk_cuts cut;
     cuts_from_edges(S, keys, n, edges, cut);
     std::vector<dk_matrix *> parts;
-    int rc = join_host_slices(ctx, S, keys, cnts, cut, min_rec, min_abund, false, nullptr,
-                              [&](dk_matrix *m, int) -> int { parts.push_back(m); return DK_OK; });
+    cudaStream_t ds = nullptr;
+    cudaEvent_t ready[2] = {nullptr, nullptr}, gone[2] = {nullptr, nullptr};
+    uint64_t *sk[2] = {nullptr, nullptr}; int32_t *sc[2] = {nullptr, nullptr};
+    uint64_t scap[2] = {0, 0};
+    bool used[2] = {false, false};
+    if (ho) {
+        DK_CUDA(ctx, cudaStreamCreateWithFlags(&ds, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; i++) { DK_CUDA(ctx, cudaEventCreateWithFlags(&ready[i], cudaEventDisableTiming)); DK_CUDA(ctx, cudaEventCreateWithFlags(&gone[i], cudaEventDisableTiming)); }
+    }
+    int rc = join_host_slices(ctx, S, keys, cnts, cut, min_rec, min_abund, false, nullptr, [&](dk_matrix *m, int c) -> int {
+        parts.push_back(m);
+        if (!ho || !m->R) return DK_OK;
+        const uint64_t rows = m->R;
+        if (ho->written + rows > ho->cap) { ho->written += rows; return DK_OK; }           // keep counting: the caller learns the need
+        const int b = c & 1;
+        if (used[b] && cudaEventSynchronize(gone[b]) != cudaSuccess) return dk_fail(ctx, DK_ERR_CUDA, "join: host copy-out failed");
+        if (scap[b] < rows) {
+            dk_dev_release(ctx, sk[b]); dk_dev_release(ctx, sc[b]);
+            scap[b] = rows + rows / 8 + 1024;
+            sk[b] = (uint64_t *)dk_dev_alloc(ctx, 8 * scap[b]);
+            sc[b] = (int32_t *)dk_dev_alloc(ctx, 4 * scap[b] * S);
+            if (!sk[b] || !sc[b]) return DK_ERR_NOMEM;
+        }
+        DK_TRY(dk_matrix_export_dev(ctx, m, 0, rows, sk[b], sc[b]));                       // dense, reference order
+        DK_CUDA(ctx, cudaEventRecord(ready[b], ctx->stream));
+        DK_CUDA(ctx, cudaStreamWaitEvent(ds, ready[b], 0));
+        DK_CUDA(ctx, cudaMemcpyAsync(ho->keys + ho->written, sk[b], 8 * rows, cudaMemcpyDeviceToHost, ds));
+        DK_CUDA(ctx, cudaMemcpyAsync(ho->cnts + ho->written * (size_t)S, sc[b], 4 * rows * S, cudaMemcpyDeviceToHost, ds));
+        DK_CUDA(ctx, cudaEventRecord(gone[b], ds));
+        used[b] = true;
+        ho->written += rows;
+        return DK_OK;
+    });
     const double ms_join = ctx->stage_ms[0], ms_merge = ctx->stage_ms[4];
+    if (ho) {
+        cudaStreamSynchronize(ds);
+        for (int i = 0; i < 2; i++) { cudaEventDestroy(ready[i]); cudaEventDestroy(gone[i]); dk_dev_release(ctx, sk[i]); dk_dev_release(ctx, sc[i]); }
+        cudaStreamDestroy(ds);
+        if (rc == DK_OK && ho->written > ho->cap)
+            rc = dk_fail(ctx, DK_ERR_ARG, "matrix_out: %llu rows, the host buffers hold %llu", (unsigned long long)ho->written, (unsigned long long)ho->cap);
+    }
     if (rc != DK_OK) { for (auto *p : parts) dk_matrix_release(ctx, p); return rc; }
     rc = concat_matrices(ctx, parts, out);
     ctx->stage_ms[0] = ms_join; ctx->stage_ms[4] = ms_merge;
     return rc;
 }
 
-extern "C" int dk_join_counts(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts,
-                              const uint64_t *n, int min_rec, int min_abund, int emit_stale_tail, dk_matrix **out)
+static int join_counts_host(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                            int min_rec, int min_abund, int emit_stale_tail, dk_matrix **out, dk_host_out *ho);
+
+static int join_counts_host(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                            int min_rec, int min_abund, int emit_stale_tail, dk_matrix **out, dk_host_out *ho)
 {
     if (!ctx || !keys || !cnts || !n) return dk_fail(ctx, DK_ERR_ARG, "join_counts: NULL argument");
     if (S < 1 || S > DK_MAX_SAMPLES) return dk_fail(ctx, DK_ERR_ARG, "join: S=%d outside [1,%d]", S, DK_MAX_SAMPLES);
@@ -202,7 +247,7 @@ extern "C" int dk_join_counts(dk_ctx *ctx, int S, const uint64_t *const *keys, c
         if (const char *e = getenv("DK_JOIN_SLICES")) nslices = atoi(e);
         if (nslices > 64) nslices = 64;
         if (nslices > 1 && !emit_stale_tail && total >= (uint64_t)nslices * 1024)
-            return join_host_pipelined(ctx, S, keys, cnts, n, min_rec, min_abund, nslices, out);
+            return join_host_pipelined(ctx, S, keys, cnts, n, min_rec, min_abund, nslices, out, ho);
     }
     unsigned char *slab = nullptr;
     std::vector<const uint64_t *> kd(S);
@@ -211,8 +256,23 @@ extern "C" int dk_join_counts(dk_ctx *ctx, int S, const uint64_t *const *keys, c
     int rc = dk_join_impl(ctx, S, kd.data(), cd.data(), n, min_rec, min_abund, emit_stale_tail, out);
     cudaStreamSynchronize(ctx->stream);
     dk_dev_release(ctx, slab);
+    if (rc == DK_OK && ho) {                                     // small input: one plain copy after the join
+        ho->written = (*out)->R;
+        if (ho->written > ho->cap) {
+            dk_matrix_release(ctx, *out); *out = nullptr;
+            return dk_fail(ctx, DK_ERR_ARG, "matrix_out: %llu rows, the host buffers hold %llu", (unsigned long long)ho->written, (unsigned long long)ho->cap);
+        }
+        rc = dk_matrix_export(ctx, *out, 0, ho->written, ho->keys, ho->cnts);
+    }
     return rc;
 }
+
+extern "C" int dk_join_counts(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts,
+                              const uint64_t *n, int min_rec, int min_abund, int emit_stale_tail, dk_matrix **out)
+{
+    return join_counts_host(ctx, S, keys, cnts, n, min_rec, min_abund, emit_stale_tail, out, nullptr);
+}
+
 
 // ---- count-balanced shard boundaries --------------------------------------------------------------
 // Shards are k-mer ranges; real dumps are far from uniform in the key (low-complexity sequence clusters), so equal
@@ -704,7 +764,7 @@ static int run_path_impl(dk_ctx *ctx, int S, const uint64_t *const *keys, const 
                          int device_inputs, int min_rec, int min_abund, int nf_mode, const int *idxA, int nA,
                          const int *idxB, int nB, double pmax, double fmin_, int nf_text_roundtrip, bool masked,
                          const uint64_t *mask_keys, uint64_t n_mask, int mask_on_device, dk_path_stats *stats,
-                         uint64_t *rows_masked, dk_matrix **out_matrix, dk_ttest **out_test)
+                         uint64_t *rows_masked, dk_matrix **out_matrix, dk_ttest **out_test, dk_host_out *ho = nullptr)
 {
     if (!ctx || !keys || !cnts || !n) return dk_fail(ctx, DK_ERR_ARG, "run_path: NULL argument");
     if (rows_masked) *rows_masked = 0;
@@ -713,7 +773,14 @@ static int run_path_impl(dk_ctx *ctx, int S, const uint64_t *const *keys, const 
     dk_matrix *m = nullptr;
     dk_ttest *t = nullptr;
     int rc = device_inputs ? dk_join_counts_dev(ctx, S, keys, cnts, n, min_rec, min_abund, 0, &m)
-                           : dk_join_counts(ctx, S, keys, cnts, n, min_rec, min_abund, 0, &m);
+                           : join_counts_host(ctx, S, keys, cnts, n, min_rec, min_abund, 0, &m, ho);
+    if (rc == DK_OK && device_inputs && ho) {                    // device-resident dumps: one copy after the join
+        ho->written = m->R;
+        rc = ho->written <= ho->cap ? dk_matrix_export(ctx, m, 0, m->R, ho->keys, ho->cnts)
+                                    : dk_fail(ctx, DK_ERR_ARG, "matrix_out: %llu rows, the host buffers hold %llu",
+                                              (unsigned long long)ho->written, (unsigned long long)ho->cap);
+        if (rc != DK_OK) { dk_matrix_release(ctx, m); return rc; }
+    }
     if (rc != DK_OK) return rc;
     dk_path_stats st;
     memset(&st, 0, sizeof st);
@@ -781,4 +848,19 @@ extern "C" int dk_run_path_masked(dk_ctx *ctx, int S, const uint64_t *const *key
     if (n_mask && !mask_keys) return dk_fail(ctx, DK_ERR_ARG, "run_path_masked: NULL mask");
     return run_path_impl(ctx, S, keys, cnts, n, device_inputs, min_rec, min_abund, nf_mode, idxA, nA, idxB, nB, pmax, fmin_,
                          nf_text_roundtrip, true, mask_keys, n_mask, mask_on_device, stats, rows_masked, out_matrix, out_test);
+}
+
+extern "C" int dk_run_path_matrix_out(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                                      int device_inputs, int min_rec, int min_abund, int nf_mode, const int *idxA, int nA,
+                                      const int *idxB, int nB, double pmax, double fmin_, int nf_text_roundtrip,
+                                      uint64_t *matrix_keys_host, int32_t *matrix_cnts_host, uint64_t matrix_cap_rows,
+                                      uint64_t *matrix_rows, dk_path_stats *stats, dk_matrix **out_matrix, dk_ttest **out_test)
+{
+    if (!matrix_keys_host || !matrix_cnts_host) return dk_fail(ctx, DK_ERR_ARG, "run_path_matrix_out: NULL host buffer");
+    dk_host_out ho;
+    ho.keys = matrix_keys_host; ho.cnts = matrix_cnts_host; ho.cap = matrix_cap_rows;
+    const int rc = run_path_impl(ctx, S, keys, cnts, n, device_inputs, min_rec, min_abund, nf_mode, idxA, nA, idxB, nB, pmax, fmin_,
+                                 nf_text_roundtrip, false, nullptr, 0, 0, stats, nullptr, out_matrix, out_test, &ho);
+    if (matrix_rows) *matrix_rows = ho.written;
+    return rc;
 }

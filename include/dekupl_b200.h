@@ -236,6 +236,17 @@ int dk_run_path(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *
                 const int *idxA, int nA, const int *idxB, int nB, double pmax, double fmin,
                 int nf_text_roundtrip /* round NFs through "%f" like the pipeline does */,
                 dk_path_stats *stats, dk_matrix **out_matrix /* may be NULL */, dk_ttest **out_test /* may be NULL */);
+/* dk_run_path that also RETURNS the filtered count matrix (the rows joinCounts prints, joinCounts.c:104-110; the
+ * pipeline's raw-counts.tsv.gz, Snakefile:594-596) in caller-owned host buffers, reference order: matrix_keys_host
+ * [cap_rows], matrix_cnts_host [cap_rows * S] row-major; pinned memory makes the copy asynchronous. With host dumps the
+ * rows of every key-range slice leave on a third stream while later slices are still being copied in (PCIe is full
+ * duplex). *matrix_rows = rows written; if they exceed cap_rows the call fails with DK_ERR_ARG and *matrix_rows = the need. */
+int dk_run_path_matrix_out(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                           int device_inputs, int min_rec, int min_abund, int nf_mode,
+                           const int *idxA, int nA, const int *idxB, int nB, double pmax, double fmin,
+                           int nf_text_roundtrip, uint64_t *matrix_keys_host, int32_t *matrix_cnts_host,
+                           uint64_t matrix_cap_rows, uint64_t *matrix_rows /* may be NULL */,
+                           dk_path_stats *stats, dk_matrix **out_matrix /* may be NULL */, dk_ttest **out_test /* may be NULL */);
 /* RNA-Seq mode (Snakefile:654): the same path with the mask between computeNF and TtestFilter.
  * NFs come from the raw matrix; the t-test, BH and the survivors from the masked one, which is
  * what *out_matrix receives. stats->R stays the raw row count; *rows_masked = rows the mask removed. */

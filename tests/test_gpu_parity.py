@@ -730,3 +730,40 @@ def test_ttest_kernels_vs_scipy_only_goldens(ctx, tag):
     np.testing.assert_allclose(fc, G[f"{tag}_fc"], rtol=RTOL, atol=1e-12)
     np.testing.assert_allclose(adj, G[f"{tag}_adj"], rtol=RTOL, atol=1e-300)
     assert int((p == 0.5).sum()) == int((G[f"{tag}_p"] == 0.5).sum())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("slices,device_inputs", [(6, False), (1, False), (1, True)])
+def test_run_path_matrix_out_returns_the_matrix_in_reference_order(ctx, slices, device_inputs, monkeypatch):
+    """dk_run_path_matrix_out: the filtered matrix written to host buffers (slice by slice beside the H2D copies when the
+    dumps are host arrays) == joinCounts' rows in order (oracle), same statistics as dk_run_path; too small a buffer is
+    refused with the need reported"""
+    import ctypes as C
+    import torch
+    from common import plant_effect
+    rng = np.random.default_rng(9 + slices)
+    S, nA = 8, 4
+    keys, cnts = random_dumps(rng, S, 90_000, 62, 0.2, 40, p_core=0.3)
+    cnts = plant_effect(rng, keys, cnts, set(range(nA, S)))
+    ok, oc, oU = orc.join(keys, cnts, 2, 5)
+    monkeypatch.setenv("DK_JOIN_SLICES", str(slices))
+    if device_inputs:
+        tk = [torch.from_numpy(k.view(np.int64).copy()).cuda() for k in keys]
+        tc = [torch.from_numpy(c.copy()).cuda() for c in cnts]
+        kp, cp = [t.data_ptr() for t in tk], [t.data_ptr() for t in tc]
+    else:
+        kp, cp = [k.ctypes.data for k in keys], [c.ctypes.data for c in cnts]
+    n = [len(k) for k in keys]
+    cap = len(ok) + 10
+    hk, hc = np.zeros(cap, np.uint64), np.zeros((cap, S), np.int32)
+    st, m, t, rows = ctx.run_path_matrix_out(kp, cp, n, device_inputs, 2, 5, dk.NF_REFERENCE, list(range(nA)), list(range(nA, S)), 0.05, 0.0,
+                                             hk.ctypes.data, hc.ctypes.data, cap)
+    assert rows == len(ok) == st["R"] and st["U"] == oU and st["D"] > 0
+    np.testing.assert_array_equal(hk[:rows], ok)
+    np.testing.assert_array_equal(hc[:rows], oc)
+    st2 = ctx.run_path(kp, cp, n, device_inputs, 2, 5, dk.NF_REFERENCE, list(range(nA)), list(range(nA, S)), 0.05, 0.0)
+    assert (st2["U"], st2["R"], st2["D"]) == (st["U"], st["R"], st["D"])
+    t.free(); m.free()
+    with pytest.raises(dk.DkError, match="host buffers hold"):
+        ctx.run_path_matrix_out(kp, cp, n, device_inputs, 2, 5, dk.NF_REFERENCE, list(range(nA)), list(range(nA, S)), 0.05, 0.0,
+                                hk.ctypes.data, hc.ctypes.data, 100)
