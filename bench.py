@@ -56,6 +56,7 @@ def parse():
     ap.add_argument("--no-parity", action="store_true", help="skip the full-size invariants and the seeded-sample oracle check")
     ap.add_argument("--no-mask", action="store_true", help="skip the reference-transcript mask measurement")
     ap.add_argument("--no-ingest", action="store_true", help="skip the k-mer counting measurement")
+    ap.add_argument("--no-other", action="store_true", help="skip the other single-GPU configuration (cfg 5) measured beside the headline")
     ap.add_argument("--cpu-rows", type=int, default=6_000_000, help="union rows of the CPU-baseline sample")
     ap.add_argument("--ref-rows-per-core", type=int, default=1_000_000, help="--impl reference: union rows of the sample per host core")
     return ap.parse_args()
@@ -171,6 +172,10 @@ def make_cpu_sample(cfg, rows, row0=0, **eff):
 REF_DIR = os.path.join(ROOT, "oracle", "_ref")
 
 
+class UndefinedZone(RuntimeError):
+    pass
+
+
 def _host_cores():
     try:
         return sorted(os.sched_getaffinity(0))
@@ -220,6 +225,7 @@ def cpu_reference_text(files, cfg, nA, workdir, cores):
         procs.append(subprocess.Popen(pin(p) + [jc, "-r", str(cfg["r"]), "-a", str(cfg["a"])] + files[p], stdout=open(raw, "wb")))
     if any(q.wait() != 0 for q in procs):
         raise RuntimeError("reference joinCounts failed")
+    t_join = time.perf_counter()
     table = os.path.join(workdir, "raw-counts.tsv")
     with open(table, "wb") as out:
         out.write(("tag\t" + "\t".join(f"s{i}" for i in range(S)) + "\n").encode())
@@ -230,22 +236,30 @@ def cpu_reference_text(files, cfg, nA, workdir, cores):
                     if not b:
                         break
                     out.write(b)
+    t_cat = time.perf_counter()
     r = subprocess.run(pin(0) + [nfb, table], capture_output=True, text=True)
+    t_nf = time.perf_counter()
     if r.returncode != 0:
         raise RuntimeError("reference computeNF failed: " + r.stderr[-200:])
     nf = [ln.split("\t")[1] for ln in r.stdout.strip().splitlines()[1:]]          # "%f" text, as TtestFilter reads it
+    if any(not (float(x) > 0) for x in nf):
+        # 1,000,000 <= rows < 2,000,000: the reference computeNF prints uninitialised memory, usually zeros
+        raise UndefinedZone("computeNF printed non-positive factors: the sample's table has between 1M and 2M rows")
     procs = []
     for p in range(P):
         procs.append(subprocess.Popen(pin(p) + [tt, raws[p], str(S), str(nA), raws[p] + ".p", raws[p] + ".fc"] + nf,
                                       stdout=subprocess.DEVNULL))
     if any(q.wait() != 0 for q in procs):
         raise RuntimeError("ttest_text failed")
+    t_tt = time.perf_counter()
     pv = np.concatenate([np.fromfile(raw + ".p") for raw in raws])
     fc = np.concatenate([np.fromfile(raw + ".fc") for raw in raws])
     adj = orc.bh(pv)
     D = int(((adj <= PMAX) & (np.abs(fc) >= FMIN)).sum())
     dt = time.perf_counter() - t0
     cpu_reference_text.nf = [float(x) for x in nf]
+    cpu_reference_text.stage_s = {"joinCounts": t_join - t0, "cat+header": t_cat - t_join, "computeNF": t_nf - t_cat,
+                                  "TtestFilter rows (port)": t_tt - t_nf, "BH+filter": time.perf_counter() - t_tt}
     return len(pv), D, dt
 
 
@@ -271,18 +285,22 @@ def run_reference(args):
     cores = _host_cores()
     P = len(cores)
     rows = args.ref_rows_per_core * P
-    keys, cnts = make_cpu_sample(cfg, rows)
-    U = _union_size(keys)
-    wd = _workdir()
-    try:
-        files, nbytes = stage_text_sample(keys, cnts, P, wd)
-        times, R, D = [], 0, 0
-        for i in range(args.warmup + args.steps):
-            R, D, dt = cpu_reference_text(files, cfg, S // 2, wd, cores)
-            if i >= args.warmup:
-                times.append(dt)
-    finally:
-        shutil.rmtree(wd, ignore_errors=True)
+    for attempt in range(4):
+        keys, cnts = make_cpu_sample(cfg, rows)
+        U = _union_size(keys)
+        wd = _workdir()
+        try:
+            files, nbytes = stage_text_sample(keys, cnts, P, wd)
+            times, R, D = [], 0, 0
+            for i in range(args.warmup + args.steps):
+                R, D, dt = cpu_reference_text(files, cfg, S // 2, wd, cores)
+                if i >= args.warmup:
+                    times.append(dt)
+            break
+        except UndefinedZone:                           # move the sample out of computeNF's undefined zone (1M..2M table rows)
+            rows = int(rows * 0.55)
+        finally:
+            shutil.rmtree(wd, ignore_errors=True)
     ms = 1e3 * sum(times) / len(times)
     val = U / (ms / 1e3)
     sample = (f"first {rows} of {cfg['U']} union rows of the same generator (prefix shard: {U} union k-mers, "
@@ -294,6 +312,7 @@ def run_reference(args):
         "vs_baseline": None, "dtype": "u64 keys / i32 counts / f64 statistics", "data": "synthetic",
         "config": {"workload": cfg["name"], "sample": sample, "filtered_rows": R, "survivors": D},
         "cpu_baseline": {"value": val, "unit": "k-mers/s", "cores": P, "kind": "reference+port", "sample": sample,
+                         "stage_seconds_last_step": cpu_reference_text.stage_s,
                          "note": "UNMODIFIED reference joinCounts and computeNF binaries (oracle/_ref, built from /root/reference/share) "
                                  "on plain text, one taskset-pinned process per core and key range; TtestFilter needs Boost "
                                  "(unbuildable here): its row pass is the oracle port as a process over the same text "
@@ -659,6 +678,18 @@ def run_ours(args):
                      "whole_path": {"alg_bytes": b_all, "achieved": b_all / (ms / 1e3) / 1e9, "frac": b_all / (ms / 1e3) / 1e9 / peak}},
         "clocks": clocks,
     }
+    # the second kernel of the step is NOT HBM-bound: say what binds it: live HBM fraction of its stage + the
+    # counters of its committed ncu capture
+    tt_bytes = R_loc * 4 * S + 16 * R_loc
+    tt = {"bound": "fp64 issue latency (dependent fp64 chains at 24 resident warps), not HBM",
+          "kernel": "k_ttest_rows8 (groups of <= 8 in column order)" if S // 2 <= 8 else "k_ttest_rows (general groups)",
+          "kernel_ms": float(stage_avg[2]), "alg_bytes": tt_bytes, "hbm_achieved_gbs": tt_bytes / (stage_avg[2] / 1e3) / 1e9 if stage_avg[2] else None,
+          "hbm_frac": tt_bytes / (stage_avg[2] / 1e3) / 1e9 / peak if stage_avg[2] else None, "rows_per_s": R_loc / (stage_avg[2] / 1e3) if stage_avg[2] else None}
+    try:
+        tt["counters"] = json.load(open(os.path.join(ROOT, "profiles", "k4_counters.json")))
+    except (OSError, ValueError):
+        tt["counters"] = None
+    out["roofline_ttest"] = tt
     # ---- §8(f)#1, the RNA-Seq mask (bin/diffFilter.pl): not part of the headline metric, measured beside it at N=1
     if world == 1 and not args.no_mask:
         out["mask"] = run_mask(args, cfg, ctx, kp, cp, n, peak)
@@ -674,16 +705,22 @@ def run_ours(args):
                                             idxA, idxB, nf_mode)
     if rank == 0 and not args.no_cpu:
         import shutil
-        ck, cc = make_cpu_sample(cfg, args.cpu_rows)
-        cU = _union_size(ck)
-        wd = _workdir()
-        try:
-            files, nbytes = stage_text_sample(ck, cc, 1, wd)
-            cR, cD, dt = cpu_reference_text(files, cfg, S // 2, wd, _host_cores()[:1])
-        finally:
-            shutil.rmtree(wd, ignore_errors=True)
+        cpu_rows = args.cpu_rows
+        for attempt in range(4):
+            ck, cc = make_cpu_sample(cfg, cpu_rows)
+            cU = _union_size(ck)
+            wd = _workdir()
+            try:
+                files, nbytes = stage_text_sample(ck, cc, 1, wd)
+                cR, cD, dt = cpu_reference_text(files, cfg, S // 2, wd, _host_cores()[:1])
+                break
+            except UndefinedZone:                       # the reference computeNF prints garbage for 1M..2M table rows: other size
+                cpu_rows = int(cpu_rows * 0.75)
+            finally:
+                shutil.rmtree(wd, ignore_errors=True)
         out["cpu_baseline"] = {"value": cU / dt, "unit": "k-mers/s", "cores": 1, "kind": "reference+port", "seconds": dt,
-                               "sample": f"first {args.cpu_rows} of {cfg['U']} rows of the same generator ({cU} union k-mers, "
+                               "stage_seconds": cpu_reference_text.stage_s,
+                               "sample": f"first {cpu_rows} of {cfg['U']} rows of the same generator ({cU} union k-mers, "
                                          f"{nbytes / 1e9:.2f} GB of plain-text dumps staged outside the timed region): the UNMODIFIED "
                                          "reference joinCounts and computeNF binaries + the TtestFilter port (Boost absent) as "
                                          "processes over text, taskset to one core"}
@@ -696,6 +733,18 @@ def run_ours(args):
         out["e2e"] = run_e2e(args, cfg, ctx, keys, cnts, n, idxA, idxB, nf_mode)
     elif world > 1:
         out["e2e"] = {"value": None, "unit": "k-mers/s", "note": "measured at N=1 only (host staging is per-GPU identical)"}
+    # ---- BASELINE.json's other configurations: cfg 5 on this GPU; cfg 3 / cfg 4 need several GPUs (records under profiles/)
+    if world == 1 and args.config == 2 and not args.no_other:
+        keys.clear(); cnts.clear()
+        torch.cuda.empty_cache()
+        try:
+            out["other_configs"] = {"cfg5": run_other_config(args, ctx, dev, 5),
+                                    "cfg3": "multi-GPU (strong scaling over 2/4/8 GPUs): python -m torch.distributed.run ... bench.py --config 3 --gpus N; "
+                                            "records of this round: profiles/r02c_scale_cfg3_n{2,4,8}.json",
+                                    "cfg4": "streamed from pinned host memory over 8 GPUs: bench.py --config 4 --gpus 8; record: "
+                                            "profiles/r02g_scale_cfg4_n8_half_scale.json"}
+        except Exception as e:                              # the headline stands on its own
+            out["other_configs"] = {"error": str(e)}
     if rank == 0:
         print(json.dumps(out))
     if dist:
@@ -796,6 +845,57 @@ def parity_checks(args, cfg, ctx, dev, rank, world, dist, keys, cnts, kp, cp, n,
         res["equal"] = bool(res["sample_equal"] and res["full_size"]["equal"])
     return res
 
+
+
+def run_other_config(args, ctx, dev, cid):
+    """one of BASELINE.json's other single-GPU configurations, measured beside the headline (device-resident value only)"""
+    import torch
+    from dekupl_run_b200 import synth
+    import dekupl_run_b200 as dk
+    cfg = CONFIGS[cid]
+    S = cfg["S"]
+    idxA, idxB = list(range(S // 2)), list(range(S // 2, S))
+    rows = int(cfg["U"] * args.scale)
+    keys, cnts = synth.gen_shard(S, rows, 0, rows, device=dev, model=cfg["model"], q=cfg["q"], alpha=cfg["alpha"])
+    torch.cuda.synchronize(); torch.cuda.empty_cache()
+    n = [int(k.numel()) for k in keys]
+    kp, cp = [k.data_ptr() for k in keys], [c.data_ptr() for c in cnts]
+    nf_mode = dk.NF_REFERENCE
+
+    def step():
+        return ctx.run_path(kp, cp, n, True, cfg["r"], cfg["a"], nf_mode, idxA, idxB, PMAX, FMIN, nf_text_roundtrip=True)
+    for _ in range(3):
+        st = step()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    mk, K = 0.0, 3
+    e0.record()
+    for _ in range(K):
+        st = step()
+        mk += ctx.stage_ms(4)
+    e1.record()
+    torch.cuda.synchronize()
+    ms, mk = e0.elapsed_time(e1) / K, mk / K
+    b_all, b_merge = algorithmic_bytes(sum(n), st["R"], S)
+    peak = 6650.0
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except (OSError, KeyError):
+        pass
+    stm, m, t = ctx.run_path(kp, cp, n, True, cfg["r"], cfg["a"], nf_mode, idxA, idxB, PMAX, FMIN, nf_text_roundtrip=True, keep=True)
+    gx, gs = m.checksum()
+    if t is not None:
+        t.free()
+    m.free()
+    exp = synth.expected_invariants(S, rows, 0, rows, cfg["r"], cfg["a"], device=dev, model=cfg["model"], q=cfg["q"], alpha=cfg["alpha"])
+    M64 = (1 << 64) - 1
+    ok = bool(stm["U"] == exp["U"] and stm["R"] == exp["R"] and (gx & M64) == exp["key_xor"] and (gs & M64) == exp["count_sum"])
+    del keys, cnts
+    torch.cuda.empty_cache()
+    return {"workload": cfg["name"], "value": st["U"] / (ms / 1e3), "unit": "k-mers/s", "ms_per_step": ms, "union_kmers": st["U"],
+            "records": sum(n), "filtered_rows": st["R"], "survivors": st["D"], "merge_kernel_ms": mk,
+            "merge_frac_of_hbm_peak": b_merge / (mk / 1e3) / 1e9 / peak, "whole_path_frac_of_hbm_peak": b_all / (ms / 1e3) / 1e9 / peak,
+            "full_size_invariants_equal": ok, "steps": K, "warmup": 3}
 
 
 def run_ingest(args, ctx):

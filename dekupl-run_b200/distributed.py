@@ -153,8 +153,18 @@ def _all_gather_var(x, group=None):
 def _bh_global(backend, R_glob, pmax):
     """Benjamini-Hochberg over the candidates of all ranks (TtestFilter.c:456-476): leaves the adjusted values on
     backend.t; returns the global candidate count"""
+    import os
+    import time
     rank, world = dist.get_rank(), dist.get_world_size()
+    prof = [] if os.environ.get("DK_BH_PROF") else None
+
+    def mark(name):
+        if prof is not None:
+            torch.cuda.synchronize()
+            prof.append((name, time.perf_counter()))
+    mark("start")
     cand = backend.candidates(pmax)
+    mark("candidates")
     if world == 1:
         backend.adjust_global(cand, R_glob)
         n_cand = int(cand.numel())
@@ -169,6 +179,7 @@ def _bh_global(backend, R_glob, pmax):
         zero = torch.zeros(1, dtype=cuts.dtype, device=cand.device)
         full = torch.full((1,), send.numel(), dtype=cuts.dtype, device=cand.device)
         counts = torch.diff(torch.cat([zero, cuts, full])).to(torch.int64)
+        mark("sort+cuts")
         table = [torch.zeros_like(counts) for _ in range(world)]
         dist.all_gather(table, counts)
         table = torch.stack(table).cpu()                              # table[src][dst]
@@ -176,8 +187,11 @@ def _bh_global(backend, R_glob, pmax):
         recv_n = [int(x) for x in table[:, rank].tolist()]
         n_below = int(table[:, :rank].sum().item())
         n_cand = int(table.sum().item())
+        mark("count table")
         mine = _exchange(send, send_n, recv_n)
+        mark("route")
         sp, F = backend.bh_rank_slice(mine, n_below, R_glob)
+        mark("rank slice")
         # the running minimum crosses range borders: lower F by the smallest F of all higher ranges
         first = F[:1] if F.numel() else torch.full((1,), float("inf"), dtype=torch.float64, device=cand.device)
         mins = [torch.empty_like(first) for _ in range(world)]
@@ -187,8 +201,14 @@ def _bh_global(backend, R_glob, pmax):
             F = torch.minimum(F, above)
         # adjusted value of every routed candidate: adj depends on the value only, so any member of a tie run will do
         adj_mine = F[torch.searchsorted(sp, mine)] if mine.numel() else mine
+        mark("mins+lookup")
         adj_send = _exchange(adj_mine.contiguous(), recv_n, send_n)   # back to the senders, in `send` order
+        mark("route back")
         backend.apply_adjusted(send, adj_send)                        # `send` is this rank's candidate list, sorted
+        mark("apply")
+    if prof and rank == 0:
+        print("[bh prof] " + " ".join(f"{b[0]}={1e3 * (b[1] - a[1]):.2f}ms" for a, b in zip(prof[:-1], prof[1:])) + f" cand={int(cand.numel())}",
+              file=__import__("sys").stderr)
     return n_cand
 
 
