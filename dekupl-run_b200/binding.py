@@ -84,6 +84,9 @@ def load_library():
         "dk_ttest_candidates": (i32, [vp, vp, dbl, P(u64), P(vp)]),
         "dk_ttest_adjust_global": (i32, [vp, vp, vp, u64, u64]),
         "dk_ttest_adjust": (i32, [vp, vp, dbl]),
+        "dk_ttest_count_le": (i32, [vp, vp, dbl, P(u64)]),
+        "dk_bh_next_cut": (dbl, [dbl, u64, u64]),
+        "dk_ttest_candidates_narrowed": (i32, [vp, vp, dbl, dbl, P(u64), P(vp)]),
         "dk_bh_rank_slice": (i32, [vp, vp, u64, u64, u64, vp, vp]),
         "dk_bh_rank_slice_noalloc": (i32, [vp, vp, u64, u64, u64, vp, vp]),
         "dk_ttest_apply_adjusted": (i32, [vp, vp, vp, vp, u64]),
@@ -208,6 +211,16 @@ class TtestResult:
     def candidates(self, p_cut):
         n, p = C.c_uint64(0), C.c_void_p(0)
         self.ctx._chk(self.ctx.L.dk_ttest_candidates(self.ctx.h, self.h, float(p_cut), C.byref(n), C.byref(p)))
+        return int(n.value), p.value
+
+    def count_le(self, cut):
+        n = C.c_uint64(0)
+        self.ctx._chk(self.ctx.L.dk_ttest_count_le(self.ctx.h, self.h, float(cut), C.byref(n)))
+        return int(n.value)
+
+    def candidates_narrowed(self, cut, p_cut):
+        n, p = C.c_uint64(0), C.c_void_p(0)
+        self.ctx._chk(self.ctx.L.dk_ttest_candidates_narrowed(self.ctx.h, self.h, float(cut), float(p_cut), C.byref(n), C.byref(p)))
         return int(n.value), p.value
 
     def adjust_global(self, all_p_dev_ptr, n_all, R_global):

@@ -6,6 +6,7 @@
 // compute v at the last element of every tie run, take a suffix minimum, and look
 // each local candidate up. Multi-GPU: candidates are all-gathered by the caller.
 #include <math.h>
+#include <stdlib.h>
 #include "dk_common.cuh"
 
 void dk_ttest_release(dk_ctx *ctx, dk_ttest *t);
@@ -161,6 +162,46 @@ extern "C" int dk_ttest_candidates(dk_ctx *ctx, dk_ttest *t, double p_cut, uint6
     return DK_OK;
 }
 
+// #{ p_raw <= cut } of this object's rows: the counting pass of the candidate narrowing below (one read of p_raw)
+extern "C" int dk_ttest_count_le(dk_ctx *ctx, const dk_ttest *t, double cut, uint64_t *n)
+{
+    if (!ctx || !t || !n) return dk_fail(ctx, DK_ERR_ARG, "ttest_count_le: NULL argument");
+    *n = 0;
+    if (!t->R) return DK_OK;
+    cudaStream_t st = ctx->stream;
+    unsigned long long *ctr = (unsigned long long *)dk_dev_alloc(ctx, 64);
+    if (!ctr) return DK_ERR_NOMEM;
+    DK_CUDA(ctx, cudaMemsetAsync(ctr, 0, 64, st));
+    const unsigned grid = (unsigned)((t->R + BHC_T * BHC_V - 1) / (BHC_T * BHC_V));
+    k_bh_candidates<<<grid, 256, 0, st>>>(t->p_raw, t->R, cut, ctr, nullptr, nullptr, 0); DK_LAUNCHED(ctx);
+    uint64_t nc = 0;
+    DK_CUDA(ctx, cudaMemcpyAsync(&nc, ctr, 8, cudaMemcpyDeviceToHost, st));
+    DK_CUDA(ctx, cudaStreamSynchronize(st));
+    dk_dev_release(ctx, ctr);
+    *n = nc;
+    return DK_OK;
+}
+// Candidate narrowing. A row reaches an adjusted p <= P only through some q >= p with R/rank(q) * q <= P, i.e.
+// q <= P * rank(q) / R. With n = #{p <= c} over ALL rows (all ranks), every q <= c has rank(q) <= n, hence
+// q <= c' = P * n / R: candidates above c' can neither survive nor lower anybody's adjusted value to <= P. Starting from
+// c = P the cut falls 0.05 -> P * n0 / R -> ... in a few counting passes (8 M -> a few thousand candidates at cfg 2),
+// and sort / rank / lookup shrink with it. The margin keeps rows within the 1e-9 tie window of P in the census.
+extern "C" double dk_bh_next_cut(double p_cut, uint64_t n_le_cut_global, uint64_t R_global)
+{
+    if (!(p_cut < 1.0) || R_global == 0) return p_cut;
+    return p_cut * ((double)n_le_cut_global / (double)R_global) * (1.0 + 1e-8) + 1e-300;
+}
+// dk_ttest_candidates at a NARROWED cut: the list holds p_raw <= cut, and the adjusted values written through it are
+// declared exact up to p_cut (the caller derived `cut` from p_cut with dk_bh_next_cut over the global counts)
+extern "C" int dk_ttest_candidates_narrowed(dk_ctx *ctx, dk_ttest *t, double cut, double p_cut, uint64_t *n_cand,
+                                            const double **cand_p_dev)
+{
+    if (!(cut <= p_cut)) return dk_fail(ctx, DK_ERR_ARG, "ttest_candidates_narrowed: cut %g above p_cut %g", cut, p_cut);
+    DK_TRY(dk_ttest_candidates(ctx, t, cut, n_cand, cand_p_dev));
+    t->p_cut = p_cut;
+    return DK_OK;
+}
+
 // Rank one p-value slice of the (global) candidate list: sorted ascending, then F[j] = min_{i >= j in the slice}
 // R/(n_below+i+1) * p_i taken at the last element of every tie run (TtestFilter.c:459-475 restated on ascending order).
 // n_below = number of candidates (anywhere) smaller than every value of this slice. A multi-GPU caller owns one
@@ -274,8 +315,19 @@ extern "C" int dk_ttest_adjust_global(dk_ctx *ctx, dk_ttest *t, const double *al
 
 extern "C" int dk_ttest_adjust(dk_ctx *ctx, dk_ttest *t, double p_cut)
 {
+    if (!ctx || !t) return dk_fail(ctx, DK_ERR_ARG, "ttest_adjust: NULL argument");
     uint64_t nc = 0;
     const double *cp = nullptr;
-    DK_TRY(dk_ttest_candidates(ctx, t, p_cut, &nc, &cp));
+    double cut = p_cut;
+    if (p_cut < 1.0 && t->R && !getenv("DK_BH_NO_NARROW")) {
+        for (int it = 0; it < 4; it++) {                          // each pass: one read of p_raw (dk_bh_next_cut)
+            uint64_t n = 0;
+            DK_TRY(dk_ttest_count_le(ctx, t, cut, &n));
+            const double next = dk_bh_next_cut(p_cut, n, t->R);
+            if (!(next < cut * 0.75)) break;                      // no longer worth a pass
+            cut = next;
+        }
+    }
+    DK_TRY(dk_ttest_candidates_narrowed(ctx, t, cut, p_cut, &nc, &cp));
     return dk_ttest_adjust_global(ctx, t, cp, nc, t->R);
 }

@@ -75,9 +75,15 @@ class GpuBackend:
     def ttest_rows(self, nf, idxA, idxB):
         self.t = self.ctx.ttest_rows(self.m, nf, idxA, idxB)
 
-    def candidates(self, p_cut):
-        """-> float64 tensor (device) of this rank's candidate p-values"""
-        n, ptr = self.t.candidates(p_cut)
+    def count_le(self, cut):
+        return self.t.count_le(cut) if self.t is not None else 0
+
+    def next_cut(self, p_cut, n_global, R_global):
+        return float(self.ctx.L.dk_bh_next_cut(float(p_cut), int(n_global), int(R_global)))
+
+    def candidates(self, p_cut, cut=None):
+        """-> float64 tensor (device) of this rank's candidate p-values (p <= cut, the narrowed p_cut)"""
+        n, ptr = self.t.candidates(p_cut) if cut is None or cut >= p_cut else self.t.candidates_narrowed(cut, p_cut)
         self.ctx.sync()
         if n == 0:
             return torch.empty(0, dtype=torch.float64, device=self.device)
@@ -163,17 +169,30 @@ def _bh_global(backend, R_glob, pmax):
             torch.cuda.synchronize()
             prof.append((name, time.perf_counter()))
     mark("start")
-    cand = backend.candidates(pmax)
+    # candidate narrowing over the GLOBAL counts (dk_bh_next_cut): a few counting passes + scalar all-reduces shrink the
+    # candidate lists of all ranks from |{p <= P}| to about the rows that can matter, and everything below with them
+    cut = pmax
+    if pmax < 1.0 and R_glob > 0 and hasattr(backend, "count_le"):
+        for _ in range(4):
+            nle = torch.tensor([backend.count_le(cut)], dtype=torch.int64, device=backend.device)
+            if world > 1:
+                dist.all_reduce(nle)
+            nxt = backend.next_cut(pmax, int(nle.item()), R_glob)
+            if not (nxt < cut * 0.75):
+                break
+            cut = nxt
+    mark("narrow")
+    cand = backend.candidates(pmax, cut)
     mark("candidates")
     if world == 1:
         backend.adjust_global(cand, R_glob)
         n_cand = int(cand.numel())
     else:
-        # BH is split by p-value range: rank g owns the candidates in (g*P/world, (g+1)*P/world] (equal values share a
-        # range; under the null p is uniform, so the ranges are balanced). Every rank ROUTES its candidates to their
+        # BH is split by p-value range: rank g owns the candidates in (g*cut/world, (g+1)*cut/world] (equal values share a
+        # range; under the null p is uniform, so the ranges are balanced; `cut` is the narrowed P). Every rank ROUTES its candidates to their
         # owners (all-to-all), the owner ranks its range and answers with the adjusted values (all-to-all back): the
         # traffic and the sort per rank stay those of one shard however many ranks there are.
-        edges = torch.tensor([pmax * g / world for g in range(1, world)], dtype=torch.float64, device=cand.device)
+        edges = torch.tensor([cut * g / world for g in range(1, world)], dtype=torch.float64, device=cand.device)
         send, _ = torch.sort(cand)                                    # ranges become contiguous: edges[g-1] < p <= edges[g] -> g
         cuts = torch.searchsorted(send, edges, right=True)            # elements <= edges[g]
         zero = torch.zeros(1, dtype=cuts.dtype, device=cand.device)
@@ -267,10 +286,10 @@ class StreamBackend(GpuBackend):
         self.stream_stats = None
 
     # a rank whose chunks held no candidate row has no test object; it still takes part in every collective
-    def candidates(self, p_cut):
+    def candidates(self, p_cut, cut=None):
         if self.t is None:
             return torch.empty(0, dtype=torch.float64, device=self.device)
-        return super().candidates(p_cut)
+        return super().candidates(p_cut, cut)
 
     def adjust_global(self, all_p, R_global):
         if self.t is not None:

@@ -175,6 +175,15 @@ int dk_poisson_rows(dk_ctx *ctx, const dk_matrix *m, const int *idxA, int nA, co
 int dk_ttest_candidates(dk_ctx *ctx, dk_ttest *t, double p_cut, uint64_t *n_cand, const double **cand_p_dev);
 int dk_ttest_adjust_global(dk_ctx *ctx, dk_ttest *t, const double *all_cand_p_dev, uint64_t n_all, uint64_t R_global);
 int dk_ttest_adjust(dk_ctx *ctx, dk_ttest *t, double p_cut);
+/* Candidate narrowing (what dk_ttest_adjust does internally; the multi-GPU caller does it over global counts): with
+ * n = #{p <= c} over ALL rows of all ranks, no row above c' = dk_bh_next_cut(p_cut, n, R_global) = p_cut * n / R_global
+ * can survive or lower an adjusted value to <= p_cut, so the cut may fall from p_cut to c', then again from the new
+ * count, ... (a few counting passes), and the candidate list shrinks from |{p <= p_cut}| to about the rows that matter.
+ * dk_ttest_count_le counts this object's rows; dk_ttest_candidates_narrowed builds the list at the narrowed cut while
+ * keeping p_cut as the bound up to which adjusted values are exact (what dk_ttest_filter checks). */
+int dk_ttest_count_le(dk_ctx *ctx, const dk_ttest *t, double cut, uint64_t *n);
+double dk_bh_next_cut(double p_cut, uint64_t n_le_cut_global, uint64_t R_global);
+int dk_ttest_candidates_narrowed(dk_ctx *ctx, dk_ttest *t, double cut, double p_cut, uint64_t *n_cand, const double **cand_p_dev);
 /* Scalable multi-GPU BH: after the all-gather every rank takes ONE p-value range of the candidates (equal p-values
  * always share a range), ranks it with dk_bh_rank_slice (n_below = candidates below the range), lowers F by the
  * minimum F of all higher ranges, all-gathers (sorted p, F) in range order and applies them to its own rows. */

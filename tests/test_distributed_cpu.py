@@ -87,8 +87,19 @@ class OracleBackend:
     def ttest_rows(self, nf, idxA, idxB):
         self.p, _, _, self.fc = self.orc.ttest_rows(self.mc, nf, idxA, idxB)
 
-    def candidates(self, p_cut):
-        self.cand = np.nonzero(self.p <= p_cut)[0]
+    device = torch.device("cpu")
+
+    def count_le(self, cut):
+        return int((self.p <= cut).sum())
+
+    def next_cut(self, p_cut, n_global, R_global):                 # the rule of dk_bh_next_cut (csrc/dk_bh.cu)
+        if not (p_cut < 1.0) or R_global == 0:
+            return p_cut
+        return p_cut * (n_global / R_global) * (1.0 + 1e-8) + 1e-300
+
+    def candidates(self, p_cut, cut=None):
+        self.cand = np.nonzero(self.p <= (p_cut if cut is None else min(cut, p_cut)))[0]
+        self.narrowed_to = cut
         return torch.from_numpy(self.p[self.cand].copy())
 
     def adjust_global(self, all_p, R_global):
