@@ -36,7 +36,7 @@ CONFIGS = {
 PMAX, FMIN = 0.05, 0.0
 
 
-MERGE_KERNEL_NAME = {"5": "k_merge5", "4": "k_merge4", "3": "k_merge3", "2": "k_merge2", "1": "k_merge"}
+MERGE_KERNEL_NAME = {"5": "k_merge5", "4": "k_merge4", "3": "k_merge3", "1": "k_merge"}
 
 
 def parse():

@@ -349,7 +349,6 @@ __global__ void __launch_bounds__(128) k_merge(MergeParams P)
     }
 }
 
-#include "dk_merge2.cuh"
 #include "dk_merge3.cuh"
 #include "dk_merge4.cuh"
 #include "dk_merge5.cuh"
@@ -474,7 +473,7 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     T.n = (const uint64_t *)(tab + (size_t)S * 16);
 
     // kernel choice: v4 (bucket join, S <= 64) by default, v3 (merge-path tree, any S) otherwise and whenever a dump
-    // holds copies of a k-mer; DK_MERGE=1|2|3 forces the older kernels (profiling)
+    // holds copies of a k-mer; DK_MERGE=1|3|4 forces the older kernels (profiling, tests)
     size_t budget = ctx->smem_optin ? ctx->smem_optin : 227 * 1024;
     int which = 5;
     bool auto_pick = true;           // v4 hands sparse unions to v3 after a probe of the data (below) unless DK_MERGE forces a kernel
@@ -490,7 +489,7 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
     if (which == 4 && !m4_make_cfg(S, budget, G4)) which = 3;
     const bool have3 = m3_make_cfg(S, budget, G3);
     if (which == 3 && !have3) which = 1;
-    if (which == 2 && S > M2_S) which = 1;
+    if (which == 2) which = 1;                                          // v2 (thread per key range) was removed in round 2
 
     // ---- K1: partitions of ~PART_TARGET records (v3 consumes ~4K records per round: longer partitions
     //      amortise the partial last round)
@@ -636,14 +635,6 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
                     if (per_sm < 1) per_sm = 1;
                     if (per_sm > 3) per_sm = 3;
                     k3<<<clampg(ctx->sm_count * per_sm), M3_NT, G3.smem_bytes, ctx->stream>>>(P, G3, overflow_d);
-                    e = cudaGetLastError();
-                }
-            } else if (wk == 2) {
-                e = cudaFuncSetAttribute(k_merge2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M2Smem));
-                if (e == cudaSuccess) {
-                    int per_sm = (int)(budget / (sizeof(M2Smem) + 1024));
-                    if (per_sm < 1) per_sm = 1;
-                    k_merge2<<<ctx->sm_count * per_sm, M2_NT, sizeof(M2Smem), ctx->stream>>>(P);
                     e = cudaGetLastError();
                 }
             } else if (cfg.gw == 16) e = launch_merge<16, 1, 8, 4>(ctx, P, warps, grid, smem);
