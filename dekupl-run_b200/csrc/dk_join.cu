@@ -694,10 +694,10 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
             uint32_t pr[12];
             cudaMemcpy(pr, scal + 4, sizeof pr, cudaMemcpyDeviceToHost);
             double tot = 0;
-            for (int i = 1; i < 9; i++) tot += pr[i];
-            fprintf(stderr, "[m5 prof] kernel %.3f ms; phase shares: tma wait %.3f pivot %.3f copy-out %.3f table %.3f classify+light %.3f "
+            for (int i = 1; i < 10; i++) tot += pr[i];
+            fprintf(stderr, "[m5 prof] kernel %.3f ms; phase shares: tma wait %.3f pivot(warp 0) %.3f B1 wait %.3f copy-out %.3f table %.3f classify+light %.3f "
                     "simple rows %.3f complex rows %.3f scan+alloc %.3f\n",
-                    ms, pr[1] / tot, pr[2] / tot, pr[3] / tot, pr[4] / tot, pr[5] / tot, pr[6] / tot, pr[7] / tot, pr[8] / tot);
+                    ms, pr[1] / tot, pr[9] / tot, pr[2] / tot, pr[3] / tot, pr[4] / tot, pr[5] / tot, pr[6] / tot, pr[7] / tot, pr[8] / tot);
         }
 #endif
 #ifdef DK_M4_PROF

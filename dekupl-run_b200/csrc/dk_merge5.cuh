@@ -246,26 +246,9 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
 #ifdef DK_M5_PROF
             if (tid == 0) tprev = clock64();
 #endif
-            m5_mbar_wait(bar, phase);
-            phase ^= 1u;
-            M5_MARK(1);
-            // R1 (warp 0 alone): pivot = smallest look-ahead key, base = smallest first key
-            if (warp == 0) {
-                unsigned long long candk = DK_SENTINEL, firstk = DK_SENTINEL, lastk = 0;
-                uint32_t ncm = 0;
-                if (owner && o_L) {
-                    const unsigned long long *kw = bufK + (size_t)tid * ks + o_lo;
-                    firstk = kw[0];
-                    if (o_L == o_cap + 1u) { candk = kw[o_cap]; ncm = o_cap; } else ncm = o_L;
-                    lastk = kw[ncm - 1];
-                }
-                candk = m5_warp_min64(candk);
-                firstk = m5_warp_min64(firstk);
-                lastk = m5_warp_max64(lastk);
-                if (firstk != DK_SENTINEL && lastk + 1ull < candk) candk = lastk + 1ull;   // span of the keys staged
-                if (lane < SP) ss.ncm[lane] = ncm;
-                if (lane == 0) { sm.pivot = candk; sm.base = firstk; }
-            }
+#ifdef M5_OVERLAP
+            // the chunk bookkeeping is published one barrier early, so that warps 1..7 copy the previous round's rows out
+            // WHILE warp 0 waits for the windows and computes the pivot (a single warp's dependent chain: 10 % of a round)
             if (tid == M5_BK) {   // chunk bookkeeping on warp 1: warp 0 is the round's critical path (pivot, copy issue)
                 uint32_t cpn = 0;
                 if (pend) {
@@ -286,16 +269,66 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                 }
                 sm.cp_nout = cpn;
             }
+            __syncthreads();                                            // B0
+            if (warp == 0) m5_mbar_wait(bar, phase);
+#else
+            m5_mbar_wait(bar, phase);
+#endif
+            M5_MARK(1);
+            // R1 (warp 0 alone): pivot = smallest look-ahead key, base = smallest first key
+            if (warp == 0) {
+                unsigned long long candk = DK_SENTINEL, firstk = DK_SENTINEL, lastk = 0;
+                uint32_t ncm = 0;
+                if (owner && o_L) {
+                    const unsigned long long *kw = bufK + (size_t)tid * ks + o_lo;
+                    firstk = kw[0];
+                    if (o_L == o_cap + 1u) { candk = kw[o_cap]; ncm = o_cap; } else ncm = o_L;
+                    lastk = kw[ncm - 1];
+                }
+                candk = m5_warp_min64(candk);
+                firstk = m5_warp_min64(firstk);
+                lastk = m5_warp_max64(lastk);
+                if (firstk != DK_SENTINEL && lastk + 1ull < candk) candk = lastk + 1ull;   // span of the keys staged
+                if (lane < SP) ss.ncm[lane] = ncm;
+                if (lane == 0) { sm.pivot = candk; sm.base = firstk; }
+            }
+#ifndef M5_OVERLAP
+            if (tid == M5_BK) {   // chunk bookkeeping on warp 1: warp 0 is the round's critical path (pivot, copy issue)
+                uint32_t cpn = 0;
+                if (pend) {
+                    for (uint32_t k = 0; k < a_nnew; k++) {
+                        const uint32_t id = a_nb + k;
+                        if (id < P.max_chunks) { P.chunk_part[id] = part; P.chunk_seq[id] = sm.seq + k; P.chunk_rows[id] = DK_CH; }
+                    }
+                    sm.cp_have = a_have; sm.cp_nb = a_nb; sm.cp_rp = a_have ? sm.rowpos : 0u; sm.cp_ccur = sm.chunk_cur;
+                    cpn = p_nout;
+                    const uint32_t v = (a_have ? sm.rowpos : 0u) + p_nout;
+                    if (a_nnew) {
+                        sm.chunk_cur = a_nb + a_nnew - 1;
+                        sm.seq += a_nnew;
+                        sm.rowpos = v - (a_have + a_nnew - 1) * DK_CH;
+                    } else sm.rowpos = v;
+                    if (sm.chunk_cur != CHUNK_NONE && sm.rowpos == DK_CH) { sm.chunk_cur = CHUNK_NONE; sm.rowpos = 0; }
+                    pend = false;
+                }
+                sm.cp_nout = cpn;
+            }
+            M5_MARK(9);
             __syncthreads();                                            // B1
             M5_MARK(2);
+            const uint32_t cw = (uint32_t)tid, cn = M5_NT;              // every thread copies out
             // the previous round's rows go out now: staging, bpos and the copy descriptor are rewritten behind B3 / B4 only
             {
+#else
+            const uint32_t cw = (uint32_t)tid - 32u, cn = M5_NT - 32u;  // warps 1..7 copy out, beside warp 0's pivot
+            if (warp != 0) {
+#endif
                 const uint32_t nprev = sm.cp_nout;
                 if (nprev) {
                     const uint32_t have = sm.cp_have, nb = sm.cp_nb, rp = sm.cp_rp, ccur = sm.cp_ccur;
                     if (G.S4) {
                         const uint32_t S4 = G.S4, n4 = nprev * S4;
-                        for (uint32_t i = tid; i < n4; i += M5_NT) {
+                        for (uint32_t i = cw; i < n4; i += cn) {
                             const uint32_t rr = S4 == 1 ? i : __umulhi(i, G.divS4), c4 = i - rr * S4;
                             const uint32_t meta = smeta[rr];
                             const uint32_t v = rp + (uint32_t)bpos[meta & 0xffffu] + (meta >> 16), k = v / DK_CH, off = v % DK_CH;
@@ -305,7 +338,7 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                                 reinterpret_cast<int4 *>(P.out_cnts + ((size_t)chunk * DK_CH + off) * S)[c4] = make_int4(src[0], src[1], src[2], src[3]);
                         }
                     } else {
-                        for (uint32_t rr = tid / 32u; rr < nprev; rr += M5_NT / 32u) {
+                        for (uint32_t rr = cw / 32u; rr < nprev; rr += cn / 32u) {
                             const uint32_t meta = smeta[rr];
                             const uint32_t v = rp + (uint32_t)bpos[meta & 0xffffu] + (meta >> 16), k = v / DK_CH, off = v % DK_CH;
                             const uint32_t chunk = (have && k == 0) ? ccur : nb + (k - have);
@@ -313,7 +346,7 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                                 for (uint32_t c = lane; c < (uint32_t)S; c += 32u) P.out_cnts[((size_t)chunk * DK_CH + off) * S + c] = stage[rr * RS + c];
                         }
                     }
-                    for (uint32_t rr = tid; rr < nprev; rr += M5_NT) {
+                    for (uint32_t rr = cw; rr < nprev; rr += cn) {
                         const uint32_t meta = smeta[rr];
                         const uint32_t v = rp + (uint32_t)bpos[meta & 0xffffu] + (meta >> 16), k = v / DK_CH, off = v % DK_CH;
                         const uint32_t chunk = (have && k == 0) ? ccur : nb + (k - have);
@@ -321,6 +354,13 @@ __global__ void __launch_bounds__(M5_NT, M5_CTAS) k_merge5(MergeParams P, M5Cfg 
                     }
                 }
             }
+#ifdef M5_OVERLAP
+            if (warp != 0) m5_mbar_wait(bar, phase);                    // every thread observes the copies itself
+            M5_MARK(9);
+            __syncthreads();                                            // B1
+            M5_MARK(2);
+#endif
+            phase ^= 1u;
             M5_MARK(3);
             unsigned long long pivot = sm.pivot;
             const unsigned long long base = sm.base;

@@ -460,7 +460,7 @@ extern "C" int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf, 
     for (int s = 0; s < S; s++) if (!(nf[s] >= 1e-30 && nf[s] <= 1e30)) nf_ok = false;
     const char *force_old = getenv("DK_TTEST_OLD");
     if (ident && nf_ok && nA <= TT8_N && nB <= TT8_N && nA + nB <= S && !(force_old && atoi(force_old)) &&
-        (size_t)S * TT8_TN * 16 + 16 * S + (size_t)TT8_THREADS * 104 + 1024 <= 110 * 1024) {
+        (size_t)S * TT8_TN * 16 + 16 * S + (size_t)TT8_THREADS * 104 + 1024 <= (size_t)(227 * 1024) / TT8_MINB - 1024) {
         double2 *tab2 = (double2 *)dk_dev_alloc(ctx, sizeof(double2) * (size_t)S * TT8_TN2);
         if (!tab2) { dk_ttest_release(ctx, t); return DK_ERR_NOMEM; }
         k_tt8_table<<<(unsigned)(((size_t)S * TT8_TN2 + 255) / 256), 256, 0, st>>>(t->nf_dev, S, tab2); DK_LAUNCHED(ctx);

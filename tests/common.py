@@ -25,11 +25,33 @@ def dec(v, k):
     return "".join(BASES[(v >> (2 * (k - 1 - i))) & 3] for i in range(k))
 
 
+_LUT = np.full(256, 255, np.uint8)
+for _i, _c in enumerate(b"ACGT"):
+    _LUT[_c] = _i
+
+
+def enc_many(kmers):
+    """packed uint64 keys of a list of equal-length ACGT strings (vectorised enc)"""
+    if not kmers:
+        return np.zeros(0, np.uint64)
+    k = len(kmers[0])
+    a = np.frombuffer("".join(kmers).encode(), np.uint8)
+    if len(a) != k * len(kmers):
+        return np.array([enc(s) for s in kmers], dtype=np.uint64)            # ragged input: the slow exact way
+    codes = _LUT[a].reshape(len(kmers), k)
+    if (codes == 255).any():
+        raise KeyError("non-ACGT base in a k-mer")
+    v = np.zeros(len(kmers), np.uint64)
+    for j in range(k):
+        v = (v << np.uint64(2)) | codes[:, j].astype(np.uint64)
+    return v
+
+
 def parse_dump_text(txt):
     t = txt.split()
     kmers, cnts = t[0::2], t[1::2]
     k = len(kmers[0]) if kmers else 0
-    return np.array([enc(s) for s in kmers], dtype=np.uint64), np.array([int(c) for c in cnts], dtype=np.int32), k
+    return enc_many(kmers), np.array(cnts, dtype=np.int64).astype(np.int32) if cnts else np.zeros(0, np.int32), k
 
 
 def format_join(keys, cnts, k):

@@ -94,9 +94,8 @@ def _mask_keys():
 
 def _table(path):
     rows = [l.split("\t") for l in gzip.open(path, "rt").read().strip().split("\n")[1:]]
-    from common import enc
-    return (np.array([enc(r[0]) for r in rows], np.uint64), np.array([[int(x) for x in r[1:]] for r in rows], np.int32),
-            [r[0] for r in rows])
+    from common import enc_many
+    return (enc_many([r[0] for r in rows]), np.array([r[1:] for r in rows], dtype=np.int64).astype(np.int32), [r[0] for r in rows])
 
 
 def test_oracle_antijoin_equals_diffFilter_pl_output():
