@@ -51,6 +51,8 @@ def parse():
     ap.add_argument("--nf-from", default="sweep", choices=["auto", "sweep"],
                     help="config 4: computeNF factors from the head of the table when its early stop fires there (auto), or always from a first sweep over the all-positive rows")
     ap.add_argument("--chunk-records", type=int, default=1_000_000_000, help="config 4: records per streamed chunk (12 B each, two chunks in flight)")
+    ap.add_argument("--sharded-impl", default="c", choices=["c", "torch"],
+                    help="N > 1: the multi-GPU driver — dk_run_path_sharded (NCCL inside the library) or distributed.run_sharded (torch.distributed)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the full-size invariants and the seeded-sample oracle check")
@@ -591,6 +593,16 @@ def run_ours(args):
     if world == 1:
         def step():
             return ctx.run_path(kp, cp, n, True, cfg["r"], cfg["a"], nf_mode, idxA, idxB, PMAX, FMIN, nf_text_roundtrip=True)
+    elif args.sharded_impl == "c":
+        # the communicator lives under the C ABI: rank 0's unique id reaches the other ranks through the launcher's process group
+        uid = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            uid = torch.tensor(list(ctx.comm_unique_id()), dtype=torch.uint8, device=dev)
+        dist.broadcast(uid, src=0)
+        ctx.comm_init(bytes(uid.cpu().tolist()), rank, world)
+
+        def step():
+            return ctx.run_path_sharded(kp, cp, n, True, cfg["r"], cfg["a"], nf_mode, idxA, idxB, PMAX, FMIN, nf_text_roundtrip=True)
     else:
         from dekupl_run_b200.distributed import GpuBackend, run_sharded
         be = GpuBackend(ctx, dev)
@@ -658,13 +670,14 @@ def run_ours(args):
     stage_avg = stage / args.steps
     if world > 1:       # BH runs as several calls around the collectives there: report what the other stages leave of the step
         stage_avg[3] = max(0.0, ms - stage_avg[0] - stage_avg[1] - stage_avg[2])
+        out_driver = "dk_run_path_sharded (NCCL inside libdekupl_b200.so)" if args.sharded_impl == "c" else "distributed.run_sharded (torch.distributed)"
     out = {
         "metric": "union k-mers/s merged+tested", "value": value, "unit": "k-mers/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None,
         "dtype": "u64 keys / i32 counts / f64 statistics", "data": "synthetic",
         "config": {"workload": cfg["name"] + (f" (scale {args.scale})" if args.scale != 1.0 else ""), "rows_per_gpu": rows_rank,
                    "union_kmers": U, "records": n_rec_all, "filtered_rows": R, "survivors": stats["D"],
-                   "nf_mode": args.nf, "pmax": PMAX, "l2": "inputs (%.1f GB/GPU) far larger than the 126 MB L2" % (12 * n_rec / 1e9),
+                   "nf_mode": args.nf, "pmax": PMAX, **({"multi_gpu_driver": out_driver} if world > 1 else {}), "l2": "inputs (%.1f GB/GPU) far larger than the 126 MB L2" % (12 * n_rec / 1e9),
                    "gen_s": round(t_gen, 1), "ties": list(stats["ties"]),
                    **({"shards": "k-mer ranges with equal record counts (dk_key_splitters on a 1-in-%d row sample)" % max(1, rows_total // 250_000),
                        "records_rank0": n_rec} if world > 1 else {})},
@@ -774,6 +787,13 @@ def parity_checks(args, cfg, ctx, dev, rank, world, dist, keys, cnts, kp, cp, n,
         if t is not None:
             t.free()
         m.free()
+    elif args.sharded_impl == "c":
+        st, m, t = ctx.run_path_sharded(kp, cp, n, True, cfg["r"], cfg["a"], nf_mode, idxA, idxB, PMAX, FMIN, nf_text_roundtrip=True, keep=True)
+        gx, gs = m.checksum()
+        gU, gR = st["U_local"], st["R_local"]
+        if t is not None:
+            t.free()
+        m.free()
     else:
         from dekupl_run_b200.distributed import GpuBackend, run_sharded
         be = GpuBackend(ctx, dev)
@@ -814,10 +834,21 @@ def parity_checks(args, cfg, ctx, dev, rank, world, dist, keys, cnts, kp, cp, n,
     else:
         # reference-mode NF needs its million-row steps inside rank 0's shard: the small sample uses the shard-symmetric full mode
         sample_nf_mode = "full"
-        be = GpuBackend(ctx, dev)
-        st = run_sharded(be, skp, scp, sn, cfg["r"], cfg["a"], idxA, idxB, PMAX, FMIN, nf_mode=sample_nf_mode, device=dev)
-        gx, gs = be.m.checksum()
-        surv = be.t.export_survivors()
+        be = None
+        if args.sharded_impl == "c":
+            st, m_s, t_s = ctx.run_path_sharded(skp, scp, sn, True, cfg["r"], cfg["a"], dk.NF_FULL, idxA, idxB, PMAX, FMIN,
+                                                nf_text_roundtrip=True, keep=True)
+            gx, gs = m_s.checksum()
+            surv = t_s.export_survivors() if t_s is not None else {"key": np.zeros(0, np.uint64), "p_adj": np.zeros(0)}
+            if t_s is not None:
+                t_s.free()
+            m_s.free()
+        else:
+            from dekupl_run_b200.distributed import GpuBackend, run_sharded
+            be = GpuBackend(ctx, dev)
+            st = run_sharded(be, skp, scp, sn, cfg["r"], cfg["a"], idxA, idxB, PMAX, FMIN, nf_mode=sample_nf_mode, device=dev)
+            gx, gs = be.m.checksum()
+            surv = be.t.export_survivors()
         loc = torch.tensor([gx & 0x7FFFFFFFFFFFFFFF, gx >> 63, gs & 0x7FFFFFFFFFFFFFFF, gs >> 63,
                             _xor_fold(surv["key"]) & 0x7FFFFFFFFFFFFFFF, _xor_fold(surv["key"]) >> 63], dtype=torch.int64, device=dev)
         allv = [torch.zeros_like(loc) for _ in range(world)]
@@ -828,7 +859,8 @@ def parity_checks(args, cfg, ctx, dev, rank, world, dist, keys, cnts, kp, cp, n,
         g = dict(U=st["U"], R=st["R"], D=st["D"], key_xor=_xor_fold(v[0] | (v[1] << 63) for v in allv),
                  count_sum=sum(v[2] | (v[3] << 63) for v in allv) & M64, nf=[float(x) for x in st["nf"]],
                  surv_xor=_xor_fold(v[4] | (v[5] << 63) for v in allv), surv_adj_sum=float(adj.item()))
-        be.free()
+        if be is not None:
+            be.free()
     del sk, sc
     if rank == 0:
         ck, cc = make_cpu_sample(cfg, rows, **PARITY_EFF)

@@ -101,6 +101,10 @@ def load_library():
                                  P(StreamStats), P(vp), P(vp)]),
         "dk_run_path_matrix_out": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, i32, P(i32), i32, P(i32), i32, dbl, dbl, i32,
                                          vp, vp, u64, P(u64), P(PathStats), P(vp), P(vp)]),
+        "dk_comm_unique_id": (i32, [vp, vp]), "dk_comm_init": (i32, [vp, vp, i32, i32]), "dk_comm_free": (None, [vp]),
+        "dk_comm_rank": (i32, [vp]), "dk_comm_world": (i32, [vp]),
+        "dk_run_path_sharded": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, i32, P(i32), i32, P(i32), i32, dbl, dbl, i32,
+                                      P(PathStats), P(u64), P(vp), P(vp)]),
         "dk_run_path": (i32, [vp, i32, P(vp), P(vp), P(u64), i32, i32, i32, i32, P(i32), i32, P(i32), i32, dbl, dbl, i32,
                               P(PathStats), P(vp), P(vp)]),
     }
@@ -412,6 +416,40 @@ class Context:
         out, info = C.c_void_p(0), (C.c_uint64 * 3)()
         self._chk(self.L.dk_poisson_rows(self.h, m.h, a, len(idxA), b, len(idxB), C.byref(out), info))
         return TtestResult(self, out, m), tuple(int(x) for x in info)
+
+    # ---- several GPUs: an NCCL communicator owned by the context ----------------------
+    def comm_unique_id(self):
+        """rank 0: the bytes every rank passes to comm_init (hand them over by any means)"""
+        buf = (C.c_ubyte * 128)()
+        self._chk(self.L.dk_comm_unique_id(self.h, buf))
+        return bytes(buf)
+
+    def comm_init(self, uid, rank, world):
+        buf = (C.c_ubyte * 128).from_buffer_copy(uid)
+        self._chk(self.L.dk_comm_init(self.h, buf, int(rank), int(world)))
+
+    def comm_free(self):
+        self.L.dk_comm_free(self.h)
+
+    def run_path_sharded(self, key_ptrs, cnt_ptrs, n, device_inputs, min_rec, min_abund, nf_mode, idxA, idxB, pmax, fmin,
+                         nf_text_roundtrip=True, keep=False):
+        """dk_run_path on this rank's shard, global pieces by NCCL inside the library; stats are GLOBAL (+ *_local)"""
+        S, kp, cp, nn = self._tables(key_ptrs, cnt_ptrs, n)
+        a, b = (C.c_int * len(idxA))(*idxA), (C.c_int * len(idxB))(*idxB)
+        st, loc, om, ot = PathStats(), (C.c_uint64 * 3)(), C.c_void_p(0), C.c_void_p(0)
+        self._chk(self.L.dk_run_path_sharded(self.h, S, kp, cp, nn, int(device_inputs), min_rec, min_abund, nf_mode, a, len(idxA), b,
+                                             len(idxB), float(pmax), float(fmin), int(nf_text_roundtrip), C.byref(st), loc,
+                                             C.byref(om) if keep else None, C.byref(ot) if keep else None))
+        stats = dict(U=int(st.U), R=int(st.R), R_pos=int(st.R_pos), D=int(st.D), ties=tuple(int(x) for x in st.ties),
+                     nf=np.array(st.nf[:S]), ms_join=st.ms_join, ms_nf=st.ms_nf, ms_ttest=st.ms_ttest, ms_bh=st.ms_bh,
+                     U_local=int(loc[0]), R_local=int(loc[1]), D_local=int(loc[2]))
+        if keep:
+            m = Matrix(self, om)
+            t = TtestResult(self, ot, m) if ot.value else None
+            if t is not None:
+                t.D, t.ties = stats["D_local"], stats["ties"]
+            return stats, m, t
+        return stats
 
     # ---- chunk-streamed path (host dumps larger than device memory) ----------------
     def stream_nf_reference(self, key_ptrs, cnt_ptrs, n, min_rec, min_abund, chunk_records, step_rows=0, widen=True):

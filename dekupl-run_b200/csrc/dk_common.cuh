@@ -27,6 +27,9 @@ struct dk_ctx {
     std::map<void *, size_t> live;
     size_t cached_bytes = 0;
     uint64_t chunk_hint = 0;      // matrix chunks the previous join of THIS context needed (sizes the next one)
+    // multi-GPU (dk_comm.cu): an NCCL communicator owned by the context; world == 1 without one
+    void *comm = nullptr;
+    int rank = 0, world = 1;
 };
 
 int dk_fail(dk_ctx *ctx, int code, const char *fmt, ...);

@@ -55,6 +55,7 @@ extern "C" void dk_free(dk_ctx *ctx)
 {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
+    dk_comm_free(ctx);
     cudaStreamSynchronize(ctx->stream);
     dk_dev_trim(ctx);
     for (auto &kv : ctx->live) cudaFree(kv.first);

@@ -266,6 +266,30 @@ int dk_run_path_masked(dk_ctx *ctx, int S, const uint64_t *const *keys, const in
                        dk_path_stats *stats, uint64_t *rows_masked /* may be NULL */,
                        dk_matrix **out_matrix /* may be NULL */, dk_ttest **out_test /* may be NULL */);
 
+/* ---- several GPUs, one process per GPU ("NCCL over NVLink only for the global pieces") -----------
+ * The reference is one process; these calls have no counterpart there. The context can own an NCCL communicator:
+ * rank 0 calls dk_comm_unique_id and hands the DK_COMM_ID_BYTES to every rank by any means (a file, MPI, a socket,
+ * torch.distributed); every rank then calls dk_comm_init (collective). NCCL is resolved with dlopen("libnccl.so.2") at
+ * that moment; single-GPU callers never need it. Rank order must be k-mer order: rank g owns the slice of every sorted
+ * dump between two boundaries of dk_key_splitters.
+ * dk_run_path_sharded is dk_run_path on this rank's shard with the global pieces done by NCCL inside: R and U (one
+ * all-reduce), computeNF's factors (reference mode: rank 0's prefix + one broadcast, DK_ERR_UNSUPPORTED on every rank if
+ * its early stop does not fire inside rank 0's shard; full mode: one all-reduce of S*256 bins per radix round), BH
+ * (candidate narrowing over global counts, then an all-gather of the few candidates left) and D. stats holds the GLOBAL
+ * U, R, D, ties and the NFs on every rank; local_URD (may be NULL) this rank's U, R, D; *out_matrix / *out_test this
+ * rank's shard (row indices are local). Without a communicator it is dk_run_path. */
+#define DK_COMM_ID_BYTES 128
+int dk_comm_unique_id(dk_ctx *ctx, unsigned char *id /* out [DK_COMM_ID_BYTES] */);
+int dk_comm_init(dk_ctx *ctx, const unsigned char *id, int rank, int world);
+void dk_comm_free(dk_ctx *ctx);
+int dk_comm_rank(const dk_ctx *ctx);
+int dk_comm_world(const dk_ctx *ctx);
+int dk_run_path_sharded(dk_ctx *ctx, int S, const uint64_t *const *keys, const int32_t *const *cnts, const uint64_t *n,
+                        int device_inputs, int min_rec, int min_abund, int nf_mode,
+                        const int *idxA, int nA, const int *idxB, int nB, double pmax, double fmin,
+                        int nf_text_roundtrip, dk_path_stats *stats, uint64_t *local_URD /* [3], may be NULL */,
+                        dk_matrix **out_matrix /* may be NULL */, dk_ttest **out_test /* may be NULL */);
+
 /* ---- chunk-streamed path: dumps larger than device memory, kept in (pinned) HOST memory -----------------------
  * The reference streams too: joinCounts holds one record per input (joinCounts.c:43-69), TtestFilter reads the table
  * row by row (TtestFilter.c:340-444). Here the key space is cut into chunks of about chunk_records records (all dumps

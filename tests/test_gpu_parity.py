@@ -767,3 +767,39 @@ def test_run_path_matrix_out_returns_the_matrix_in_reference_order(ctx, slices, 
     with pytest.raises(dk.DkError, match="host buffers hold"):
         ctx.run_path_matrix_out(kp, cp, n, device_inputs, 2, 5, dk.NF_REFERENCE, list(range(nA)), list(range(nA, S)), 0.05, 0.0,
                                 hk.ctypes.data, hc.ctypes.data, 100)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nf_mode", ["reference", "full"])
+def test_run_path_sharded_under_the_c_abi_one_rank_communicator(nf_mode):
+    """dk_comm_* + dk_run_path_sharded with a ONE-rank NCCL communicator: every collective of the C driver runs (all-reduce,
+    broadcast, the radix-select histogram all-reduce) and the result must equal dk_run_path and the oracle. The N > 1 case
+    is checked against the oracle inside every multi-GPU bench run (parity_check)."""
+    from common import plant_effect
+    c = dk.Context(0)
+    try:
+        c.comm_init(c.comm_unique_id(), 0, 1)
+        assert c.L.dk_comm_world(c.h) == 1 and c.L.dk_comm_rank(c.h) == 0
+        rng = np.random.default_rng(31)
+        S, nA = 8, 4
+        keys, cnts = random_dumps(rng, S, 150_000, 62, 0.15, 60, p_core=0.3)
+        cnts = plant_effect(rng, keys, cnts, set(range(nA, S)))
+        kp, cp, n = [k.ctypes.data for k in keys], [x.ctypes.data for x in cnts], [len(k) for k in keys]
+        mode = dk.NF_REFERENCE if nf_mode == "reference" else dk.NF_FULL
+        st, m, t = c.run_path_sharded(kp, cp, n, False, 2, 5, mode, list(range(nA)), list(range(nA, S)), 0.05, 0.0, keep=True)
+        ok, oc, oU = orc.join(keys, cnts, 2, 5)
+        onf = orc.nf_reference(oc)[0] if nf_mode == "reference" else orc.nf_full(oc)
+        assert (st["U"], st["R"], st["U_local"], st["R_local"]) == (oU, len(ok), oU, len(ok))
+        np.testing.assert_allclose(st["nf"], onf, rtol=RTOL)
+        op, _, _, _ = orc.ttest_rows(oc, np.array([float("%f" % v) for v in onf]), list(range(nA)), list(range(nA, S)))
+        oadj = orc.bh(op)
+        keep = np.nonzero(oadj <= 0.05)[0]
+        sv = t.export_survivors()
+        assert st["D"] == len(keep) > 50 and np.array_equal(sv["row"].astype(np.int64), keep)
+        np.testing.assert_allclose(sv["p_adj"], oadj[keep], rtol=RTOL, atol=1e-300)
+        st1 = c.run_path(kp, cp, n, False, 2, 5, mode, list(range(nA)), list(range(nA, S)), 0.05, 0.0)
+        assert (st1["U"], st1["R"], st1["D"]) == (st["U"], st["R"], st["D"])
+        t.free(); m.free()
+        c.comm_free()
+    finally:
+        c.close()

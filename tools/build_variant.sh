@@ -9,8 +9,8 @@ FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompil
 mkdir -p ../../build/var
 $NVCC $FLAGS $FLAGS_X -c $F.cu -o ../../build/var/${F}_$NAME.o 2>&1 | grep -v deprecated || true
 OBJS=""
-for f in dk_ctx dk_join dk_nf dk_ttest dk_sort dk_bh dk_filter dk_mask dk_format dk_ingest dk_tags dk_api; do
+for f in dk_ctx dk_join dk_nf dk_ttest dk_sort dk_bh dk_filter dk_mask dk_format dk_ingest dk_tags dk_api dk_comm; do
   if [ $f = $F ]; then OBJS="$OBJS ../../build/var/${F}_$NAME.o"; else OBJS="$OBJS build/$f.o"; fi
 done
-$NVCC -shared -o ../../build/var/lib_$NAME.so $OBJS -cudart static 2>&1 | grep -v deprecated || true
+$NVCC -shared -o ../../build/var/lib_$NAME.so $OBJS -cudart static -ldl 2>&1 | grep -v deprecated || true
 echo built build/var/lib_$NAME.so
