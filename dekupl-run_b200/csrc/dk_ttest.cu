@@ -239,9 +239,9 @@ __global__ void k_tt8_table(const double *nf_g, int S, double2 *tab2)
 }
 
 __device__ __forceinline__ void tt8_lookup(int32_t cc, int k, const double2 *tab, const double2 *tab2, const double *nf,
-                                           const double *rnf, double &a, double &l)
+                                           const double *rnf, double &a, double &l, const uint32_t tn = TT8_TN)
 {
-    if ((uint32_t)cc < TT8_TN) { const double2 t = tab[(uint32_t)k * TT8_TN + (uint32_t)cc]; a = t.x; l = t.y; }
+    if ((uint32_t)cc < tn) { const double2 t = tab[(uint32_t)k * tn + (uint32_t)cc]; a = t.x; l = t.y; }
     else if ((uint32_t)cc < TT8_TN2) { const double2 t = __ldg(tab2 + (size_t)k * TT8_TN2 + (uint32_t)cc); a = t.x; l = t.y; }
     else dk_norm_log<true>(cc, nf[k], rnf[k], a, l);
 }
@@ -259,14 +259,18 @@ __device__ __forceinline__ void tt8_lookup(int32_t cc, int k, const double2 *tab
 // VEC (S % 4 == 0, nA % 4 == 0): the tile's rows are fetched by cp.async one tile ahead into a per-thread 64-byte
 // slot (r2i ncu: after the re-binning the kernel waited on its 16 dependent 4-byte count loads, long scoreboard
 // 3.2 per issue), and read back with 16-byte shared loads (slot segments swizzled: conflict-free)
-template <bool VEC>
+// BIG (groups of more than TT8_N samples, cfg 3 / cfg 4): the logs of a group do not fit registers, so the moments take
+// two passes over the row's counts (means, then squared deviations: the table look-ups are cheap next to the fp64 work)
+// and the shared-memory table holds tn <= TT8_TN counts per sample, sized by the host.
+template <bool VEC, bool BIG>
 __global__ void __launch_bounds__(TT8_THREADS, TT8_MINB)
 k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, uint32_t n_chunks, int S, const double *nf_g,
-              const double2 *tab2, int nA, int nB, TT8Consts K, double *p_raw, double *log2fc, unsigned long long *tie_sd)
+              const double2 *tab2, int nA, int nB, TT8Consts K, double *p_raw, double *log2fc, unsigned long long *tie_sd, uint32_t tn_arg)
 {
     extern __shared__ __align__(16) unsigned char sm[];
-    double2 *tab = (double2 *)sm;                                // [S][TT8_TN] (a, l)
-    double *nf = (double *)(tab + (size_t)S * TT8_TN);           // [S]
+    const uint32_t TNv = BIG ? tn_arg : (uint32_t)TT8_TN;
+    double2 *tab = (double2 *)sm;                                // [S][TNv] (a, l)
+    double *nf = (double *)(tab + (size_t)S * TNv);              // [S]
     double *rnf = nf + S;                                        // [S]
     const uint32_t T = blockDim.x, cpb = T / DK_CH;
     double *q_x = rnf + S, *q_v = q_x + T, *q_f = q_v + T, *q_d = q_f + T;   // [T] each: queue of fraction arguments
@@ -287,8 +291,8 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
     for (int i = threadIdx.x; i < S; i += T) { nf[i] = nf_g[i]; rnf[i] = 1.0 / nf_g[i]; }
-    for (uint32_t e = threadIdx.x; e < (uint32_t)S * TT8_TN; e += T) {
-        const uint32_t k = e / TT8_TN, cc = e - k * TT8_TN;
+    for (uint32_t e = threadIdx.x; e < (uint32_t)S * TNv; e += T) {
+        const uint32_t k = e / TNv, cc = e - k * TNv;
         tab[e] = tab2[(size_t)k * TT8_TN2 + cc];
     }
     __syncthreads();
@@ -308,36 +312,46 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
         bool lower = false;
         if (act) {
             const int32_t *c = cnts + ((size_t)order[oc] * DK_CH + j) * (size_t)S;
-            int32_t cA[TT8_N], cB[TT8_N];
-            if (VEC) {
-                asm volatile("cp.async.wait_group 0;" ::: "memory");           // my own copy: no barrier needed
-                const int4 *s4 = reinterpret_cast<const int4 *>(slot);
-                const uint32_t qb = (uint32_t)nA >> 2;
-                const int4 a0 = s4[0 ^ swz], a1 = s4[1 ^ swz], b0v = s4[(qb & 3u) ^ swz], b1v = s4[((qb + 1u) & 3u) ^ swz];
-                cA[0] = a0.x; cA[1] = a0.y; cA[2] = a0.z; cA[3] = a0.w; cA[4] = a1.x; cA[5] = a1.y; cA[6] = a1.z; cA[7] = a1.w;
-                cB[0] = b0v.x; cB[1] = b0v.y; cB[2] = b0v.z; cB[3] = b0v.w; cB[4] = b1v.x; cB[5] = b1v.y; cB[6] = b1v.z; cB[7] = b1v.w;
+            double sa = 0, sb = 0, m1, m2, s1 = 0, s2 = 0;
+            if constexpr (!BIG) {
+                int32_t cA[TT8_N], cB[TT8_N];
+                if (VEC) {
+                    asm volatile("cp.async.wait_group 0;" ::: "memory");           // my own copy: no barrier needed
+                    const int4 *s4 = reinterpret_cast<const int4 *>(slot);
+                    const uint32_t qb = (uint32_t)nA >> 2;
+                    const int4 a0 = s4[0 ^ swz], a1 = s4[1 ^ swz], b0v = s4[(qb & 3u) ^ swz], b1v = s4[((qb + 1u) & 3u) ^ swz];
+                    cA[0] = a0.x; cA[1] = a0.y; cA[2] = a0.z; cA[3] = a0.w; cA[4] = a1.x; cA[5] = a1.y; cA[6] = a1.z; cA[7] = a1.w;
+                    cB[0] = b0v.x; cB[1] = b0v.y; cB[2] = b0v.z; cB[3] = b0v.w; cB[4] = b1v.x; cB[5] = b1v.y; cB[6] = b1v.z; cB[7] = b1v.w;
+                } else {
+    #pragma unroll
+                    for (int i = 0; i < TT8_N; i++) { cA[i] = i < nA ? __ldg(c + i) : 0; cB[i] = i < nB ? __ldg(c + nA + i) : 0; }
+                }
+                // ---- group moments (TtestFilter.c:379-411; sum/mean/sd :77-98), sums sequential in column order
+                double la[TT8_N], sl = 0;
+    #pragma unroll
+                for (int i = 0; i < TT8_N; i++)
+                    if (i < nA) { double a, l; tt8_lookup(cA[i], i, tab, tab2, nf, rnf, a, l); sa += a; sl += l; la[i] = l; }
+                m1 = sl / nA;                           // mean() of the logs: a true division (it decides sd == 0)
+    #pragma unroll
+                for (int i = 0; i < TT8_N; i++) if (i < nA) { const double d = la[i] - m1; s1 += d * d; }
+                sl = 0;
+    #pragma unroll
+                for (int i = 0; i < TT8_N; i++)
+                    if (i < nB) { double a, l; tt8_lookup(cB[i], nA + i, tab, tab2, nf, rnf, a, l); sb += a; sl += l; la[i] = l; }
+                m2 = sl / nB;
+    #pragma unroll
+                for (int i = 0; i < TT8_N; i++) if (i < nB) { const double d = la[i] - m2; s2 += d * d; }
             } else {
-#pragma unroll
-                for (int i = 0; i < TT8_N; i++) { cA[i] = i < nA ? __ldg(c + i) : 0; cB[i] = i < nB ? __ldg(c + nA + i) : 0; }
+                // ---- group moments, two passes (TtestFilter.c:379-411; sum/mean/sd :77-98), sums sequential in column order
+                double sl = 0;
+                for (int i = 0; i < nA; i++) { double a, l; tt8_lookup(__ldg(c + i), i, tab, tab2, nf, rnf, a, l, TNv); sa += a; sl += l; }
+                m1 = sl / nA;
+                for (int i = 0; i < nA; i++) { double a, l; tt8_lookup(__ldg(c + i), i, tab, tab2, nf, rnf, a, l, TNv); const double d = l - m1; s1 += d * d; }
+                sl = 0;
+                for (int i = 0; i < nB; i++) { double a, l; tt8_lookup(__ldg(c + nA + i), nA + i, tab, tab2, nf, rnf, a, l, TNv); sb += a; sl += l; }
+                m2 = sl / nB;
+                for (int i = 0; i < nB; i++) { double a, l; tt8_lookup(__ldg(c + nA + i), nA + i, tab, tab2, nf, rnf, a, l, TNv); const double d = l - m2; s2 += d * d; }
             }
-            // ---- group moments (TtestFilter.c:379-411; sum/mean/sd :77-98), sums sequential in column order
-            double la[TT8_N], sa = 0, sl = 0;
-#pragma unroll
-            for (int i = 0; i < TT8_N; i++)
-                if (i < nA) { double a, l; tt8_lookup(cA[i], i, tab, tab2, nf, rnf, a, l); sa += a; sl += l; la[i] = l; }
-            const double m1 = sl / nA;                           // mean() of the logs: a true division (it decides sd == 0)
-            double s1 = 0;
-#pragma unroll
-            for (int i = 0; i < TT8_N; i++) if (i < nA) { const double d = la[i] - m1; s1 += d * d; }
-            double sb = 0;
-            sl = 0;
-#pragma unroll
-            for (int i = 0; i < TT8_N; i++)
-                if (i < nB) { double a, l; tt8_lookup(cB[i], nA + i, tab, tab2, nf, rnf, a, l); sb += a; sl += l; la[i] = l; }
-            const double m2 = sl / nB;
-            double s2 = 0;
-#pragma unroll
-            for (int i = 0; i < TT8_N; i++) if (i < nB) { const double d = la[i] - m2; s2 += d * d; }
             // ---- Welch (TtestFilter.c:120-150) on sd^2 = s/(n-1)
             double p = 0.5;                                      // sd1 == 0 && sd2 == 0 (:128)
             if (!(s1 == 0 && s2 == 0)) {
@@ -459,14 +473,19 @@ extern "C" int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf, 
     bool nf_ok = true;
     for (int s = 0; s < S; s++) if (!(nf[s] >= 1e-30 && nf[s] <= 1e30)) nf_ok = false;
     const char *force_old = getenv("DK_TTEST_OLD");
-    if (ident && nf_ok && nA <= TT8_N && nB <= TT8_N && nA + nB <= S && !(force_old && atoi(force_old)) &&
-        (size_t)S * TT8_TN * 16 + 16 * S + (size_t)TT8_THREADS * 104 + 1024 <= (size_t)(227 * 1024) / TT8_MINB - 1024) {
+    const bool small_groups = nA <= TT8_N && nB <= TT8_N;
+    uint32_t tn_big = TT8_TN;                                        // large groups: the table shrinks until two CTAs fit an SM
+    while (tn_big > 16 && (size_t)S * tn_big * 16 + 16 * S + (size_t)TT8_THREADS * 40 + 2048 > (size_t)(227 * 1024) / TT8_MINB - 1024) tn_big >>= 1;
+    const bool fits = small_groups ? (size_t)S * TT8_TN * 16 + 16 * S + (size_t)TT8_THREADS * 104 + 1024 <= (size_t)(227 * 1024) / TT8_MINB - 1024
+                                   : (size_t)S * tn_big * 16 + 16 * S + (size_t)TT8_THREADS * 40 + 2048 <= (size_t)(227 * 1024) / TT8_MINB - 1024;
+    if (ident && nf_ok && nA + nB <= S && !(force_old && atoi(force_old)) && fits) {
         double2 *tab2 = (double2 *)dk_dev_alloc(ctx, sizeof(double2) * (size_t)S * TT8_TN2);
         if (!tab2) { dk_ttest_release(ctx, t); return DK_ERR_NOMEM; }
         k_tt8_table<<<(unsigned)(((size_t)S * TT8_TN2 + 255) / 256), 256, 0, st>>>(t->nf_dev, S, tab2); DK_LAUNCHED(ctx);
-        const bool vec = (S % 4 == 0) && (nA % 4 == 0) && S <= 16;
-        auto k8 = vec ? k_ttest_rows8<true> : k_ttest_rows8<false>;
-        const size_t smem8 = (size_t)S * TT8_TN * 16 + 16 * S + (size_t)TT8_THREADS * 40 + (2 * TT8_BINS + 4) * 4 + (vec ? (size_t)TT8_THREADS * 64 : 0);
+        const bool vec = small_groups && (S % 4 == 0) && (nA % 4 == 0) && S <= 16;
+        auto k8 = !small_groups ? k_ttest_rows8<false, true> : (vec ? k_ttest_rows8<true, false> : k_ttest_rows8<false, false>);
+        const uint32_t tn8 = small_groups ? (uint32_t)TT8_TN : tn_big;
+        const size_t smem8 = (size_t)S * tn8 * 16 + 16 * S + (size_t)TT8_THREADS * 40 + (2 * TT8_BINS + 4) * 4 + (vec ? (size_t)TT8_THREADS * 64 : 0);
         DK_CUDA(ctx, cudaFuncSetAttribute(k8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem8));
         const uint32_t nch8 = (uint32_t)m->n_chunks;
         if (nch8) {
@@ -479,7 +498,7 @@ extern "C" int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf, 
             TT8Consts K;
             K.rnA = 1.0 / nA; K.rnB = 1.0 / nB; K.rnA1 = 1.0 / (nA - 1); K.rnB1 = 1.0 / (nB - 1);
             k8<<<grid, TT8_THREADS, smem8, st>>>(m->cnts, m->order, m->lbase, nch8, S, t->nf_dev, tab2, nA, nB, K,
-                                                            t->p_raw, t->log2fc, (unsigned long long *)(t->tie_counts + 2));
+                                                            t->p_raw, t->log2fc, (unsigned long long *)(t->tie_counts + 2), tn8);
             DK_LAUNCHED(ctx);
         }
         DK_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));

@@ -803,3 +803,23 @@ def test_run_path_sharded_under_the_c_abi_one_rank_communicator(nf_mode):
         c.comm_free()
     finally:
         c.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("R,nA,nB", [(20000, 24, 24), (6000, 100, 100), (9000, 9, 31), (4000, 33, 12)])
+def test_ttest_large_groups_fast_kernel_vs_oracle(ctx, R, nA, nB):
+    """groups of more than 8 samples (cfg 3: 24 v 24, cfg 4: 100 v 100, uneven groups): the two-pass variant of the fast row
+    kernel against the oracle — p, log2FC, survivors, adjusted p — and bit-identical to the general kernel's exact tests
+    (p == 0.5 rows)"""
+    rng = np.random.default_rng(R + nA)
+    S = nA + nB
+    base = np.floor(rng.pareto(1.2, size=(R, 1)) * 4 + 1)
+    cnts = rng.poisson(base * rng.uniform(0.5, 2.0, size=(1, S))).astype(np.int32)
+    cnts[rng.random((R, S)) < 0.1] = 0
+    cnts[: R // 25, nA:] *= 3
+    cnts[-20:] = 0                                             # both sds exactly 0
+    cnts[-40:-20, :nA] = 4; cnts[-40:-20, nA:] = 11            # constant groups with different means
+    cnts[R // 2, :] = 2 ** 31 - 1                              # far beyond both tables
+    nf = np.array([float("%f" % v) for v in rng.uniform(0.6, 1.8, S)])
+    D, ties = _ttest_both(ctx, cnts, nf, list(range(nA)), list(range(nA, S)), 0.05, 0.0)
+    assert D > 0
