@@ -53,6 +53,8 @@ def parse():
     ap.add_argument("--chunk-records", type=int, default=1_000_000_000, help="config 4: records per streamed chunk (12 B each, two chunks in flight)")
     ap.add_argument("--sharded-impl", default="c", choices=["c", "torch"],
                     help="N > 1: the multi-GPU driver — dk_run_path_sharded (NCCL inside the library) or distributed.run_sharded (torch.distributed)")
+    ap.add_argument("--key-bursts", type=int, default=1,
+                    help="k-mers in runs of this many consecutive integers separated by gaps (clustered keys) instead of stratified-uniform")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the full-size invariants and the seeded-sample oracle check")
@@ -557,6 +559,7 @@ def run_ours(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    synth.BURST = max(1, args.key_bursts)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -678,7 +681,7 @@ def run_ours(args):
         "config": {"workload": cfg["name"] + (f" (scale {args.scale})" if args.scale != 1.0 else ""), "rows_per_gpu": rows_rank,
                    "union_kmers": U, "records": n_rec_all, "filtered_rows": R, "survivors": stats["D"],
                    "nf_mode": args.nf, "pmax": PMAX, **({"multi_gpu_driver": out_driver} if world > 1 else {}), "l2": "inputs (%.1f GB/GPU) far larger than the 126 MB L2" % (12 * n_rec / 1e9),
-                   "gen_s": round(t_gen, 1), "ties": list(stats["ties"]),
+                   "gen_s": round(t_gen, 1), "ties": list(stats["ties"]), **({"key_bursts": args.key_bursts} if args.key_bursts > 1 else {}),
                    **({"shards": "k-mer ranges with equal record counts (dk_key_splitters on a 1-in-%d row sample)" % max(1, rows_total // 250_000),
                        "records_rank0": n_rec} if world > 1 else {})},
         "gpu_launches": int(launches),

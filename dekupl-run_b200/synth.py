@@ -40,6 +40,10 @@ def sample_depths(S, seed=SEED):
     return (0.5 + 1.5 * torch.rand(S, generator=g, dtype=torch.float64)).tolist()
 
 
+BURST = 1      # > 1: k-mers come in runs of BURST consecutive integers separated by gaps (what low-complexity sequence
+               # and shared prefixes do to a real sorted dump) instead of one stratified-uniform key per stride
+
+
 def _rows(S, U_total, a, b, *, device, model, q, alpha, group_b, seed, eff=4.0, eff_frac=0.01, index=None):
     """rows [a,b) of the implicit union (or the rows listed in `index`): (key, [(present, count) per sample]) — the one
     place the generator is defined"""
@@ -47,7 +51,10 @@ def _rows(S, U_total, a, b, *, device, model, q, alpha, group_b, seed, eff=4.0, 
     depths = sample_depths(S, seed)
     i = torch.arange(a, b, device=device, dtype=torch.int64) if index is None else index
     h = mix64(i + seed)
-    key = i * stride + (_lsr(h, 2) % stride)
+    if BURST > 1:          # row i = member (i % BURST) of run (i // BURST): consecutive k-mers, then a gap of BURST strides
+        key = (i // BURST) * (stride * BURST) + (i % BURST)
+    else:
+        key = i * stride + (_lsr(h, 2) % stride)
     cls = _lsr(mix64(h ^ 0x5851F42D), 40).to(torch.float64) / float(1 << 24)     # row class uniform [0,1)
     effr = _lsr(mix64(h ^ 0x2545F491), 40).to(torch.float64) / float(1 << 24) < eff_frac
     if model == "genome":
