@@ -225,7 +225,7 @@ __device__ __forceinline__ void dk_beta_cf2(double a, double b, double x, double
     Ao = A; Bo = B;
 }
 
-struct TT8Consts { double rnA, rnB, rnA1, rnB1; };   // 1/nA, 1/nB, 1/(nA-1), 1/(nB-1)
+struct TT8Consts { double rnA, rnB, rnA1, rnB1; int p2A, p2B; };   // 1/nA, 1/nB, 1/(nA-1), 1/(nB-1); group size is a power of two
 
 __global__ void k_tt8_table(const double *nf_g, int S, double2 *tab2)
 {
@@ -331,25 +331,26 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
     #pragma unroll
                 for (int i = 0; i < TT8_N; i++)
                     if (i < nA) { double a, l; tt8_lookup(cA[i], i, tab, tab2, nf, rnf, a, l); sa += a; sl += l; la[i] = l; }
-                m1 = sl / nA;                           // mean() of the logs: a true division (it decides sd == 0)
+                m1 = K.p2A ? sl * K.rnA : sl / nA;    // mean() of the logs decides sd == 0: a true division, or for a group of 2^k
+                                                      // samples the exact multiply by 2^-k (same bits)
     #pragma unroll
                 for (int i = 0; i < TT8_N; i++) if (i < nA) { const double d = la[i] - m1; s1 += d * d; }
                 sl = 0;
     #pragma unroll
                 for (int i = 0; i < TT8_N; i++)
                     if (i < nB) { double a, l; tt8_lookup(cB[i], nA + i, tab, tab2, nf, rnf, a, l); sb += a; sl += l; la[i] = l; }
-                m2 = sl / nB;
+                m2 = K.p2B ? sl * K.rnB : sl / nB;
     #pragma unroll
                 for (int i = 0; i < TT8_N; i++) if (i < nB) { const double d = la[i] - m2; s2 += d * d; }
             } else {
                 // ---- group moments, two passes (TtestFilter.c:379-411; sum/mean/sd :77-98), sums sequential in column order
                 double sl = 0;
                 for (int i = 0; i < nA; i++) { double a, l; tt8_lookup(__ldg(c + i), i, tab, tab2, nf, rnf, a, l, TNv); sa += a; sl += l; }
-                m1 = sl / nA;
+                m1 = K.p2A ? sl * K.rnA : sl / nA;
                 for (int i = 0; i < nA; i++) { double a, l; tt8_lookup(__ldg(c + i), i, tab, tab2, nf, rnf, a, l, TNv); const double d = l - m1; s1 += d * d; }
                 sl = 0;
                 for (int i = 0; i < nB; i++) { double a, l; tt8_lookup(__ldg(c + nA + i), nA + i, tab, tab2, nf, rnf, a, l, TNv); sb += a; sl += l; }
-                m2 = sl / nB;
+                m2 = K.p2B ? sl * K.rnB : sl / nB;
                 for (int i = 0; i < nB; i++) { double a, l; tt8_lookup(__ldg(c + nA + i), nA + i, tab, tab2, nf, rnf, a, l, TNv); const double d = l - m2; s2 += d * d; }
             }
             // ---- Welch (TtestFilter.c:120-150) on sd^2 = s/(n-1)
@@ -370,10 +371,13 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
                     else {
                         const double INV_SQRT_PI = 0.56418958354775628695;
                         const double lx = (y < 0.5) ? log1p(-y) : log(x);
+                        // Gamma(v+1/2)/Gamma(v): shift up to w >= 12, then the asymptotic series with 6 terms (the next one,
+                        // 5461/(65536*7) / w^13, is below 1e-16 there; stopping at 12 instead of 20 saves 8 trips of the loop)
                         double num = 1.0, dg = 1.0, w = v;
-                        while (w < 20.0) { num *= w; dg *= (w + 0.5); w += 1.0; }
+                        while (w < 12.0) { num *= w; dg *= (w + 0.5); w += 1.0; }
                         const double r = 1.0 / w, rr = r * r;
-                        const double ser = r * (-1.0 / 8.0 + rr * (1.0 / 192.0 + rr * (-1.0 / 640.0 + rr * (17.0 / 14336.0 + rr * (-31.0 / 18432.0)))));
+                        const double ser = r * (-1.0 / 8.0 + rr * (1.0 / 192.0 + rr * (-1.0 / 640.0 + rr * (17.0 / 14336.0 +
+                                           rr * (-31.0 / 18432.0 + rr * (691.0 / 180224.0))))));
                         lower = x * (v + 2.5) < (v + 1.0);       // x < (v+1)/(v+2.5)
                         c_x = lower ? x : y;
                         c_v = v;
@@ -497,6 +501,7 @@ extern "C" int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf, 
             if (grid > (unsigned)(ctx->sm_count * per_sm)) grid = (unsigned)(ctx->sm_count * per_sm);
             TT8Consts K;
             K.rnA = 1.0 / nA; K.rnB = 1.0 / nB; K.rnA1 = 1.0 / (nA - 1); K.rnB1 = 1.0 / (nB - 1);
+            K.p2A = (nA & (nA - 1)) == 0; K.p2B = (nB & (nB - 1)) == 0;
             k8<<<grid, TT8_THREADS, smem8, st>>>(m->cnts, m->order, m->lbase, nch8, S, t->nf_dev, tab2, nA, nB, K,
                                                             t->p_raw, t->log2fc, (unsigned long long *)(t->tie_counts + 2), tn8);
             DK_LAUNCHED(ctx);
