@@ -131,7 +131,9 @@ __global__ void k_bh_lookup(const double *cp, const uint32_t *crow, uint64_t nc,
     p_adj[crow[i]] = f > 1.0 ? 1.0 : f;                              // dmin(1,new) :475
 }
 
-extern "C" int dk_ttest_candidates(dk_ctx *ctx, dk_ttest *t, double p_cut, uint64_t *n_cand, const double **cand_p_dev)
+// n_known: the number of rows with p_raw <= p_cut when the caller has just counted them (dk_ttest_count_le at the same cut),
+// else UINT64_MAX and this function counts first
+static int ttest_candidates_impl(dk_ctx *ctx, dk_ttest *t, double p_cut, uint64_t n_known, uint64_t *n_cand, const double **cand_p_dev)
 {
     if (!ctx || !t) return dk_fail(ctx, DK_ERR_ARG, "ttest_candidates: NULL argument");
     cudaStream_t st = ctx->stream;
@@ -140,7 +142,8 @@ extern "C" int dk_ttest_candidates(dk_ctx *ctx, dk_ttest *t, double p_cut, uint6
     DK_CUDA(ctx, cudaMemsetAsync(ctr, 0, 64, st));
     unsigned grid = (unsigned)((t->R + BHC_T * BHC_V - 1) / (BHC_T * BHC_V));
     uint64_t nc = 0;
-    if (t->R) {
+    if (n_known != ~0ull) nc = n_known;
+    else if (t->R) {
         k_bh_candidates<<<grid, 256, 0, st>>>(t->p_raw, t->R, p_cut, ctr, nullptr, nullptr, 0); DK_LAUNCHED(ctx);
         DK_CUDA(ctx, cudaMemcpyAsync(&nc, ctr, 8, cudaMemcpyDeviceToHost, st));
         DK_CUDA(ctx, cudaStreamSynchronize(st));
@@ -160,6 +163,11 @@ extern "C" int dk_ttest_candidates(dk_ctx *ctx, dk_ttest *t, double p_cut, uint6
     if (n_cand) *n_cand = nc;
     if (cand_p_dev) *cand_p_dev = t->cand_p;
     return DK_OK;
+}
+
+extern "C" int dk_ttest_candidates(dk_ctx *ctx, dk_ttest *t, double p_cut, uint64_t *n_cand, const double **cand_p_dev)
+{
+    return ttest_candidates_impl(ctx, t, p_cut, ~0ull, n_cand, cand_p_dev);
 }
 
 // #{ p_raw <= cut } of this object's rows: the counting pass of the candidate narrowing below (one read of p_raw)
@@ -313,21 +321,34 @@ extern "C" int dk_ttest_adjust_global(dk_ctx *ctx, dk_ttest *t, const double *al
     return rc;
 }
 
+// internal (dk_comm.cu): the candidate list at a narrowed cut when the caller already knows this rank's count at that cut
+int dk_ttest_candidates_known(dk_ctx *ctx, dk_ttest *t, double cut, double p_cut, uint64_t n_known, uint64_t *n_cand,
+                              const double **cand_p_dev)
+{
+    if (!(cut <= p_cut)) return dk_fail(ctx, DK_ERR_ARG, "ttest_candidates: cut %g above p_cut %g", cut, p_cut);
+    DK_TRY(ttest_candidates_impl(ctx, t, cut, n_known, n_cand, cand_p_dev));
+    t->p_cut = p_cut;
+    return DK_OK;
+}
+
 extern "C" int dk_ttest_adjust(dk_ctx *ctx, dk_ttest *t, double p_cut)
 {
     if (!ctx || !t) return dk_fail(ctx, DK_ERR_ARG, "ttest_adjust: NULL argument");
-    uint64_t nc = 0;
+    uint64_t nc = 0, n_known = ~0ull;
     const double *cp = nullptr;
     double cut = p_cut;
     if (p_cut < 1.0 && t->R && !getenv("DK_BH_NO_NARROW")) {
         for (int it = 0; it < 4; it++) {                          // each pass: one read of p_raw (dk_bh_next_cut)
             uint64_t n = 0;
             DK_TRY(dk_ttest_count_le(ctx, t, cut, &n));
+            n_known = n;                                          // the compaction below need not count again at this cut
             const double next = dk_bh_next_cut(p_cut, n, t->R);
-            if (!(next < cut * 0.75)) break;                      // no longer worth a pass
-            cut = next;
+            if (n <= DK_BH_SMALL_LIST || !(next < cut * 0.75)) break;   // a list this short sorts for free: no more passes
+            cut = next; n_known = ~0ull;
         }
     }
-    DK_TRY(dk_ttest_candidates_narrowed(ctx, t, cut, p_cut, &nc, &cp));
+    if (!(cut <= p_cut)) return dk_fail(ctx, DK_ERR_ARG, "ttest_adjust: cut %g above p_cut %g", cut, p_cut);
+    DK_TRY(ttest_candidates_impl(ctx, t, cut, n_known, &nc, &cp));
+    t->p_cut = p_cut;                                             // adjusted values are exact up to the REQUESTED cut
     return dk_ttest_adjust_global(ctx, t, cp, nc, t->R);
 }

@@ -204,19 +204,21 @@ extern "C" int dk_run_path_sharded(dk_ctx *ctx, int S, const uint64_t *const *ke
         if (R_loc) { SH_FAIL(dk_ttest_rows(ctx, m, nf_used, idxA, nA, idxB, nB, &t)); st.ms_ttest = ctx->stage_ms[2]; }
         cudaEventRecord(e0, ctx->stream);
         double cut = pmax;
+        uint64_t n_known = ~0ull;
         if (pmax < 1.0) {
             for (int it = 0; it < 4; it++) {
                 uint64_t c = 0;
                 if (t) SH_FAIL(dk_ttest_count_le(ctx, t, cut, &c));
+                n_known = c;                                               // this rank's count at `cut`
                 SH_FAIL(comm_allreduce_u64(ctx, &c, 1));
                 const double next = dk_bh_next_cut(pmax, c, st.R);
-                if (!(next < cut * 0.75)) break;
-                cut = next;
+                if (c <= (uint64_t)DK_BH_SMALL_LIST * (uint64_t)world || !(next < cut * 0.75)) break;
+                cut = next; n_known = ~0ull;
             }
         }
         uint64_t nc = 0;
         const double *cp = nullptr;
-        if (t) SH_FAIL(dk_ttest_candidates_narrowed(ctx, t, cut, pmax, &nc, &cp));
+        if (t) SH_FAIL(dk_ttest_candidates_known(ctx, t, cut, pmax, n_known, &nc, &cp));
         if (world == 1) {
             if (t) SH_FAIL(dk_ttest_adjust_global(ctx, t, cp, nc, st.R));
         } else {

@@ -105,6 +105,9 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
                  const uint64_t *n, int min_rec, int min_abund, int emit_stale_tail, dk_matrix **out);
 int dk_scan_excl_u64(dk_ctx *ctx, const uint64_t *in, uint64_t *out, size_t n);   // out[n] = total
 int dk_scan_excl_u32(dk_ctx *ctx, const uint32_t *in, uint32_t *out, size_t n);
+int dk_ttest_candidates_known(dk_ctx *ctx, dk_ttest *t, double cut, double p_cut, uint64_t n_known, uint64_t *n_cand,
+                              const double **cand_p_dev);
+#define DK_BH_SMALL_LIST (1u << 20)   // candidate lists up to this size cost less to process than another pass over p_raw
 int dk_sort_keys_u64_scratch(dk_ctx *ctx, uint64_t *keys, uint64_t *keys_tmp, size_t n, uint32_t *cnt /* 256*ceil(n/4096) */);
 int dk_sort_pairs_u64(dk_ctx *ctx, uint64_t *keys, uint32_t *vals, uint64_t *keys_tmp, uint32_t *vals_tmp,
                       size_t n, uint64_t **keys_sorted, uint32_t **vals_sorted);

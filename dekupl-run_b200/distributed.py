@@ -178,7 +178,7 @@ def _bh_global(backend, R_glob, pmax):
             if world > 1:
                 dist.all_reduce(nle)
             nxt = backend.next_cut(pmax, int(nle.item()), R_glob)
-            if not (nxt < cut * 0.75):
+            if int(nle.item()) <= (1 << 20) * world or not (nxt < cut * 0.75):   # a list this short sorts for free
                 break
             cut = nxt
     mark("narrow")
