@@ -71,6 +71,71 @@ struct DkCursor {
     }
 };
 
+// The same cursor over a file that is inflated in blocks instead of being held in memory as a whole (a dump of 300 M
+// records is ~10 GB of text): the buffer is refilled when a token or a line runs into its end, the unfinished bytes moving
+// to the front. A token pointer stays valid until the next call. `bufsize` is a parameter for the tokeniser's own test.
+struct DkStreamCursor {
+    gzFile fp = nullptr;
+    std::vector<char> buf;
+    size_t p = 0, end = 0;
+    bool file_eof = false;
+    int dret = 0;
+    bool open(const char *path, size_t bufsize = (size_t)8 << 20)
+    {
+        fp = gzopen(path, "r");                   // transparent for plain files, concatenated members handled by zlib
+        if (!fp) return false;
+        gzbuffer(fp, 1 << 20);
+        buf.resize(bufsize < 16 ? 16 : bufsize);
+        return true;
+    }
+    ~DkStreamCursor() { if (fp) gzclose(fp); }
+    // keep [from, end) at the front of the buffer (growing it when a single token is longer than the buffer) and read on
+    bool refill(size_t from)
+    {
+        if (file_eof) return false;
+        const size_t keep = end - from;
+        if (keep && from) memmove(buf.data(), buf.data() + from, keep);
+        if (keep == buf.size()) buf.resize(buf.size() * 2);
+        p -= from; end = keep;
+        const int n = gzread(fp, buf.data() + end, (unsigned)(buf.size() - end));
+        if (n <= 0) { file_eof = true; return false; }
+        end += (size_t)n;
+        return true;
+    }
+    bool eof()
+    {
+        if (p < end) return false;
+        p = end = 0;
+        return !refill(0);
+    }
+    bool token(const char *&s, size_t &len)
+    {
+        if (eof()) { dret = 0; return false; }
+        size_t start = p;
+        for (;;) {
+            while (p < end && !isspace((unsigned char)buf[p])) p++;
+            if (p < end) break;                   // delimiter found
+            const size_t from = start;
+            if (!refill(from)) break;             // end of file: the token ends with the data
+            start = 0;
+        }
+        s = buf.data() + start;
+        len = p - start;
+        if (p < end) { dret = (unsigned char)buf[p]; p++; } else dret = 0;
+        return true;
+    }
+    void skip_line()
+    {
+        if (dret == '\n') return;
+        for (;;) {
+            while (p < end && buf[p] != '\n') p++;
+            if (p < end) { dret = '\n'; p++; return; }
+            p = end = 0;
+            if (!refill(0)) { dret = 0; return; }
+        }
+    }
+};
+
 static inline int dk_atoi(const char *s, size_t len)   // atoi on a non-terminated token
 {
     size_t i = 0;

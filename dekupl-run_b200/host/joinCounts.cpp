@@ -39,15 +39,12 @@ int main(int argc, char *argv[])
     std::vector<std::string> err(S);
     auto parse_one = [&](int i) {
         const char *path = argv[optind + i];
-        DkFile f;
-        if (!f.load(path)) { status[i] = 1; return; }     // joinCounts.c:52
-        DkCursor cur(f);
+        DkStreamCursor cur;                                // inflated and tokenised block by block, never held as a whole
+        if (!cur.open(path)) { status[i] = 1; return; }   // joinCounts.c:52
         const char *s;
         size_t len;
         bool first = true;
         int k = 0;
-        keys[i].reserve(f.size() / 34 + 16);
-        cnts[i].reserve(f.size() / 34 + 16);
         // joinCounts.c:55-68 (first record: skip the rest of its line) and :86-92 (then strictly token pairs)
         while (cur.token(s, len)) {
             if (len == 0 && cur.eof()) break;

@@ -70,6 +70,32 @@ def test_poisson_flag_is_accepted_in_usage():
     assert r.returncode == 1 and "-l        disregard the program name" in r.stderr
 
 
+def test_block_streamed_tokeniser_matches_the_in_memory_one(tmp_path):
+    """joinCounts reads each dump through DkStreamCursor (dk_text.h), a few MB at a time; test_text replays the parser's
+    loop over the same file with the whole-file cursor and with buffers down to 16 bytes and compares the record streams."""
+    cases = {
+        "plain.txt": b"ACGT 5 extra tokens here\nCCGT\t7\nGGGT 9\r\nTTTT   \n",
+        "no_newline_at_end.txt": b"AAAA 3\nCCCC 4",
+        "empty.txt": b"",
+        "long_first_line.txt": b"ACGT 1 " + b"x" * 5000 + b"\nCCCC 2\n",
+        "blank_lines.txt": b"ACGT 1\n\n\nCCCC 2\n",
+    }
+    for nm, data in cases.items():
+        (tmp_path / nm).write_bytes(data)
+    (tmp_path / "two_members.gz").write_bytes(gzip.compress(cases["plain.txt"]) + gzip.compress(cases["no_newline_at_end.txt"]))
+    files = [str(tmp_path / nm) for nm in list(cases) + ["two_members.gz"]] + [os.path.join(GOLD, "config1", "sample1.txt.gz")]
+    for f in files:
+        outs = set()
+        for b in (16, 17, 61, 4096, 8 << 20):
+            r = subprocess.run([os.path.join(BIN, "test_text"), f, str(b)], capture_output=True)
+            assert r.returncode == 0, (f, b)
+            outs.add(r.stdout)
+        assert len(outs) == 1, f
+    with gzip.open(files[-1], "rt") as fh:
+        n = sum(1 for _ in fh)
+    assert r.stdout.count(b"\n") == n
+
+
 @pytest.mark.gpu
 def test_joinCounts_cli_matches_reference_binary_bytes(tmp_path):
     for ci, case in enumerate(load_json("join_cases.json")):
