@@ -1,9 +1,9 @@
 #!/bin/bash
 # final evidence of a round on one B200: GPU suite, smoke, default bench, reference arm (then tools/r2p.sh for the ncu captures)
 O=gpurun_out; mkdir -p $O; TAG=$1
-python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?"; tail -2 $O/${TAG}_pytest.log
-python __graft_entry__.py smoke > $O/${TAG}_smoke.log 2>&1; echo "smoke rc=$?"; tail -1 $O/${TAG}_smoke.log
 python bench.py > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench rc=$?"
+python __graft_entry__.py smoke > $O/${TAG}_smoke.log 2>&1; echo "smoke rc=$?"; tail -1 $O/${TAG}_smoke.log
+python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?"; tail -2 $O/${TAG}_pytest.log
 python bench.py --impl reference --steps 3 --warmup 1 > $O/${TAG}_reference.json 2> $O/${TAG}_reference.err; echo "reference rc=$?"
 python - "$O/${TAG}_bench.json" "$O/${TAG}_reference.json" <<'PY'
 import sys, json
