@@ -569,6 +569,7 @@ extern "C" int dk_stream_path(dk_ctx *ctx, int S, const uint64_t *const *keys, c
                         cudaStreamSynchronize(ctx->stream) != cudaSuccess) r = dk_fail(ctx, DK_ERR_CUDA, "stream: candidate count");
                 }
                 if (r == DK_OK && nc) r = acc_reserve(ctx, acc, S, acc.n + nc);
+                if (r == DK_OK && nc) r = dk_ttest_need_log2fc(ctx, t, nullptr, 0);   // the gather reads it at the flagged rows
                 if (r == DK_OK && nc) {
                     k_gather_flagged<<<(unsigned)((R + 7) / 8), 256, 0, ctx->stream>>>(m->keys, m->cnts, m->lbase, m->order, (uint32_t)m->n_chunks,
                                                                                        S, R, t->p_raw, t->log2fc, flag, acc.n, acc.keys,

@@ -85,6 +85,7 @@ struct dk_ttest {
     int *idx_dev = nullptr;       // [nA+nB]
     double *p_raw = nullptr;      // [R] logical order
     double *log2fc = nullptr;     // [R]
+    mutable bool fc_lazy = false; // log2fc not written by the row kernel: dk_ttest_need_log2fc fills it before it is read
     double *p_adj = nullptr;      // [R] NaN where not computed
     // candidates (p_raw <= p_cut)
     uint64_t n_cand = 0;
@@ -105,6 +106,8 @@ int dk_join_impl(dk_ctx *ctx, int S, const uint64_t *const *keys_dev, const int3
                  const uint64_t *n, int min_rec, int min_abund, int emit_stale_tail, dk_matrix **out);
 int dk_scan_excl_u64(dk_ctx *ctx, const uint64_t *in, uint64_t *out, size_t n);   // out[n] = total
 int dk_scan_excl_u32(dk_ctx *ctx, const uint32_t *in, uint32_t *out, size_t n);
+// log2FC of the listed logical rows (rows == NULL: all rows) when the row kernel left it out; no-op otherwise
+int dk_ttest_need_log2fc(dk_ctx *ctx, const dk_ttest *t, const uint32_t *rows, uint64_t n);
 int dk_ttest_candidates_known(dk_ctx *ctx, dk_ttest *t, double cut, double p_cut, uint64_t n_known, uint64_t *n_cand,
                               const double **cand_p_dev);
 #define DK_BH_SMALL_LIST (1u << 20)   // candidate lists up to this size cost less to process than another pass over p_raw

@@ -89,6 +89,8 @@ extern "C" int dk_ttest_filter(dk_ctx *ctx, dk_ttest *t, double pmax, double fmi
     const bool by_cand = t->cand_row != nullptr;                      // the list the adjusted values were written through
     const unsigned cgrid = (unsigned)((t->n_cand + 255) / 256);
     uint64_t D = 0;
+    // log2FC is read at the candidate rows (or at every row without a candidate list)
+    DK_TRY(dk_ttest_need_log2fc(ctx, t, by_cand ? t->cand_row : nullptr, by_cand ? t->n_cand : 0));
     if (t->R && !(by_cand && t->n_cand == 0)) {
         if (by_cand) k_filter_cand<<<cgrid, 256, 0, st>>>(t->cand_row, t->n_cand, t->p_adj, t->log2fc, pmax, fmin_, ctr, nullptr, 0,
                                                          (unsigned long long *)t->tie_counts);
@@ -178,6 +180,7 @@ extern "C" int dk_ttest_export_rows(dk_ctx *ctx, const dk_ttest *t, double *p_ra
 {
     if (!ctx || !t) return dk_fail(ctx, DK_ERR_ARG, "export_rows: NULL argument");
     cudaStream_t st = ctx->stream;
+    if (log2fc) DK_TRY(dk_ttest_need_log2fc(ctx, t, nullptr, 0));
     if (p_raw) DK_CUDA(ctx, cudaMemcpyAsync(p_raw, t->p_raw, 8 * t->R, cudaMemcpyDeviceToHost, st));
     if (log2fc) DK_CUDA(ctx, cudaMemcpyAsync(log2fc, t->log2fc, 8 * t->R, cudaMemcpyDeviceToHost, st));
     if (p_adj) {

@@ -195,12 +195,38 @@ k_ttest_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, 
 // a few ulp at most, far inside the 1e-9 contract (tests/test_gpu_parity.py).
 #define TT8_N 8
 #ifndef TT8_THREADS
-#define TT8_THREADS 384
+#define TT8_THREADS 448
 #endif
 #ifndef TT8_TN
 #define TT8_TN 256
 #endif
 #define TT8_TN2 4096
+// the small-group kernel's second-level table is larger (L2-resident: S * tn2 * 16 bytes <= 16 MB) so that a row with a
+// count beyond it — the only case that leaves the branch-free look-ups — is rare even for a heavy-tailed spectrum
+#define TT8_TN2F 65536
+#ifndef TT8_FAST
+#define TT8_FAST 1        // 0: branchy three-level look-up; 1: table hit + predicated second-level load; 2: one generic load
+#endif
+#ifndef TT8_ONELOG
+#define TT8_ONELOG 1
+#endif
+#ifndef TT8_GW
+#define TT8_GW 8.0
+#endif
+// log2FC is read at the rows that pass the p-value cut only (TtestFilter.c:486-489 prints it for the survivors): the
+// small-group kernel leaves it out — no second log, no division, no sums of the normalised counts, 8 bytes per row less
+// to write — and dk_ttest_need_log2fc computes it where and when somebody reads it, from the same look-up arithmetic
+#ifndef TT8_LAZYFC
+#define TT8_LAZYFC 1
+#endif
+// with log2FC gone the look-ups need the logs only: the shared-memory table holds 8-byte entries for twice as many counts
+#ifndef TT8_LTAB
+#define TT8_LTAB 0        // measured: 14.6 ms against 14.2 ms with the 16-byte entries at cfg 2
+#endif
+#define TT8_TNL (2 * TT8_TN)
+#if TT8_LTAB && !TT8_LAZYFC
+#error "TT8_LTAB drops the normalised counts the in-kernel log2FC sums"
+#endif
 
 // continued fraction of I_x(a,b) (Wallis form, see dk_beta_cf): returns A and B unreduced
 __device__ __forceinline__ void dk_beta_cf2(double a, double b, double x, double &Ao, double &Bo)
@@ -227,11 +253,11 @@ __device__ __forceinline__ void dk_beta_cf2(double a, double b, double x, double
 
 struct TT8Consts { double rnA, rnB, rnA1, rnB1; int p2A, p2B; };   // 1/nA, 1/nB, 1/(nA-1), 1/(nB-1); group size is a power of two
 
-__global__ void k_tt8_table(const double *nf_g, int S, double2 *tab2)
+__global__ void k_tt8_table(const double *nf_g, int S, double2 *tab2, uint32_t tn2)
 {
     const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= (uint32_t)S * TT8_TN2) return;
-    const uint32_t k = e / TT8_TN2, cc = e - k * TT8_TN2;
+    if (e >= (uint32_t)S * tn2) return;
+    const uint32_t k = e / tn2, cc = e - k * tn2;
     const double nf = nf_g[k];
     double a, l;
     dk_norm_log<true>((int32_t)cc, nf, 1.0 / nf, a, l);
@@ -239,12 +265,62 @@ __global__ void k_tt8_table(const double *nf_g, int S, double2 *tab2)
 }
 
 __device__ __forceinline__ void tt8_lookup(int32_t cc, int k, const double2 *tab, const double2 *tab2, const double *nf,
-                                           const double *rnf, double &a, double &l, const uint32_t tn = TT8_TN)
+                                           const double *rnf, double &a, double &l, const uint32_t tn = TT8_TN,
+                                           const uint32_t tn2 = TT8_TN2)
 {
     if ((uint32_t)cc < tn) { const double2 t = tab[(uint32_t)k * tn + (uint32_t)cc]; a = t.x; l = t.y; }
-    else if ((uint32_t)cc < TT8_TN2) { const double2 t = __ldg(tab2 + (size_t)k * TT8_TN2 + (uint32_t)cc); a = t.x; l = t.y; }
+    else if ((uint32_t)cc < tn2) { const double2 t = __ldg(tab2 + (size_t)k * tn2 + (uint32_t)cc); a = t.x; l = t.y; }
     else dk_norm_log<true>(cc, nf[k], rnf[k], a, l);
 }
+// the same for a count known to be below tn2 (the caller checked the whole row): no branch, so the 16 look-ups of a row
+// are independent loads the scheduler can keep in flight together (r02final ncu: 16 % of the first phase's stall samples
+// were loads, and the three-way branch cost ~8 control instructions per look-up)
+__device__ __forceinline__ void tt8_lookup_fast(int32_t cc, int k, const double2 *tab, const double2 *tab2, const uint32_t tn2,
+                                                double &a, double &l)
+{
+    const uint32_t u = (uint32_t)cc;
+#if TT8_FAST == 2
+    const double2 *p = u < (uint32_t)TT8_TN ? tab + (uint32_t)k * TT8_TN + u : tab2 + (size_t)k * tn2 + u;
+    const double2 t = *p;
+#else
+    double2 t = tab[(uint32_t)k * TT8_TN + min(u, (uint32_t)TT8_TN - 1u)];
+    if (u >= (uint32_t)TT8_TN) t = __ldg(tab2 + (size_t)k * tn2 + u);
+#endif
+    a = t.x; l = t.y;
+}
+// log only, from the 8-byte table (TT8_LTAB)
+__device__ __forceinline__ void tt8_lookup_fast_l(int32_t cc, int k, const double *ltab, const double2 *tab2, const uint32_t tn2, double &l)
+{
+    const uint32_t u = (uint32_t)cc;
+    l = ltab[(uint32_t)k * TT8_TNL + min(u, (uint32_t)TT8_TNL - 1u)];
+    if (u >= (uint32_t)TT8_TNL) l = __ldg(&tab2[(size_t)k * tn2 + u].y);
+}
+
+// group moments in two passes over the row's counts with the general look-up (large groups; rows with a count beyond
+// the second-level table)
+__device__ __forceinline__ void tt8_moments_2pass(const int32_t *c, int nA, int nB, const double2 *tab, uint32_t tn, const double2 *tab2,
+                                                  uint32_t tn2, const double *nf, const double *rnf, const TT8Consts &K, double &sa,
+                                                  double &sb, double &m1, double &m2, double &s1, double &s2)
+{
+    double sl = 0;
+    for (int i = 0; i < nA; i++) { double a, l; tt8_lookup(__ldg(c + i), i, tab, tab2, nf, rnf, a, l, tn, tn2); sa += a; sl += l; }
+    m1 = K.p2A ? sl * K.rnA : sl / nA;
+    for (int i = 0; i < nA; i++) { double a, l; tt8_lookup(__ldg(c + i), i, tab, tab2, nf, rnf, a, l, tn, tn2); const double d = l - m1; s1 += d * d; }
+    sl = 0;
+    for (int i = 0; i < nB; i++) { double a, l; tt8_lookup(__ldg(c + nA + i), nA + i, tab, tab2, nf, rnf, a, l, tn, tn2); sb += a; sl += l; }
+    m2 = K.p2B ? sl * K.rnB : sl / nB;
+    for (int i = 0; i < nB; i++) { double a, l; tt8_lookup(__ldg(c + nA + i), nA + i, tab, tab2, nf, rnf, a, l, tn, tn2); const double d = l - m2; s2 += d * d; }
+}
+__device__ __noinline__ void tt8_moments_slow(const int32_t *c, int nA, int nB, const double2 *tab, uint32_t tn, const double2 *tab2,
+                                              uint32_t tn2, const double *nf, const double *rnf, const TT8Consts &K, double *o)
+{
+    double sa = 0, sb = 0, m1 = 0, m2 = 0, s1 = 0, s2 = 0;
+    tt8_moments_2pass(c, nA, nB, tab, tn, tab2, tn2, nf, rnf, K, sa, sb, m1, m2, s1, s2);
+    o[0] = sa; o[1] = sb; o[2] = m1; o[3] = m2; o[4] = s1; o[5] = s2;
+}
+#ifndef TT8_SLOWCALL
+#define TT8_SLOWCALL 0
+#endif
 
 #ifndef TT8_MINB
 #define TT8_MINB 2
@@ -265,7 +341,7 @@ __device__ __forceinline__ void tt8_lookup(int32_t cc, int k, const double2 *tab
 template <bool VEC, bool BIG>
 __global__ void __launch_bounds__(TT8_THREADS, TT8_MINB)
 k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, uint32_t n_chunks, int S, const double *nf_g,
-              const double2 *tab2, int nA, int nB, TT8Consts K, double *p_raw, double *log2fc, unsigned long long *tie_sd, uint32_t tn_arg)
+              const double2 *tab2, int nA, int nB, TT8Consts K, double *p_raw, double *log2fc, unsigned long long *tie_sd, uint32_t tn_arg, uint32_t tn2)
 {
     extern __shared__ __align__(16) unsigned char sm[];
     const uint32_t TNv = BIG ? tn_arg : (uint32_t)TT8_TN;
@@ -291,10 +367,26 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
     for (int i = threadIdx.x; i < S; i += T) { nf[i] = nf_g[i]; rnf[i] = 1.0 / nf_g[i]; }
-    for (uint32_t e = threadIdx.x; e < (uint32_t)S * TNv; e += T) {
-        const uint32_t k = e / TNv, cc = e - k * TNv;
-        tab[e] = tab2[(size_t)k * TT8_TN2 + cc];
+#if TT8_LTAB
+    static_assert(TT8_FAST != 0, "the 8-byte table needs the branch-free look-ups");
+    constexpr bool LT = !BIG;                                    // [S][TT8_TNL] logs in the same bytes
+#else
+    constexpr bool LT = false;
+#endif
+    double *ltab = (double *)sm;
+    if (LT) {
+        for (uint32_t e = threadIdx.x; e < (uint32_t)S * TT8_TNL; e += T) {
+            const uint32_t k = e / TT8_TNL, cc = e - k * TT8_TNL;
+            ltab[e] = tab2[(size_t)k * tn2 + cc].y;
+        }
+    } else {
+        for (uint32_t e = threadIdx.x; e < (uint32_t)S * TNv; e += T) {
+            const uint32_t k = e / TNv, cc = e - k * TNv;
+            tab[e] = tab2[(size_t)k * tn2 + cc];
+        }
     }
+    (void)ltab;
+    const uint32_t TNs = LT ? 0u : TNv;                          // the general look-up skips a table it cannot read
     __syncthreads();
     const uint32_t nblk = (n_chunks + cpb - 1) / cpb;
     unsigned long long ties = 0;
@@ -312,7 +404,8 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
         bool lower = false;
         if (act) {
             const int32_t *c = cnts + ((size_t)order[oc] * DK_CH + j) * (size_t)S;
-            double sa = 0, sb = 0, m1, m2, s1 = 0, s2 = 0;
+            double sa = 0, sb = 0, m1 = 0, m2 = 0, s1 = 0, s2 = 0;
+            bool slow = BIG;                                     // two passes over the row with the general look-up
             if constexpr (!BIG) {
                 int32_t cA[TT8_N], cB[TT8_N];
                 if (VEC) {
@@ -326,11 +419,26 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
     #pragma unroll
                     for (int i = 0; i < TT8_N; i++) { cA[i] = i < nA ? __ldg(c + i) : 0; cB[i] = i < nB ? __ldg(c + nA + i) : 0; }
                 }
+#if TT8_FAST
+                uint32_t mx = 0;
+    #pragma unroll
+                for (int i = 0; i < TT8_N; i++) mx |= (i < nA ? (uint32_t)cA[i] : 0u) | (i < nB ? (uint32_t)cB[i] : 0u);
+                slow = mx >= tn2;                                // some count beyond the tables (or negative): rare
+                if (!slow) {
+#if TT8_LTAB
+#define TT8_LK(cc, k, a, l) { a = 0; tt8_lookup_fast_l(cc, k, ltab, tab2, tn2, l); }
+#else
+#define TT8_LK(cc, k, a, l) tt8_lookup_fast(cc, k, tab, tab2, tn2, a, l)
+#endif
+#else
+                {
+#define TT8_LK(cc, k, a, l) tt8_lookup(cc, k, tab, tab2, nf, rnf, a, l, TT8_TN, tn2)
+#endif
                 // ---- group moments (TtestFilter.c:379-411; sum/mean/sd :77-98), sums sequential in column order
                 double la[TT8_N], sl = 0;
     #pragma unroll
                 for (int i = 0; i < TT8_N; i++)
-                    if (i < nA) { double a, l; tt8_lookup(cA[i], i, tab, tab2, nf, rnf, a, l); sa += a; sl += l; la[i] = l; }
+                    if (i < nA) { double a, l; TT8_LK(cA[i], i, a, l); sa += a; sl += l; la[i] = l; }
                 m1 = K.p2A ? sl * K.rnA : sl / nA;    // mean() of the logs decides sd == 0: a true division, or for a group of 2^k
                                                       // samples the exact multiply by 2^-k (same bits)
     #pragma unroll
@@ -338,20 +446,22 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
                 sl = 0;
     #pragma unroll
                 for (int i = 0; i < TT8_N; i++)
-                    if (i < nB) { double a, l; tt8_lookup(cB[i], nA + i, tab, tab2, nf, rnf, a, l); sb += a; sl += l; la[i] = l; }
+                    if (i < nB) { double a, l; TT8_LK(cB[i], nA + i, a, l); sb += a; sl += l; la[i] = l; }
                 m2 = K.p2B ? sl * K.rnB : sl / nB;
     #pragma unroll
                 for (int i = 0; i < TT8_N; i++) if (i < nB) { const double d = la[i] - m2; s2 += d * d; }
-            } else {
-                // ---- group moments, two passes (TtestFilter.c:379-411; sum/mean/sd :77-98), sums sequential in column order
-                double sl = 0;
-                for (int i = 0; i < nA; i++) { double a, l; tt8_lookup(__ldg(c + i), i, tab, tab2, nf, rnf, a, l, TNv); sa += a; sl += l; }
-                m1 = K.p2A ? sl * K.rnA : sl / nA;
-                for (int i = 0; i < nA; i++) { double a, l; tt8_lookup(__ldg(c + i), i, tab, tab2, nf, rnf, a, l, TNv); const double d = l - m1; s1 += d * d; }
-                sl = 0;
-                for (int i = 0; i < nB; i++) { double a, l; tt8_lookup(__ldg(c + nA + i), nA + i, tab, tab2, nf, rnf, a, l, TNv); sb += a; sl += l; }
-                m2 = K.p2B ? sl * K.rnB : sl / nB;
-                for (int i = 0; i < nB; i++) { double a, l; tt8_lookup(__ldg(c + nA + i), nA + i, tab, tab2, nf, rnf, a, l, TNv); const double d = l - m2; s2 += d * d; }
+                }
+#undef TT8_LK
+            }
+            if (slow) {
+                // ---- group moments, two passes (TtestFilter.c:379-411; sum/mean/sd :77-98), sums sequential in column order:
+                // the same values in the same order as above
+                if constexpr (BIG || !TT8_SLOWCALL) tt8_moments_2pass(c, nA, nB, tab, TNs, tab2, tn2, nf, rnf, K, sa, sb, m1, m2, s1, s2);
+                else {                                           // a rare row: out of line, so that it costs the others nothing
+                    double o[6];
+                    tt8_moments_slow(c, nA, nB, tab, TNs, tab2, tn2, nf, rnf, K, o);
+                    sa = o[0]; sb = o[1]; m1 = o[2]; m2 = o[3]; s1 = o[4]; s2 = o[5];
+                }
             }
             // ---- Welch (TtestFilter.c:120-150) on sd^2 = s/(n-1)
             double p = 0.5;                                      // sd1 == 0 && sd2 == 0 (:128)
@@ -370,11 +480,18 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
                     else if (!(y > 0.0)) p = 1.0;
                     else {
                         const double INV_SQRT_PI = 0.56418958354775628695;
+#if TT8_ONELOG
+                        // one log for both halves: for x > 1/2 its absolute error (an ulp of x, ~1e-16) enters exp(v * lx)
+                        // as a relative 1e-16 * v, the same order as everything else here; the log1p/log pair ran BOTH
+                        // branches in nearly every warp
+                        const double lx = log(x);
+#else
                         const double lx = (y < 0.5) ? log1p(-y) : log(x);
+#endif
                         // Gamma(v+1/2)/Gamma(v): shift up to w >= 12, then the asymptotic series with 6 terms (the next one,
                         // 5461/(65536*7) / w^13, is below 1e-16 there; stopping at 12 instead of 20 saves 8 trips of the loop)
                         double num = 1.0, dg = 1.0, w = v;
-                        while (w < 12.0) { num *= w; dg *= (w + 0.5); w += 1.0; }
+                        while (w < TT8_GW) { num *= w; dg *= (w + 0.5); w += 1.0; }
                         const double r = 1.0 / w, rr = r * r;
                         const double ser = r * (-1.0 / 8.0 + rr * (1.0 / 192.0 + rr * (-1.0 / 640.0 + rr * (17.0 / 14336.0 +
                                            rr * (-31.0 / 18432.0 + rr * (691.0 / 180224.0))))));
@@ -391,7 +508,8 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
             }
             const uint64_t row = b0 + j;
             if (!needcf) p_raw[row] = p;
-            log2fc[row] = log((sb * K.rnB) / (sa * K.rnA)) * 1.4426950408889634074;   // log(meanB/meanA)/log(2) (:72-75,433)
+            if (BIG || !TT8_LAZYFC)
+                log2fc[row] = log((sb * K.rnB) / (sa * K.rnA)) * 1.4426950408889634074;   // log(meanB/meanA)/log(2) (:72-75,433)
             const double eps2 = 1e-24;
             const double e1 = 1 + fabs(m1), e2 = 1 + fabs(m2);
             if (s1 * K.rnA1 <= eps2 * e1 * e1 && s2 * K.rnB1 <= eps2 * e2 * e2 && (m1 != 0 || m2 != 0)) ties++;
@@ -430,6 +548,53 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
         // (the next tile's first barrier orders these reads before the queue is rewritten)
     }
     if (ties) atomicAdd(tie_sd, ties);
+}
+
+// log2FC of the listed rows (rows != NULL: n logical rows) or of every row (n = 64 * n_chunks slots) of a table whose row
+// kernel left it out: the same sums of normalised counts in column order and the same expression as k_ttest_rows8
+__global__ void k_tt8_log2fc(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, uint32_t n_chunks, int S,
+                             const double *nf_g, int nA, int nB, double rnA, double rnB, const uint32_t *rows, uint64_t n,
+                             double *log2fc)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint64_t row;
+    size_t ph;
+    if (rows) {
+        row = rows[i];
+        uint32_t lo = 0, hi = n_chunks;
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (lbase[mid] <= row) lo = mid; else hi = mid;
+        }
+        ph = (size_t)order[lo] * DK_CH + (size_t)(row - lbase[lo]);
+    } else {
+        const uint32_t oc = (uint32_t)(i / DK_CH), j = (uint32_t)(i % DK_CH);
+        const uint64_t b0 = lbase[oc];
+        if (j >= lbase[oc + 1] - b0) return;
+        row = b0 + j;
+        ph = (size_t)order[oc] * DK_CH + j;
+    }
+    const int32_t *c = cnts + ph * (size_t)S;
+    double sa = 0, sb = 0;
+    for (int k = 0; k < nA; k++) { const double nf = nf_g[k]; double a, l; dk_norm_log<true>(c[k], nf, 1.0 / nf, a, l); sa += a; }
+    for (int k = 0; k < nB; k++) { const double nf = nf_g[nA + k]; double a, l; dk_norm_log<true>(c[nA + k], nf, 1.0 / nf, a, l); sb += a; }
+    log2fc[row] = log((sb * rnB) / (sa * rnA)) * 1.4426950408889634074;
+}
+
+int dk_ttest_need_log2fc(dk_ctx *ctx, const dk_ttest *t, const uint32_t *rows, uint64_t n)
+{
+    if (!t->fc_lazy || !t->R) return DK_OK;
+    const dk_matrix *m = t->m;
+    cudaStream_t st = ctx->stream;
+    if (!rows) n = (uint64_t)m->n_chunks * DK_CH;
+    if (n) {
+        k_tt8_log2fc<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(m->cnts, m->order, m->lbase, (uint32_t)m->n_chunks, t->S, t->nf_dev,
+                                                                 t->nA, t->nB, 1.0 / t->nA, 1.0 / t->nB, rows, n, t->log2fc);
+        DK_LAUNCHED(ctx);
+    }
+    if (!rows) t->fc_lazy = false;                               // every row holds its value now
+    return DK_OK;
 }
 
 void dk_ttest_release(dk_ctx *ctx, dk_ttest *t)
@@ -483,9 +648,13 @@ extern "C" int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf, 
     const bool fits = small_groups ? (size_t)S * TT8_TN * 16 + 16 * S + (size_t)TT8_THREADS * 104 + 1024 <= (size_t)(227 * 1024) / TT8_MINB - 1024
                                    : (size_t)S * tn_big * 16 + 16 * S + (size_t)TT8_THREADS * 40 + 2048 <= (size_t)(227 * 1024) / TT8_MINB - 1024;
     if (ident && nf_ok && nA + nB <= S && !(force_old && atoi(force_old)) && fits) {
-        double2 *tab2 = (double2 *)dk_dev_alloc(ctx, sizeof(double2) * (size_t)S * TT8_TN2);
+        // second-level table: 4096 counts per sample; for a large matrix of small groups as many as 16 MB hold (L2-resident)
+        uint32_t tn2 = TT8_TN2;
+        if (TT8_FAST && small_groups && t->R >= (1u << 20))
+            while (tn2 < (uint32_t)TT8_TN2F && (size_t)S * (tn2 * 2) * sizeof(double2) <= ((size_t)16 << 20)) tn2 *= 2;
+        double2 *tab2 = (double2 *)dk_dev_alloc(ctx, sizeof(double2) * (size_t)S * tn2);
         if (!tab2) { dk_ttest_release(ctx, t); return DK_ERR_NOMEM; }
-        k_tt8_table<<<(unsigned)(((size_t)S * TT8_TN2 + 255) / 256), 256, 0, st>>>(t->nf_dev, S, tab2); DK_LAUNCHED(ctx);
+        k_tt8_table<<<(unsigned)(((size_t)S * tn2 + 255) / 256), 256, 0, st>>>(t->nf_dev, S, tab2, tn2); DK_LAUNCHED(ctx);
         const bool vec = small_groups && (S % 4 == 0) && (nA % 4 == 0) && S <= 16;
         auto k8 = !small_groups ? k_ttest_rows8<false, true> : (vec ? k_ttest_rows8<true, false> : k_ttest_rows8<false, false>);
         const uint32_t tn8 = small_groups ? (uint32_t)TT8_TN : tn_big;
@@ -503,8 +672,9 @@ extern "C" int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf, 
             K.rnA = 1.0 / nA; K.rnB = 1.0 / nB; K.rnA1 = 1.0 / (nA - 1); K.rnB1 = 1.0 / (nB - 1);
             K.p2A = (nA & (nA - 1)) == 0; K.p2B = (nB & (nB - 1)) == 0;
             k8<<<grid, TT8_THREADS, smem8, st>>>(m->cnts, m->order, m->lbase, nch8, S, t->nf_dev, tab2, nA, nB, K,
-                                                            t->p_raw, t->log2fc, (unsigned long long *)(t->tie_counts + 2), tn8);
+                                                            t->p_raw, t->log2fc, (unsigned long long *)(t->tie_counts + 2), tn8, tn2);
             DK_LAUNCHED(ctx);
+            t->fc_lazy = TT8_LAZYFC && small_groups;             // log2FC on demand (dk_ttest_need_log2fc)
         }
         DK_CUDA(ctx, cudaEventRecord(ctx->ev[1], st));
         DK_CUDA(ctx, cudaStreamSynchronize(st));
