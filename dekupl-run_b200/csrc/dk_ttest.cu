@@ -205,7 +205,8 @@ k_ttest_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, 
 // count beyond it — the only case that leaves the branch-free look-ups — is rare even for a heavy-tailed spectrum
 #define TT8_TN2F 65536
 #ifndef TT8_FAST
-#define TT8_FAST 1        // 0: branchy three-level look-up; 1: table hit + predicated second-level load; 2: one generic load
+#define TT8_FAST 1        // 0: branchy three-level look-up; 1: the two table levels branch-free (a single generic load
+                          // for both levels was measured too: 15.8 against 15.5 ms)
 #endif
 #ifndef TT8_ONELOG
 #define TT8_ONELOG 1
@@ -219,14 +220,8 @@ k_ttest_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, 
 #ifndef TT8_LAZYFC
 #define TT8_LAZYFC 1
 #endif
-// with log2FC gone the look-ups need the logs only: the shared-memory table holds 8-byte entries for twice as many counts
-#ifndef TT8_LTAB
-#define TT8_LTAB 0        // measured: 14.6 ms against 14.2 ms with the 16-byte entries at cfg 2
-#endif
-#define TT8_TNL (2 * TT8_TN)
-#if TT8_LTAB && !TT8_LAZYFC
-#error "TT8_LTAB drops the normalised counts the in-kernel log2FC sums"
-#endif
+// (a shared-memory table of the logs alone, 8-byte entries for twice as many counts, was measured slower: 14.6 against
+// 14.2 ms at cfg 2)
 
 // continued fraction of I_x(a,b) (Wallis form, see dk_beta_cf): returns A and B unreduced
 __device__ __forceinline__ void dk_beta_cf2(double a, double b, double x, double &Ao, double &Bo)
@@ -272,32 +267,38 @@ __device__ __forceinline__ void tt8_lookup(int32_t cc, int k, const double2 *tab
     else if ((uint32_t)cc < tn2) { const double2 t = __ldg(tab2 + (size_t)k * tn2 + (uint32_t)cc); a = t.x; l = t.y; }
     else dk_norm_log<true>(cc, nf[k], rnf[k], a, l);
 }
-// the same for a count known to be below tn2 (the caller checked the whole row): no branch, so the 16 look-ups of a row
-// are independent loads the scheduler can keep in flight together (r02final ncu: 16 % of the first phase's stall samples
-// were loads, and the three-way branch cost ~8 control instructions per look-up)
-__device__ __forceinline__ void tt8_lookup_fast(int32_t cc, int k, const double2 *tab, const double2 *tab2, const uint32_t tn2,
-                                                double &a, double &l)
-{
-    const uint32_t u = (uint32_t)cc;
-#if TT8_FAST == 2
-    const double2 *p = u < (uint32_t)TT8_TN ? tab + (uint32_t)k * TT8_TN + u : tab2 + (size_t)k * tn2 + u;
-    const double2 t = *p;
-#else
-    double2 t = tab[(uint32_t)k * TT8_TN + min(u, (uint32_t)TT8_TN - 1u)];
-    if (u >= (uint32_t)TT8_TN) t = __ldg(tab2 + (size_t)k * tn2 + u);
+// the small-group kernel's form: the two table levels without a branch (a clamped shared-memory load, a predicated
+// second-level load), so the 16 look-ups of a row are independent loads the scheduler keeps in flight together (r02final
+// ncu: 16 % of the first phase's stall samples were loads, and the three-way branch cost ~8 control instructions per
+// look-up); only a count beyond the second-level table (or a negative one) branches to the direct computation
+#ifndef TT8_DIRECTCALL
+#define TT8_DIRECTCALL 1
 #endif
-    a = t.x; l = t.y;
+__device__ __noinline__ void tt8_direct(int32_t cc, double nf, double rnf, double *o)
+{
+    double a, l;
+    dk_norm_log<true>(cc, nf, rnf, a, l);
+    o[0] = a; o[1] = l;
 }
-// log only, from the 8-byte table (TT8_LTAB)
-__device__ __forceinline__ void tt8_lookup_fast_l(int32_t cc, int k, const double *ltab, const double2 *tab2, const uint32_t tn2, double &l)
+__device__ __forceinline__ void tt8_lookup_fast(int32_t cc, int k, const double2 *tab, const double2 *tab2, const uint32_t tn2,
+                                                const double *nf, const double *rnf, double &a, double &l)
 {
     const uint32_t u = (uint32_t)cc;
-    l = ltab[(uint32_t)k * TT8_TNL + min(u, (uint32_t)TT8_TNL - 1u)];
-    if (u >= (uint32_t)TT8_TNL) l = __ldg(&tab2[(size_t)k * tn2 + u].y);
+    double2 t = tab[(uint32_t)k * TT8_TN + min(u, (uint32_t)TT8_TN - 1u)];
+    if (u >= (uint32_t)TT8_TN) t = __ldg(tab2 + (size_t)k * tn2 + min(u, tn2 - 1u));
+    a = t.x; l = t.y;
+    if (u >= tn2) {
+#if TT8_DIRECTCALL
+        double o[2];
+        tt8_direct(cc, nf[k], rnf[k], o);
+        a = o[0]; l = o[1];
+#else
+        dk_norm_log<true>(cc, nf[k], rnf[k], a, l);
+#endif
+    }
 }
 
-// group moments in two passes over the row's counts with the general look-up (large groups; rows with a count beyond
-// the second-level table)
+// group moments in two passes over the row's counts with the general look-up (large groups)
 __device__ __forceinline__ void tt8_moments_2pass(const int32_t *c, int nA, int nB, const double2 *tab, uint32_t tn, const double2 *tab2,
                                                   uint32_t tn2, const double *nf, const double *rnf, const TT8Consts &K, double &sa,
                                                   double &sb, double &m1, double &m2, double &s1, double &s2)
@@ -311,16 +312,6 @@ __device__ __forceinline__ void tt8_moments_2pass(const int32_t *c, int nA, int 
     m2 = K.p2B ? sl * K.rnB : sl / nB;
     for (int i = 0; i < nB; i++) { double a, l; tt8_lookup(__ldg(c + nA + i), nA + i, tab, tab2, nf, rnf, a, l, tn, tn2); const double d = l - m2; s2 += d * d; }
 }
-__device__ __noinline__ void tt8_moments_slow(const int32_t *c, int nA, int nB, const double2 *tab, uint32_t tn, const double2 *tab2,
-                                              uint32_t tn2, const double *nf, const double *rnf, const TT8Consts &K, double *o)
-{
-    double sa = 0, sb = 0, m1 = 0, m2 = 0, s1 = 0, s2 = 0;
-    tt8_moments_2pass(c, nA, nB, tab, tn, tab2, tn2, nf, rnf, K, sa, sb, m1, m2, s1, s2);
-    o[0] = sa; o[1] = sb; o[2] = m1; o[3] = m2; o[4] = s1; o[5] = s2;
-}
-#ifndef TT8_SLOWCALL
-#define TT8_SLOWCALL 0
-#endif
 
 #ifndef TT8_MINB
 #define TT8_MINB 2
@@ -367,26 +358,10 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
     for (int i = threadIdx.x; i < S; i += T) { nf[i] = nf_g[i]; rnf[i] = 1.0 / nf_g[i]; }
-#if TT8_LTAB
-    static_assert(TT8_FAST != 0, "the 8-byte table needs the branch-free look-ups");
-    constexpr bool LT = !BIG;                                    // [S][TT8_TNL] logs in the same bytes
-#else
-    constexpr bool LT = false;
-#endif
-    double *ltab = (double *)sm;
-    if (LT) {
-        for (uint32_t e = threadIdx.x; e < (uint32_t)S * TT8_TNL; e += T) {
-            const uint32_t k = e / TT8_TNL, cc = e - k * TT8_TNL;
-            ltab[e] = tab2[(size_t)k * tn2 + cc].y;
-        }
-    } else {
-        for (uint32_t e = threadIdx.x; e < (uint32_t)S * TNv; e += T) {
-            const uint32_t k = e / TNv, cc = e - k * TNv;
-            tab[e] = tab2[(size_t)k * tn2 + cc];
-        }
+    for (uint32_t e = threadIdx.x; e < (uint32_t)S * TNv; e += T) {
+        const uint32_t k = e / TNv, cc = e - k * TNv;
+        tab[e] = tab2[(size_t)k * tn2 + cc];
     }
-    (void)ltab;
-    const uint32_t TNs = LT ? 0u : TNv;                          // the general look-up skips a table it cannot read
     __syncthreads();
     const uint32_t nblk = (n_chunks + cpb - 1) / cpb;
     unsigned long long ties = 0;
@@ -405,7 +380,6 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
         if (act) {
             const int32_t *c = cnts + ((size_t)order[oc] * DK_CH + j) * (size_t)S;
             double sa = 0, sb = 0, m1 = 0, m2 = 0, s1 = 0, s2 = 0;
-            bool slow = BIG;                                     // two passes over the row with the general look-up
             if constexpr (!BIG) {
                 int32_t cA[TT8_N], cB[TT8_N];
                 if (VEC) {
@@ -419,19 +393,10 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
     #pragma unroll
                     for (int i = 0; i < TT8_N; i++) { cA[i] = i < nA ? __ldg(c + i) : 0; cB[i] = i < nB ? __ldg(c + nA + i) : 0; }
                 }
-#if TT8_FAST
-                uint32_t mx = 0;
-    #pragma unroll
-                for (int i = 0; i < TT8_N; i++) mx |= (i < nA ? (uint32_t)cA[i] : 0u) | (i < nB ? (uint32_t)cB[i] : 0u);
-                slow = mx >= tn2;                                // some count beyond the tables (or negative): rare
-                if (!slow) {
-#if TT8_LTAB
-#define TT8_LK(cc, k, a, l) { a = 0; tt8_lookup_fast_l(cc, k, ltab, tab2, tn2, l); }
-#else
-#define TT8_LK(cc, k, a, l) tt8_lookup_fast(cc, k, tab, tab2, tn2, a, l)
-#endif
-#else
                 {
+#if TT8_FAST
+#define TT8_LK(cc, k, a, l) tt8_lookup_fast(cc, k, tab, tab2, tn2, nf, rnf, a, l)
+#else
 #define TT8_LK(cc, k, a, l) tt8_lookup(cc, k, tab, tab2, nf, rnf, a, l, TT8_TN, tn2)
 #endif
                 // ---- group moments (TtestFilter.c:379-411; sum/mean/sd :77-98), sums sequential in column order
@@ -453,16 +418,8 @@ k_ttest_rows8(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase,
                 }
 #undef TT8_LK
             }
-            if (slow) {
-                // ---- group moments, two passes (TtestFilter.c:379-411; sum/mean/sd :77-98), sums sequential in column order:
-                // the same values in the same order as above
-                if constexpr (BIG || !TT8_SLOWCALL) tt8_moments_2pass(c, nA, nB, tab, TNs, tab2, tn2, nf, rnf, K, sa, sb, m1, m2, s1, s2);
-                else {                                           // a rare row: out of line, so that it costs the others nothing
-                    double o[6];
-                    tt8_moments_slow(c, nA, nB, tab, TNs, tab2, tn2, nf, rnf, K, o);
-                    sa = o[0]; sb = o[1]; m1 = o[2]; m2 = o[3]; s1 = o[4]; s2 = o[5];
-                }
-            }
+            if constexpr (BIG)      // two passes (TtestFilter.c:379-411; sum/mean/sd :77-98): the same sums in the same order
+                tt8_moments_2pass(c, nA, nB, tab, TNv, tab2, tn2, nf, rnf, K, sa, sb, m1, m2, s1, s2);
             // ---- Welch (TtestFilter.c:120-150) on sd^2 = s/(n-1)
             double p = 0.5;                                      // sd1 == 0 && sd2 == 0 (:128)
             if (!(s1 == 0 && s2 == 0)) {
