@@ -696,8 +696,9 @@ def run_ours(args):
     }
     # the second kernel of the step is NOT HBM-bound: say what binds it: live HBM fraction of its stage + the
     # counters of its committed ncu capture
-    tt_bytes = R_loc * 4 * S + 16 * R_loc
-    tt = {"bound": "fp64 issue latency (dependent fp64 chains at 24 resident warps), not HBM",
+    # rows read + p written; the small-group kernel leaves log2FC to dk_ttest_need_log2fc (computed at the rows that read it)
+    tt_bytes = R_loc * 4 * S + (8 if S // 2 <= 8 else 16) * R_loc
+    tt = {"bound": "fp64 issue latency (dependent fp64 chains at 28 resident warps), not HBM",
           "kernel": "k_ttest_rows8 (groups of <= 8 in column order)" if S // 2 <= 8 else "k_ttest_rows (general groups)",
           "kernel_ms": float(stage_avg[2]), "alg_bytes": tt_bytes, "hbm_achieved_gbs": tt_bytes / (stage_avg[2] / 1e3) / 1e9 if stage_avg[2] else None,
           "hbm_frac": tt_bytes / (stage_avg[2] / 1e3) / 1e9 / peak if stage_avg[2] else None, "rows_per_s": R_loc / (stage_avg[2] / 1e3) if stage_avg[2] else None}

@@ -189,7 +189,9 @@ k_ttest_rows(const int32_t *cnts, const uint32_t *order, const uint64_t *lbase, 
 //   * reciprocals of the group-size constants, sd^2 taken straight from the sum of squares (no sqrt followed by a
 //     square), t^2 instead of t, x and y from one reciprocal, the Gamma ratio's denominator and the fraction's B folded
 //     into the final division: 7 divisions, 1 square root per row;
-//   * the logs of a group kept in registers (no shared-memory scratch), so two 512-thread CTAs share an SM.
+//   * the logs of a group kept in registers (no shared-memory scratch), so two 448-thread CTAs share an SM;
+//   * (r02final ncu: 70 % of the instructions sat before the sort, three quarters of them control and moves) both table
+//     levels read without a branch, one log for the fraction's front factor, log2FC left to dk_ttest_need_log2fc.
 // Arithmetic that decides exact comparisons is untouched: the logs and their sequential sums, mean = sum / n by a true
 // division, the sum of squared deviations (sd == 0 <=> that sum == 0; TtestFilter.c:128). Everything else moves by
 // a few ulp at most, far inside the 1e-9 contract (tests/test_gpu_parity.py).
