@@ -162,7 +162,7 @@ void dk_nf_end(dk_ctx *ctx, dk_nf_state *st);
  * reference aborts inside Boost).
  * log2FC (TtestFilter.c:72-75,433) is read by the reference for the rows it prints only: for groups of <= 8 samples in
  * column order it is computed when first read (by dk_ttest_filter at the candidate rows, by dk_ttest_export_rows at every
- * row), from the matrix `m`, which must therefore outlive the dk_ttest (as dk_ttest_export_survivors already requires). */
+ * row), from the matrix `m`, which must therefore outlive the test object, as dk_ttest_export_survivors already requires. */
 int dk_ttest_rows(dk_ctx *ctx, const dk_matrix *m, const double *nf,
                   const int *idxA, int nA, const int *idxB, int nB, dk_ttest **out);
 /* TtestFilter -l: Poisson likelihood ratio of the two group means of (count+1) against the pooled rate
