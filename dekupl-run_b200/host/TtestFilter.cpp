@@ -39,10 +39,10 @@ int main(int argc, char *argv[])
     const char *conditionA = argv[optind++], *conditionB = argv[optind++];
 
     dk_async_init_start();                      // CUDA context comes up while the table is inflated and parsed
-    DkFile f;
-    if (!f.load(counts_file)) { fprintf(stderr, "Failed to open %s\n", counts_file); exit(EXIT_FAILURE); }
-    DkMatrixText mt;
-    size_t bad = mt.parse(f, true);
+    DkMatrixText mt;                            // read in blocks: only the packed counts and the tags stay in memory
+    bool opened = false;
+    size_t bad = mt.load(counts_file, true, opened);
+    if (!opened) { fprintf(stderr, "Failed to open %s\n", counts_file); exit(EXIT_FAILURE); }
     const int S = mt.S;
 
     // conditions: skip header; per line sample, condition, NF (TtestFilter.c:251-284)
@@ -118,7 +118,7 @@ int main(int argc, char *argv[])
         CHECK(dk_ttest_export_rows(ctx, t, p.data(), nullptr, nullptr));
         DkOut o;
         o.gz = pf;
-        for (uint64_t i = 0; i < mt.R; i++) { o.put(mt.tags[i].first, mt.tags[i].second); o.printf_("\t%f\n", p[i]); }
+        for (uint64_t i = 0; i < mt.R; i++) { o.put(mt.tag(i), mt.tag_len(i)); o.printf_("\t%f\n", p[i]); }
         o.flush();
         gzclose(pf);
     }
@@ -136,7 +136,7 @@ int main(int argc, char *argv[])
     DkOut out;
     out.fp = stdout;
     for (uint64_t i = 0; i < D; i++) {   // :487-489
-        out.put(mt.tags[row[i]].first, mt.tags[row[i]].second);
+        out.put(mt.tag(row[i]), mt.tag_len(row[i]));
         out.printf_("\t%f", pa[i]); out.printf_("\t%f", mA[i]); out.printf_("\t%f", mB[i]); out.printf_("\t%f", fc[i]);
         for (int j = 0; j < S; j++) out.printf_("\t%.2f", norm[i * (size_t)S + j]);
         out.putc_('\n');

@@ -16,10 +16,10 @@ int main(int argc, char *argv[])
     }
     const char *path = argv[optind];
     dk_async_init_start();                      // CUDA context comes up while the table is inflated and parsed
-    DkFile f;
-    if (!f.load(path)) { fprintf(stderr, "Failed to open %s\n", path); exit(EXIT_FAILURE); }
-    DkMatrixText mt;
-    size_t bad = mt.parse(f, false);
+    DkMatrixText mt;                            // read in blocks: only the packed counts stay in memory
+    bool opened = false;
+    size_t bad = mt.load(path, false, opened);
+    if (!opened) { fprintf(stderr, "Failed to open %s\n", path); exit(EXIT_FAILURE); }
     if (bad) { fprintf(stderr, "inconsistent number of column (line %zu)\n", bad); exit(EXIT_FAILURE); }
     if (mt.S < 1 || mt.S > DK_MAX_SAMPLES) { fprintf(stderr, "computeNF: %d samples unsupported (1..%d)\n", mt.S, DK_MAX_SAMPLES); return EXIT_FAILURE; }
     dk_ctx *ctx = nullptr;

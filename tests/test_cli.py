@@ -96,6 +96,62 @@ def test_block_streamed_tokeniser_matches_the_in_memory_one(tmp_path):
     assert r.stdout.count(b"\n") == n
 
 
+def test_block_streamed_table_reader_matches_the_whole_file_one(tmp_path):
+    """computeNF and TtestFilter read the count table through DkMatrixText::load (dk_matrix_text.h), a block at a time;
+    test_matrix_text reads the same file with the whole-file reader too and compares names, rows, counts, tags and the
+    reported inconsistent line — for blocks down to 64 bytes, one to seven parser threads, and the irregular inputs that
+    must fall back to the token-by-token reader (a short row in the middle, a row split over two lines, CR LF)."""
+    rng = np.random.default_rng(3)
+
+    def table(n, S=6, trail=True):
+        lines = ["tag\t" + "\t".join("s%d" % i for i in range(S))]
+        for _ in range(n):
+            lines.append("".join(rng.choice(list("ACGT"), 31)) + "\t" + "\t".join(str(int(v)) for v in rng.integers(0, 5000, S)))
+        return ("\n".join(lines) + ("\n" if trail else "")).encode()
+
+    cases = {
+        "regular.tsv": (table(3000), 3000, 0),
+        "no_trailing_newline.tsv": (table(777, trail=False), 777, 0),
+        "header_only.tsv": (b"tag\ta\tb\n", 0, 0),
+        "header_no_newline.tsv": (b"tag\ta\tb", 0, 0),
+        "empty.tsv": (b"", 0, 0),
+        "one_row.tsv": (b"tag\ta\tb\nACGT\t1\t2\n", 1, 0),
+        "short_last_row.tsv": (b"tag\ta\tb\tc\nACGT\t1\t2\t3\nCCGT\t4", 2, 0),          # padded with zeros at EOF (computeNF.c:124-131)
+        "short_last_row_nl.tsv": (b"tag\ta\tb\tc\nACGT\t1\t2\t3\nCCGT\t4\n", 2, 0),
+        "blank_line_end.tsv": (table(100) + b"\n", 100, 0),
+        "space_separated.tsv": (table(300).replace(b"\t", b" "), 300, 0),
+        "long_lines.tsv": (table(40, S=200), 40, 0),
+    }
+    t = table(2000).split(b"\n")
+    t[1200] = t[1200].rsplit(b"\t", 1)[0]
+    cases["short_row_in_the_middle.tsv"] = (b"\n".join(t), None, 1200)
+    t = table(2000).split(b"\n")
+    t[37] += b"\t9"
+    cases["long_row.tsv"] = (b"\n".join(t), None, 37)
+    t = table(500).split(b"\n")
+    a = t[250].split(b"\t")
+    t[250] = b"\t".join(a[:4]) + b"\n" + b"\t".join(a[4:])        # the reference reads S tokens whatever the line ends: one row
+    cases["row_over_two_lines.tsv"] = (b"\n".join(t), 500, 0)
+    for nm, (data, _, _) in cases.items():
+        (tmp_path / nm).write_bytes(data)
+    reg = cases["regular.tsv"][0]
+    (tmp_path / "two_members.gz").write_bytes(gzip.compress(reg[:100000]) + gzip.compress(reg[100000:]))
+    cases["two_members.gz"] = (None, 3000, 0)
+    for nm, (_, rows, bad) in cases.items():
+        outs = set()
+        for block in (64, 100, 333, 4096, 64 << 20):
+            for threads in ("1", "4", "7"):
+                r = subprocess.run([os.path.join(BIN, "test_matrix_text"), str(tmp_path / nm), str(block)], capture_output=True,
+                                   text=True, env={**os.environ, "DK_PARSE_THREADS": threads})
+                assert r.returncode == 0, (nm, block, threads, r.stdout)
+                outs.add(r.stdout)
+        assert len(outs) == 1, (nm, outs)
+        S, R, b, _ = outs.pop().split()
+        assert int(b) == bad, nm
+        if rows is not None:
+            assert int(R) == rows, nm
+
+
 @pytest.mark.gpu
 def test_joinCounts_cli_matches_reference_binary_bytes(tmp_path):
     for ci, case in enumerate(load_json("join_cases.json")):
