@@ -9,6 +9,7 @@
 #include <atomic>
 #include <thread>
 #include "../../include/dekupl_b200.h"
+#include <sys/stat.h>
 #include "dk_text.h"
 
 int main(int argc, char *argv[])
@@ -45,6 +46,16 @@ int main(int argc, char *argv[])
         size_t len;
         bool first = true;
         int k = 0;
+        {   // one allocation instead of a doubling series: ~34 bytes of text per record, gzip shrinks a dump about 4x
+            struct stat sb;
+            if (stat(path, &sb) == 0 && S_ISREG(sb.st_mode)) {
+                const size_t n = strlen(path);
+                const bool gz = n > 3 && strcmp(path + n - 3, ".gz") == 0;
+                const size_t guess = (size_t)sb.st_size * (gz ? 4 : 1) / 34 + 16;
+                keys[i].reserve(guess);
+                cnts[i].reserve(guess);
+            }
+        }
         // joinCounts.c:55-68 (first record: skip the rest of its line) and :86-92 (then strictly token pairs)
         while (cur.token(s, len)) {
             if (len == 0 && cur.eof()) break;
