@@ -81,6 +81,8 @@ extern "C" int dk_ttest_filter(dk_ctx *ctx, dk_ttest *t, double pmax, double fmi
     if (t->p_cut < 1.0 && pmax > t->p_cut)
         return dk_fail(ctx, DK_ERR_ARG, "ttest_filter: pmax %g exceeds the cut %g the adjusted p-values were computed for", pmax, t->p_cut);
     cudaStream_t st = ctx->stream;
+    // log2FC is read at the candidate rows (or at every row without a candidate list)
+    DK_TRY(dk_ttest_need_log2fc(ctx, t, t->cand_row, t->cand_row ? t->n_cand : 0));
     unsigned long long *ctr = (unsigned long long *)dk_dev_alloc(ctx, 64);
     if (!ctr) return DK_ERR_NOMEM;
     DK_CUDA(ctx, cudaMemsetAsync(ctr, 0, 64, st));
@@ -89,8 +91,6 @@ extern "C" int dk_ttest_filter(dk_ctx *ctx, dk_ttest *t, double pmax, double fmi
     const bool by_cand = t->cand_row != nullptr;                      // the list the adjusted values were written through
     const unsigned cgrid = (unsigned)((t->n_cand + 255) / 256);
     uint64_t D = 0;
-    // log2FC is read at the candidate rows (or at every row without a candidate list)
-    DK_TRY(dk_ttest_need_log2fc(ctx, t, by_cand ? t->cand_row : nullptr, by_cand ? t->n_cand : 0));
     if (t->R && !(by_cand && t->n_cand == 0)) {
         if (by_cand) k_filter_cand<<<cgrid, 256, 0, st>>>(t->cand_row, t->n_cand, t->p_adj, t->log2fc, pmax, fmin_, ctr, nullptr, 0,
                                                          (unsigned long long *)t->tie_counts);
