@@ -210,3 +210,27 @@ def test_student_t_tail_two_evaluation_paths_agree():
         np.testing.assert_allclose(orc.student_t_2tail(t, 1.0), cauchy, rtol=1e-13)
         np.testing.assert_allclose(orc.student_t_2tail_boost_branches(t, 1.0), cauchy, rtol=1e-13)
         np.testing.assert_allclose(orc.student_t_2tail(t, 2.0), 2 / (np.sqrt(2 + t * t) * (np.sqrt(2 + t * t) + t)), rtol=1e-13)
+
+
+def test_gamma_ratio_series_of_the_row_kernel():
+    """k_ttest_rows8 (dk_ttest.cu) takes Gamma(v+1/2)/Gamma(v) from an upward shift to w >= 8 and a 6-term asymptotic
+    series; this is the same arithmetic in numpy against 40-digit mpmath over the v = df/2 range of groups of 2..8 samples
+    and beyond (exp(gammaln - gammaln) cancels to 3e-13 at v ~ 200 and cannot referee). The kernel's p-values are held
+    to 1e-9 relative: the ratio must be far inside that."""
+    mp = pytest.importorskip("mpmath")
+    mp.mp.dps = 40
+    rng = np.random.default_rng(5)
+    v = np.concatenate([rng.uniform(0.5, 8.0, 3000), rng.uniform(8.0, 200.0, 1000)])
+    num, dg, w = np.ones_like(v), np.ones_like(v), v.copy()
+    for _ in range(8):
+        m = w < 8.0
+        num[m] *= w[m]
+        dg[m] *= w[m] + 0.5
+        w[m] += 1.0
+    assert (w >= 8.0).all()
+    r = 1.0 / w
+    rr = r * r
+    ser = r * (-1 / 8 + rr * (1 / 192 + rr * (-1 / 640 + rr * (17 / 14336 + rr * (-31 / 18432 + rr * (691 / 180224))))))
+    got = np.sqrt(w) * np.exp(ser) * num / dg
+    want = np.array([float(mp.gamma(mp.mpf(float(x)) + 0.5) / mp.gamma(mp.mpf(float(x)))) for x in v])
+    assert np.max(np.abs(got / want - 1)) < 5e-14
